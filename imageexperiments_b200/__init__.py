@@ -1,0 +1,12 @@
+"""imageexperiments_b200 — B200-native encoder hot path of mnesbit/ImageExperiments' CompressionLib (`.mn` format).
+
+Only the path BASELINE.json names lives here: csrc/ (CUDA kernels + C ABI, built into libmnenc.so) and the
+host-side mirror of the reference's encoder interface (compressed.py).
+"""
+from .compressed import (CompressionContextFast, createCompressionContextFast, createQuantizationTables, encodeImageFast,
+                         lastSymbols, packSymbols, planSequenceHost)
+from .dictionary import Dictionary
+from ._lib import MnencError
+
+__all__ = ["CompressionContextFast", "createCompressionContextFast", "createQuantizationTables", "encodeImageFast", "lastSymbols",
+           "packSymbols", "planSequenceHost", "Dictionary", "MnencError"]

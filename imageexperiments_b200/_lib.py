@@ -1,0 +1,63 @@
+"""ctypes binding of the C ABI in include/mnenc.h (imageexperiments_b200/libmnenc.so).
+
+There is no fallback: a missing or unloadable library raises ImportError-like RuntimeError, and every GPU
+entry point returns an error code (raised as MnencError) when no sm_100 device is usable.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libmnenc.so")
+
+_vp, _sz = C.c_void_p, C.c_size_t
+
+#: every symbol include/mnenc.h declares (checked by tests/test_abi.py)
+EXPORTS = (
+    "mnenc_last_error", "mnenc_create", "mnenc_destroy", "mnenc_quant_tables", "mnenc_set_quant", "mnenc_encode_rgb8",
+    "mnenc_encode_rgb8_device", "mnenc_free", "mnenc_get_symbols", "mnenc_pack_symbols", "mnenc_last_timing", "mnenc_last_work",
+    "mnenc_debug_plan_sequence",
+)
+
+
+class MnencError(RuntimeError):
+    def __init__(self, code: int, text: str):
+        super().__init__(f"mnenc error {code}: {text}")
+        self.code = code
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(make -C imageexperiments_b200/csrc). There is no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    L.mnenc_last_error.restype = C.c_char_p
+    L.mnenc_create.argtypes = [_vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp]
+    L.mnenc_destroy.argtypes = [_vp]
+    L.mnenc_destroy.restype = None
+    L.mnenc_quant_tables.argtypes = [C.c_int, C.c_int, C.c_double, _vp]
+    L.mnenc_set_quant.argtypes = [_vp, _vp]
+    L.mnenc_encode_rgb8.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp, _vp]
+    L.mnenc_encode_rgb8_device.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp, _vp]
+    L.mnenc_free.argtypes = [_vp]
+    L.mnenc_free.restype = None
+    L.mnenc_get_symbols.argtypes = [_vp, _vp, _vp]
+    L.mnenc_pack_symbols.argtypes = [_vp, _sz, _sz, _vp, _vp, _vp, _vp]
+    L.mnenc_last_timing.argtypes = [_vp, _vp]
+    L.mnenc_last_work.argtypes = [_vp, _vp, _vp, _vp]
+    L.mnenc_debug_plan_sequence.argtypes = [_vp, _vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _vp]
+    _lib = L
+    return L
+
+
+def check(rc: int) -> int:
+    if rc < 0:
+        raise MnencError(rc, load().mnenc_last_error().decode(errors="replace"))
+    return rc

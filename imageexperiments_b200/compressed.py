@@ -1,0 +1,159 @@
+"""Host-side mirror of the reference's encoder interface (CompressionLib/inc/CompressedImage.h:54-76), backed by
+the sm_100a library through the C ABI of include/mnenc.h.
+
+    ctx = createCompressionContextFast(32, 8, 3.5)         # CompressedImage.cpp:317
+    data = encodeImageFast(rgb, ctx)                       # CompressedImage.cpp:578 -> bytes of the .mn stream
+
+Names and argument meaning follow the reference; Python conveniences: images are HxWx3 uint8 numpy arrays (or
+CUDA torch tensors for the device entry point), the quality parameter is ``bppAllocation`` (a float, or "max"
+as in Compression.cpp:104-114), and errors are exceptions (MnencError) instead of thrown pointers.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple, Union
+
+import numpy as np
+
+from . import _lib
+from .dictionary import Dictionary
+
+_vp = C.c_void_p
+
+
+def _p(a: np.ndarray):
+    return a.ctypes.data_as(_vp)
+
+
+def createQuantizationTables(K: int, blockSize: int, bppAllocation: float) -> np.ndarray:
+    """float overload of compressed::createQuantizationTables (CompressedImage.cpp:168-210) -> [3K] (Y,U,V)."""
+    q = np.zeros(3 * K, np.float32)
+    _lib.check(_lib.load().mnenc_quant_tables(K, blockSize, float(bppAllocation), _p(q)))
+    return q
+
+
+class CompressionContextFast:
+    """compressed::CompressionContextFast (CompressedImage.h:46-55) living on one B200."""
+
+    def __init__(self, K: int, blockSize: int, quant: np.ndarray, dictionary: Dictionary, device: int = 0):
+        self.K, self.BlockSize, self.device = K, blockSize, device
+        self.dictionary = dictionary
+        self._h = _vp()
+        L = _lib.load()
+        d = dictionary
+        _lib.check(L.mnenc_create(C.byref(self._h), device, K, blockSize, _p(d.base), d.n_base, _p(d.detail_rows), _p(d.detail[0]),
+                                  _p(d.detail[1]), _p(d.detail[2])))
+        self.setQuant(quant)
+
+    def setQuant(self, quant) -> None:
+        self.Quant = np.ascontiguousarray(quant, np.float32).reshape(3 * self.K).copy()
+        _lib.check(_lib.load().mnenc_set_quant(self._h, _p(self.Quant)))
+
+    def close(self) -> None:
+        if self._h:
+            _lib.load().mnenc_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- accounting of the last encode --------------------------------------------------------------
+    def last_timing(self) -> Tuple[np.ndarray, int]:
+        ms = np.zeros(8, np.float32)
+        n = _lib.check(_lib.load().mnenc_last_timing(self._h, _p(ms)))
+        return ms, n
+
+    def last_work(self) -> Tuple[float, int, int]:
+        f, s, b = C.c_double(), C.c_uint64(), C.c_uint64()
+        _lib.check(_lib.load().mnenc_last_work(self._h, C.byref(f), C.byref(s), C.byref(b)))
+        return f.value, s.value, b.value
+
+
+def createCompressionContextFast(K: int = 32, blockSize: int = 8, bppAllocation: Union[float, str] = 3.5,
+                                 dictionary: Optional[Dictionary] = None, device: int = 0) -> CompressionContextFast:
+    """compressed::createCompressionContextFast (CompressedImage.cpp:317-341); the dictionary is imported data."""
+    if dictionary is None:
+        dictionary = Dictionary.load()
+    if isinstance(bppAllocation, str):
+        if bppAllocation != "max":
+            raise ValueError("quality is a number or 'max'")
+        quant = np.ones(3 * K, np.float32)  # Compression.cpp:104-114: "max" sets every quantiser to 1
+    else:
+        quant = createQuantizationTables(K, blockSize, bppAllocation)
+    return CompressionContextFast(K, blockSize, quant, dictionary, device)
+
+
+def _take(out: _vp, n: int) -> bytes:
+    try:
+        return C.string_at(out, n)
+    finally:
+        _lib.load().mnenc_free(out)
+
+
+def encodeImageFast(imgIn, context: CompressionContextFast) -> bytes:
+    """compressed::encodeImageFast (CompressedImage.cpp:578-633). ``imgIn``: HxWx3 uint8 numpy array on the host
+    (copied to the GPU inside the call) or a CUDA torch uint8 tensor of the same shape (already resident)."""
+    L = _lib.load()
+    out, n = _vp(), C.c_size_t()
+    if isinstance(imgIn, np.ndarray):
+        if imgIn.dtype != np.uint8 or imgIn.ndim != 3 or imgIn.shape[2] != 3:
+            raise ValueError("expected HxWx3 uint8")
+        if not imgIn.flags.c_contiguous:
+            imgIn = np.ascontiguousarray(imgIn)
+        h, w, _ = imgIn.shape
+        _lib.check(L.mnenc_encode_rgb8(context._h, _p(imgIn), w, h, imgIn.strides[0], C.byref(out), C.byref(n)))
+    else:  # torch tensor
+        if not imgIn.is_cuda:
+            if str(imgIn.dtype) != "torch.uint8" or imgIn.dim() != 3 or imgIn.shape[2] != 3 or not imgIn.is_contiguous():
+                raise ValueError("expected contiguous HxWx3 uint8")
+            h, w, _ = imgIn.shape
+            _lib.check(L.mnenc_encode_rgb8(context._h, _vp(imgIn.data_ptr()), w, h, 3 * w, C.byref(out), C.byref(n)))
+        else:
+            if str(imgIn.dtype) != "torch.uint8" or imgIn.dim() != 3 or imgIn.shape[2] != 3 or not imgIn.is_contiguous():
+                raise ValueError("expected contiguous HxWx3 uint8")
+            if imgIn.device.index != context.device:
+                raise ValueError("tensor is on another device than the context")
+            h, w, _ = imgIn.shape
+            _lib.check(L.mnenc_encode_rgb8_device(context._h, _vp(imgIn.data_ptr()), w, h, 3 * w, C.byref(out), C.byref(n)))
+    return _take(out, n.value)
+
+
+def lastSymbols(context: CompressionContextFast, width: int, height: int) -> Tuple[np.ndarray, np.ndarray]:
+    """Debug tap: (counts [nblocks,3], pairs [nblocks,3,K,2]) of the last encode, column-major block order."""
+    nb = ((width + 7) // 8) * ((height + 7) // 8)
+    counts = np.zeros((nb, 3), np.uint16)
+    pairs = np.zeros((nb, 3, context.K, 2), np.uint16)
+    _lib.check(_lib.load().mnenc_get_symbols(context._h, _p(counts), _p(pairs)))
+    return counts, pairs
+
+
+def packSymbols(context: CompressionContextFast, width: int, height: int, counts: np.ndarray, pairs: np.ndarray) -> bytes:
+    """Back end only (compressed::writeCompressed, CompressedImage.cpp:462-519) on given symbols."""
+    counts = np.ascontiguousarray(counts, np.uint16)
+    pairs = np.ascontiguousarray(pairs, np.uint16)
+    nb = ((width + 7) // 8) * ((height + 7) // 8)
+    if counts.size != 3 * nb or pairs.size != 3 * nb * context.K * 2:
+        raise ValueError("symbol arrays do not match the image geometry")
+    out, n = _vp(), C.c_size_t()
+    _lib.check(_lib.load().mnenc_pack_symbols(context._h, width, height, _p(counts), _p(pairs), C.byref(out), C.byref(n)))
+    return _take(out, n.value)
+
+
+def planSequenceHost(symbols, freqs, first_pos):
+    """Host table builder test hook (mnenc_debug_plan_sequence): returns a dict describing the coding plan."""
+    symbols = np.ascontiguousarray(symbols, np.uint32)
+    freqs = np.ascontiguousarray(freqs, np.uint32)
+    first_pos = np.ascontiguousarray(first_pos, np.uint32)
+    n = symbols.size
+    codes = np.zeros(max(n, 1), np.uint32)
+    lens = np.zeros(max(n, 1), np.uint8)
+    cap = 64 + 8 * (n + 2) + 2 * 70
+    header = np.zeros(cap, np.uint8)
+    m, eofc, eofl, hb, pb = C.c_uint32(), C.c_uint32(), C.c_uint8(), C.c_uint64(), C.c_uint64()
+    _lib.check(_lib.load().mnenc_debug_plan_sequence(_p(symbols), _p(freqs), _p(first_pos), n, C.byref(m), _p(codes), _p(lens),
+                                                     C.byref(eofc), C.byref(eofl), _p(header), cap, C.byref(hb), C.byref(pb)))
+    return dict(golomb_m=m.value, codes=codes[:n], lens=lens[:n], eof_code=eofc.value, eof_len=eofl.value,
+                header=header[: (hb.value + 7) // 8].tobytes(), header_bits=hb.value, payload_bits=pb.value)

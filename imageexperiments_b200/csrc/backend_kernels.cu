@@ -1,0 +1,570 @@
+// Device side of the entropy back end. See backend_kernels.cuh for the reference functions replaced.
+// All kernels are HBM/L2-bound integer work: coalesced accesses, warp-shuffle prefix sums, grids sized by
+// the data (a few MB per image), no tensor-core shaping.
+#include "backend_kernels.cuh"
+
+namespace mnenc {
+
+namespace {
+
+constexpr unsigned kFull = 0xFFFFFFFFu;
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 8;
+constexpr int kScanTile = kScanThreads * kScanItems;
+
+// ------------------------------------------------------------------------------------------------
+// Generic three-phase device-wide exclusive scan with fused input / output functors.
+//   phase 1: blockSums[b] = sum of in(i) over tile b
+//   phase 2: one CTA turns blockSums into exclusive prefixes, total at blockSums[nTiles]
+//   phase 3: out(i, exclusive prefix of i, in(i)) for every i, and out.total(sum) once
+// `nPtr` (optional) is a device-resident element count that overrides `n` (tiles past it exit at once).
+// ------------------------------------------------------------------------------------------------
+template <class T>
+__device__ __forceinline__ T warpInclusive(T v, int lane) {
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        T t = __shfl_up_sync(kFull, v, off);
+        if (lane >= off) v += t;
+    }
+    return v;
+}
+
+// Exclusive prefix of `v` across the CTA (kScanThreads threads); returns the prefix, sets total.
+template <class T>
+__device__ __forceinline__ T blockExclusive(T v, T* total) {
+    __shared__ T warpSums[kScanThreads / 32];
+    __shared__ T blockTotal;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    T incl = warpInclusive(v, lane);
+    if (lane == 31) warpSums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        T w = lane < kScanThreads / 32 ? warpSums[lane] : T(0);
+        T wi = warpInclusive(w, lane);
+        if (lane < kScanThreads / 32) warpSums[lane] = wi - w;
+        if (lane == kScanThreads / 32 - 1) blockTotal = wi;
+    }
+    __syncthreads();
+    T res = warpSums[warp] + incl - v;
+    *total = blockTotal;
+    __syncthreads();
+    return res;
+}
+
+template <class T, class In>
+__global__ void __launch_bounds__(kScanThreads) scanReduceKernel(In in, uint32_t n, const uint32_t* nPtr, T* blockSums) {
+    if (nPtr) n = *nPtr;
+    const uint32_t base = blockIdx.x * kScanTile;
+    if (base >= n) {
+        if (threadIdx.x == 0) blockSums[blockIdx.x] = T(0);
+        return;
+    }
+    T sum = T(0);
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        const uint32_t i = base + k * kScanThreads + threadIdx.x;  // strided: coalesced, order irrelevant for a sum
+        if (i < n) sum += static_cast<T>(in(i));
+    }
+    T total;
+    blockExclusive(sum, &total);
+    if (threadIdx.x == 0) blockSums[blockIdx.x] = total;
+}
+
+template <class T>
+__global__ void __launch_bounds__(1024) scanBlockSumsKernel(T* blockSums, uint32_t nTiles) {
+    __shared__ T warpSums[32];
+    __shared__ T carryS, chunkTotal;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carryS = T(0);
+    __syncthreads();
+    for (uint32_t base = 0; base < nTiles; base += 1024) {
+        const uint32_t i = base + threadIdx.x;
+        const T v = i < nTiles ? blockSums[i] : T(0);
+        const T incl = warpInclusive(v, lane);
+        if (lane == 31) warpSums[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const T w = warpSums[lane];
+            const T wi = warpInclusive(w, lane);
+            warpSums[lane] = wi - w;
+            if (lane == 31) chunkTotal = wi;
+        }
+        __syncthreads();
+        if (i < nTiles) blockSums[i] = carryS + warpSums[warp] + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 0) carryS += chunkTotal;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) blockSums[nTiles] = carryS;
+}
+
+template <class T, class In, class Out>
+__global__ void __launch_bounds__(kScanThreads) scanApplyKernel(In in, Out out, uint32_t n, const uint32_t* nPtr, const T* blockSums,
+                                                                uint32_t nTiles) {
+    if (nPtr) n = *nPtr;
+    if (blockIdx.x == 0 && threadIdx.x == 0) out.total(blockSums[nTiles], n);
+    const uint32_t base = blockIdx.x * kScanTile;
+    if (base >= n) return;
+    // blocked arrangement: thread t owns items [base + t*8, base + t*8 + 8) so prefixes stay in registers
+    T vals[kScanItems];
+    T sum = T(0);
+    const uint32_t first = base + threadIdx.x * kScanItems;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        vals[k] = (first + k < n) ? static_cast<T>(in(first + k)) : T(0);
+        sum += vals[k];
+    }
+    T total;
+    T prefix = blockExclusive(sum, &total) + blockSums[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        if (first + k < n) out(first + k, prefix, vals[k]);
+        prefix += vals[k];
+    }
+}
+
+template <class T, class In, class Out>
+int deviceScan(In in, Out out, uint32_t nUpper, const uint32_t* nPtr, T* blockSums, cudaStream_t st) {
+    const uint32_t nTiles = (nUpper + kScanTile - 1) / kScanTile;
+    if (nTiles == 0) {
+        // still report the total (0) so downstream sentinels are written
+        scanBlockSumsKernel<T><<<1, 1024, 0, st>>>(blockSums, 0);
+        scanApplyKernel<T, In, Out><<<1, kScanThreads, 0, st>>>(in, out, 0, nPtr, blockSums, 0);
+        return 2;
+    }
+    scanReduceKernel<T, In><<<nTiles, kScanThreads, 0, st>>>(in, nUpper, nPtr, blockSums);
+    scanBlockSumsKernel<T><<<1, 1024, 0, st>>>(blockSums, nTiles);
+    scanApplyKernel<T, In, Out><<<nTiles, kScanThreads, 0, st>>>(in, out, nUpper, nPtr, blockSums, nTiles);
+    return 3;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Stream scatter (CompressedImage.cpp:612-629): stream (layer, depth) receives one entry from every block
+// whose count in that layer exceeds depth, in column-major block order == ascending block index.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTileBlocks) tileCountsKernel(const uint16_t* counts, uint32_t nblocks, int K, uint32_t* tileCounts) {
+    __shared__ uint32_t hist[3][kMaxK + 1];
+    for (int i = threadIdx.x; i < 3 * (kMaxK + 1); i += blockDim.x) (&hist[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t blk = blockIdx.x * kTileBlocks + threadIdx.x;
+    if (blk < nblocks) {
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) atomicAdd(&hist[ch][counts[3 * blk + ch]], 1u);
+    }
+    __syncthreads();
+    // #blocks with count > d  ==  sum_{c > d} hist[c]
+    for (int i = threadIdx.x; i < 3 * K; i += blockDim.x) {
+        const int ch = i / K, d = i - ch * K;
+        uint32_t s = 0;
+        for (int c = d + 1; c <= K; ++c) s += hist[ch][c];
+        tileCounts[static_cast<size_t>(blockIdx.x) * 3 * K + i] = s;
+    }
+}
+
+// One warp per (layer, depth) column: exclusive scan over tiles in place, column total -> totals[col].
+__global__ void tileScanKernel(uint32_t* tileCounts, uint32_t ntiles, int cols, uint32_t* totals) {
+    const int lane = threadIdx.x & 31;
+    const int col = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (col >= cols) return;
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < ntiles; base += 32) {
+        const uint32_t t = base + lane;
+        const uint32_t v = t < ntiles ? tileCounts[static_cast<size_t>(t) * cols + col] : 0;
+        const uint32_t incl = warpInclusive(v, lane);
+        if (t < ntiles) tileCounts[static_cast<size_t>(t) * cols + col] = carry + incl - v;
+        carry += __shfl_sync(kFull, incl, 31);
+    }
+    if (lane == 0) totals[col] = carry;
+}
+
+__global__ void __launch_bounds__(kTileBlocks) scatterKernel(const uint16_t* counts, const uint32_t* pairs, uint32_t nblocks, int K,
+                                                             const uint32_t* tileOffsets, const __grid_constant__ StreamOffsets so,
+                                                             uint16_t* arena) {
+    __shared__ uint32_t warpCnt[kTileBlocks / 32][kMaxK];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t blk = blockIdx.x * kTileBlocks + threadIdx.x;
+    for (int ch = 0; ch < 3; ++ch) {
+        const int count = blk < nblocks ? counts[3 * blk + ch] : 0;
+        // rank of this block among the tile's blocks with count > d, for every d < count
+        int maxCount = count;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) maxCount = max(maxCount, __shfl_xor_sync(kFull, maxCount, off));
+        for (int d = lane; d < K; d += 32) warpCnt[warp][d] = 0;
+        __syncwarp();
+        uint32_t myRank[kMaxK];  // only entries < count are meaningful; kept in local memory only when K large
+        for (int d = 0; d < maxCount; ++d) {
+            const unsigned m = __ballot_sync(kFull, count > d);
+            if (count > d) myRank[d] = __popc(m & ((1u << lane) - 1u));
+            if (lane == 0) warpCnt[warp][d] = __popc(m);
+        }
+        __syncthreads();
+        if (count > 0) {
+            const uint32_t* tileOff = tileOffsets + static_cast<size_t>(blockIdx.x) * 3 * K + ch * K;
+            const uint32_t* pp = pairs + (static_cast<size_t>(3) * blk + ch) * K;
+            for (int d = 0; d < count; ++d) {
+                uint32_t before = 0;
+                for (int w = 0; w < warp; ++w) before += warpCnt[w][d];
+                const uint32_t pos = tileOff[d] + before + myRank[d];
+                const uint32_t pr = pp[d];
+                const int sid = 2 * (ch * K + d);
+                arena[so.off[sid] + pos] = static_cast<uint16_t>(pr & 0xFFFFu);
+                arena[so.off[sid + 1] + pos] = static_cast<uint16_t>(pr >> 16);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// DC delta + zig-zag of the three depth-0 coefficient streams (CompressedImage.cpp:487-505), two steps so the
+// update can be written back in place.
+__global__ void dcDeltaKernel(const uint16_t* arena, const __grid_constant__ StreamOffsets so, int K, uint16_t* tmp, uint32_t tmpStride) {
+    const int ch = blockIdx.y;
+    const uint32_t off = so.off[2 * ch * K + 1], n = so.off[2 * ch * K + 2] - off;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t cur = arena[off + i];
+    const int32_t prev = i ? arena[off + i - 1] : 0;
+    const int32_t d = cur - prev;
+    tmp[static_cast<size_t>(ch) * tmpStride + i] = static_cast<uint16_t>((static_cast<uint32_t>(d) << 1) ^ static_cast<uint32_t>(d >> 31));
+}
+__global__ void dcWriteBackKernel(uint16_t* arena, const __grid_constant__ StreamOffsets so, int K, const uint16_t* tmp, uint32_t tmpStride) {
+    const int ch = blockIdx.y;
+    const uint32_t off = so.off[2 * ch * K + 1], n = so.off[2 * ch * K + 2] - off;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) arena[off + i] = tmp[static_cast<size_t>(ch) * tmpStride + i];
+}
+
+}  // namespace
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// Run-length coding of all 6K streams at once (Huffman.cpp:246-279). Runs never cross a stream boundary.
+//   run of v, length L  ->  floor(L / 32769) x [v, v, 32767]  then  L % 32769 == 1 ? [v] : >= 2 ? [v, v, rem-2]
+// ------------------------------------------------------------------------------------------------
+__global__ void rleFlagsKernel(const uint16_t* arena, uint32_t n, uint8_t* flags) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = (i == 0 || arena[i] != arena[i - 1]) ? 1 : 0;
+}
+__global__ void rleMarkStreamStartsKernel(const __grid_constant__ StreamOffsets so, int nStreams, uint32_t n, uint8_t* flags) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < nStreams && so.off[s] < n) flags[so.off[s]] = 1;
+}
+
+struct FlagIn {
+    const uint8_t* flags;
+    __device__ uint32_t operator()(uint32_t i) const { return flags[i]; }
+};
+struct RunStartOut {
+    uint32_t* runIdx;    // [n+1]
+    uint32_t* startPos;  // [n+1]
+    __device__ void operator()(uint32_t i, uint32_t prefix, uint32_t v) const {
+        runIdx[i] = prefix;
+        if (v) startPos[prefix] = i;
+    }
+    __device__ void total(uint32_t nRuns, uint32_t n) const {
+        runIdx[n] = nRuns;
+        startPos[nRuns] = n;
+    }
+};
+
+__device__ __forceinline__ uint32_t rleOutSize(uint32_t L) {
+    const uint32_t full = L / 32769u, rem = L - full * 32769u;
+    return 3u * full + (rem == 0 ? 0u : (rem == 1 ? 1u : 3u));
+}
+struct RunSizeIn {
+    const uint32_t* startPos;
+    __device__ uint32_t operator()(uint32_t r) const { return rleOutSize(startPos[r + 1] - startPos[r]); }
+};
+struct RleWriteOut {
+    const uint32_t* startPos;
+    const uint16_t* arena;
+    uint16_t* rle;
+    uint32_t* outOff;  // [nRuns+1]
+    __device__ void operator()(uint32_t r, uint32_t prefix, uint32_t /*size*/) const {
+        outOff[r] = prefix;
+        const uint32_t s0 = startPos[r];
+        uint32_t L = startPos[r + 1] - s0;
+        const uint16_t v = arena[s0];
+        uint32_t o = prefix;
+        while (L >= 32769u) {
+            rle[o] = v, rle[o + 1] = v, rle[o + 2] = 32767;
+            o += 3;
+            L -= 32769u;
+        }
+        if (L == 1) rle[o] = v;
+        else if (L >= 2) rle[o] = v, rle[o + 1] = v, rle[o + 2] = static_cast<uint16_t>(L - 2);
+    }
+    __device__ void total(uint32_t sum, uint32_t nRuns) const { outOff[nRuns] = sum; }
+};
+
+// One CTA: RLE-or-raw decision per stream (CompressedImage.cpp:508-516) and the table of coded sequences.
+__global__ void decideKernel(const __grid_constant__ StreamOffsets so, int nStreams, uint32_t nCounts, const uint32_t* runIdx,
+                             const uint32_t* outOff, SeqTable* table, SeqTable* hostMirror) {
+    __shared__ SeqTable t;
+    const int s = threadIdx.x;
+    if (s == 0) {
+        t.desc[0] = SeqDesc{nCounts, nCounts, 0u, 0u};
+        t.nRuns = runIdx[so.off[nStreams]];
+    }
+    if (s < nStreams) {
+        const uint32_t a = so.off[s], b = so.off[s + 1];
+        const uint32_t raw = b - a;
+        const uint32_t rleOff = outOff[runIdx[a]];
+        const uint32_t rleLen = outOff[runIdx[b]] - rleOff;
+        SeqDesc d;
+        d.rawLen = raw;
+        if (rleLen + 4 < raw) d.len = rleLen, d.off = rleOff, d.src = 2;
+        else d.len = raw, d.off = a, d.src = 1;
+        t.desc[1 + s] = d;
+    }
+    __syncthreads();
+    if (s == 0) {
+        uint32_t acc = 0;
+        for (int q = 0; q <= nStreams; ++q) {
+            t.start[q] = acc;
+            acc += t.desc[q].len;
+        }
+        t.start[nStreams + 1] = acc;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < static_cast<int>(sizeof(SeqTable) / 4); i += blockDim.x) {
+        reinterpret_cast<uint32_t*>(table)[i] = reinterpret_cast<const uint32_t*>(&t)[i];
+        if (hostMirror) reinterpret_cast<uint32_t*>(hostMirror)[i] = reinterpret_cast<const uint32_t*>(&t)[i];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Access to the concatenation of the coded sequences: element g in [0, M).
+// ------------------------------------------------------------------------------------------------
+struct SeqView {
+    const SeqTable* table;
+    const uint16_t* counts;
+    const uint16_t* arena;
+    const uint16_t* rle;
+};
+__device__ __forceinline__ int findSeq(const uint32_t* start, int nSeq, uint32_t g) {
+    int lo = 0, hi = nSeq;  // largest q with start[q] <= g, skipping empty sequences automatically
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (start[mid] <= g) lo = mid;
+        else hi = mid;
+    }
+    return lo;
+}
+__device__ __forceinline__ uint16_t loadSym(const SeqView& v, const SeqDesc& d, uint32_t k) {
+    const uint16_t* base = d.src == 0 ? v.counts : (d.src == 1 ? v.arena : v.rle);
+    return base[d.off + k];
+}
+
+// ------------------------------------------------------------------------------------------------
+// Histogram + first-occurrence position per sequence (Huffman.cpp:47-64).
+// Each CTA owns 4096 consecutive elements of the concatenation; symbols < 4096 of the CTA's first
+// sequence are privatised in shared memory, everything else goes straight to L2 atomics.
+// ------------------------------------------------------------------------------------------------
+constexpr int kHistChunk = 4096;
+__global__ void __launch_bounds__(256) histogramKernel(SeqView v, int nSeq, uint32_t* hist, uint32_t* firstPos, uint32_t* maxSym) {
+    __shared__ uint32_t sStart[kMaxSeq + 1];
+    __shared__ uint32_t sHist[kSmemHistBins];
+    __shared__ uint32_t sFirst[kSmemHistBins];
+    for (int i = threadIdx.x; i <= nSeq; i += blockDim.x) sStart[i] = v.table->start[i];
+    for (int i = threadIdx.x; i < kSmemHistBins; i += blockDim.x) sHist[i] = 0, sFirst[i] = 0xFFFFFFFFu;
+    __syncthreads();
+    const uint32_t M = sStart[nSeq];
+    const uint32_t base = blockIdx.x * kHistChunk;
+    if (base >= M) return;
+    const int q0 = findSeq(sStart, nSeq, base);
+    uint32_t localMax = 0;
+    int qPrev = -1;
+    SeqDesc d;
+    for (uint32_t g = base + threadIdx.x; g < min(base + kHistChunk, M); g += blockDim.x) {
+        const int q = (g < sStart[q0 + 1]) ? q0 : findSeq(sStart, nSeq, g);
+        if (q != qPrev) {
+            if (qPrev >= 0) atomicMax(&maxSym[qPrev], localMax);
+            localMax = 0;
+            d = v.table->desc[q];
+            qPrev = q;
+        }
+        const uint32_t k = g - sStart[q];
+        const uint32_t sym = loadSym(v, d, k);
+        localMax = max(localMax, sym);
+        if (q == q0 && sym < kSmemHistBins) {
+            atomicAdd(&sHist[sym], 1u);
+            atomicMin(&sFirst[sym], k);
+        } else {
+            atomicAdd(&hist[static_cast<size_t>(q) * kHistBins + sym], 1u);
+            atomicMin(&firstPos[static_cast<size_t>(q) * kHistBins + sym], k);
+        }
+    }
+    if (qPrev >= 0) atomicMax(&maxSym[qPrev], localMax);
+    __syncthreads();
+    for (int i = threadIdx.x; i < kSmemHistBins; i += blockDim.x) {
+        const uint32_t c = sHist[i];
+        if (c) {
+            atomicAdd(&hist[static_cast<size_t>(q0) * kHistBins + i], c);
+            atomicMin(&firstPos[static_cast<size_t>(q0) * kHistBins + i], sFirst[i]);
+        }
+    }
+}
+
+// Non-empty bins -> compact entry list; the bin's firstPos slot is re-used as symbol -> entry index map,
+// the hist bin is cleared for the next encode.
+__global__ void __launch_bounds__(256) compactKernel(uint32_t* hist, uint32_t* firstPos, const uint32_t* maxSym, HistEntry* entries,
+                                                     uint32_t* nEntries, uint32_t cap) {
+    const int q = blockIdx.y;
+    const uint32_t sym = blockIdx.x * blockDim.x + threadIdx.x;
+    if (blockIdx.x * blockDim.x > maxSym[q]) return;
+    const size_t bin = static_cast<size_t>(q) * kHistBins + sym;
+    const uint32_t c = hist[bin];
+    if (c) {
+        const uint32_t e = atomicAdd(nEntries, 1u);
+        if (e < cap) {
+            entries[e] = HistEntry{static_cast<uint32_t>(q), sym, c, firstPos[bin]};
+            firstPos[bin] = e;
+        }
+        hist[bin] = 0;
+    }
+}
+__global__ void resetHistogramKernel(const HistEntry* entries, uint32_t n, uint32_t* firstPos, uint32_t* maxSym, uint32_t* nEntries) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) firstPos[static_cast<size_t>(entries[i].seq) * kHistBins + entries[i].symbol] = 0xFFFFFFFFu;
+    if (i < kMaxSeq) maxSym[i] = 0;
+    if (i == 0) *nEntries = 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Bit packing (Huffman.cpp:157-161, BitBuffer.cpp:78-110,228-241): code length per symbol -> exclusive
+// scan = bit offset -> MSB-first OR into the zeroed output. The output is a byte stream; a logical
+// big-endian 32-bit word w covers bytes 4w..4w+3, so OR-ing the byte-swapped value needs no final pass.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t golombLength(uint32_t v, uint32_t M) {
+    const uint32_t q = v / M, rem = v - q * M;
+    const uint32_t b = 32 - __clz(M);
+    const uint32_t limit = (1u << (b + 1)) - M;
+    return rem < limit ? b + q + 1 : b + q + 2;
+}
+__device__ __forceinline__ void orBits(uint32_t* out, unsigned long long pos, uint32_t value, int width) {
+    // width <= 32 bits of `value`, placed MSB-first at absolute bit `pos`
+    if (width == 0) return;
+    const unsigned long long w = pos >> 5;
+    const int off = static_cast<int>(pos & 31);
+    const unsigned long long v = static_cast<unsigned long long>(value) << (64 - off - width);
+    const uint32_t hi = static_cast<uint32_t>(v >> 32), lo = static_cast<uint32_t>(v);
+    if (hi) atomicOr(&out[w], __byte_perm(hi, 0, 0x0123));
+    if (lo) atomicOr(&out[w + 1], __byte_perm(lo, 0, 0x0123));
+}
+
+struct CodeLenIn {
+    SeqView v;
+    int nSeq;
+    const CodeTable* codes;
+    const uint32_t* symToEntry;  // == firstPos after compaction
+    const unsigned long long* entryCodes;
+    __device__ uint32_t operator()(uint32_t g) const {
+        const int q = findSeq(v.table->start, nSeq, g);
+        const SeqDesc d = v.table->desc[q];
+        const uint32_t sym = loadSym(v, d, g - v.table->start[q]);
+        const uint32_t m = codes->seq[q].golombM;
+        if (m) return golombLength(sym, m);
+        return static_cast<uint32_t>(entryCodes[symToEntry[static_cast<size_t>(q) * kHistBins + sym]] >> 32);
+    }
+};
+struct PackOut {
+    SeqView v;
+    int nSeq;
+    const CodeTable* codes;
+    const uint32_t* symToEntry;
+    const unsigned long long* entryCodes;
+    uint32_t* out;
+    __device__ void operator()(uint32_t g, unsigned long long prefix, unsigned long long /*len*/) const {
+        const int q = findSeq(v.table->start, nSeq, g);
+        const SeqDesc d = v.table->desc[q];
+        const uint32_t sym = loadSym(v, d, g - v.table->start[q]);
+        const SeqCode c = codes->seq[q];
+        unsigned long long pos = c.bitBase + prefix;
+        if (c.golombM == 0) {
+            const unsigned long long e = entryCodes[symToEntry[static_cast<size_t>(q) * kHistBins + sym]];
+            orBits(out, pos, static_cast<uint32_t>(e), static_cast<int>(e >> 32));
+        } else {
+            const uint32_t M = c.golombM;
+            uint32_t quo = sym / M;
+            const uint32_t rem = sym - quo * M;
+            while (quo >= 32) {
+                orBits(out, pos, 0xFFFFFFFFu, 32);
+                pos += 32;
+                quo -= 32;
+            }
+            // quo ones then a zero
+            orBits(out, pos, ((1u << quo) - 1u) << 1, static_cast<int>(quo) + 1);
+            pos += quo + 1;
+            const uint32_t b = 32 - __clz(M);
+            const uint32_t limit = (1u << (b + 1)) - M;
+            if (rem < limit) orBits(out, pos, rem, static_cast<int>(b));
+            else orBits(out, pos, rem + limit, static_cast<int>(b) + 1);
+        }
+    }
+    __device__ void total(unsigned long long, uint32_t) const {}
+};
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// Launch wrappers
+// ------------------------------------------------------------------------------------------------
+int launchTileCounts(const BackendBuffers& b, cudaStream_t st) {
+    const int cols = 3 * b.K;
+    tileCountsKernel<<<b.ntiles, kTileBlocks, 0, st>>>(b.counts, b.nblocks, b.K, b.tileCounts);
+    const int warpsPerCta = 8;
+    tileScanKernel<<<(cols + warpsPerCta - 1) / warpsPerCta, warpsPerCta * 32, 0, st>>>(b.tileCounts, b.ntiles, cols, b.totals);
+    return 2;
+}
+
+int launchScatter(const BackendBuffers& b, const StreamOffsets& so, cudaStream_t st) {
+    scatterKernel<<<b.ntiles, kTileBlocks, 0, st>>>(b.counts, b.pairs, b.nblocks, b.K, b.tileCounts, so, b.arena);
+    const dim3 grid((b.nblocks + 255) / 256, 3);
+    dcDeltaKernel<<<grid, 256, 0, st>>>(b.arena, so, b.K, b.dcTmp, b.nblocks);
+    dcWriteBackKernel<<<grid, 256, 0, st>>>(b.arena, so, b.K, b.dcTmp, b.nblocks);
+    return 3;
+}
+
+int launchRleAndDecide(const BackendBuffers& b, const StreamOffsets& so, uint32_t N, cudaStream_t st) {
+    const int nStreams = 6 * b.K;
+    int launches = 0;
+    if (N) {
+        rleFlagsKernel<<<(N + 255) / 256, 256, 0, st>>>(b.arena, N, b.flags);
+        rleMarkStreamStartsKernel<<<(nStreams + 255) / 256, 256, 0, st>>>(so, nStreams, N, b.flags);
+        launches += 2;
+    }
+    launches += deviceScan<uint32_t>(FlagIn{b.flags}, RunStartOut{b.runIdx, b.startPos}, N, nullptr, b.blockSums32, st);
+    // runs: count lives in device memory (runIdx[N]); launch over the upper bound N, extra tiles exit at once
+    launches += deviceScan<uint32_t>(RunSizeIn{b.startPos}, RleWriteOut{b.startPos, b.arena, b.rleArena, b.outOff}, N, b.runIdx + N,
+                                     b.blockSums32, st);
+    return launches;
+}
+
+int launchDecide(const BackendBuffers& b, const StreamOffsets& so, SeqTable* hostMirror, cudaStream_t st) {
+    decideKernel<<<1, 256, 0, st>>>(so, 6 * b.K, 3 * b.nblocks, b.runIdx, b.outOff, b.seqTable, hostMirror);
+    return 1;
+}
+
+int launchHistogram(const BackendBuffers& b, uint32_t upperBoundM, int nSeq, cudaStream_t st) {
+    SeqView v{b.seqTable, b.counts, b.arena, b.rleArena};
+    const uint32_t grid = (upperBoundM + kHistChunk - 1) / kHistChunk;
+    if (grid) histogramKernel<<<grid, 256, 0, st>>>(v, nSeq, b.hist, b.firstPos, b.maxSym);
+    compactKernel<<<dim3(kHistBins / 256, nSeq), 256, 0, st>>>(b.hist, b.firstPos, b.maxSym, b.entries, b.nEntries, b.entryCap);
+    return grid ? 2 : 1;
+}
+
+int launchPack(const BackendBuffers& b, uint32_t M, int nSeq, cudaStream_t st) {
+    SeqView v{b.seqTable, b.counts, b.arena, b.rleArena};
+    return deviceScan<unsigned long long>(CodeLenIn{v, nSeq, b.codeTable, b.firstPos, b.entryCodes},
+                                          PackOut{v, nSeq, b.codeTable, b.firstPos, b.entryCodes, b.outWords}, M, nullptr, b.blockSums64, st);
+}
+
+int launchResetHistogram(const BackendBuffers& b, uint32_t nEntries, cudaStream_t st) {
+    const uint32_t n = nEntries > kMaxSeq ? nEntries : kMaxSeq;
+    resetHistogramKernel<<<(n + 255) / 256, 256, 0, st>>>(b.entries, nEntries, b.firstPos, b.maxSym, b.nEntries);
+    return 1;
+}
+
+}  // namespace mnenc

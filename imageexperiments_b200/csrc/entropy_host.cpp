@@ -1,0 +1,236 @@
+// Host side of the entropy back end: everything that the reference derives per coded sequence and that depends
+// only on the symbol histogram and the first-occurrence order:
+//   huffman::huffmanEncode table construction + header   CompressionLib/src/Huffman.cpp:65-156
+//   compressed::writeHuffmanOrGolomb choice              CompressionLib/src/CompressedImage.cpp:359-390
+//   bitbuffer::golombCodeLength                          CompressionLib/src/BitBuffer.cpp:260-269
+//   bitbuffer::eliasFanoSequenceCodeLength / write       CompressionLib/src/BitBuffer.cpp:292-317,345-354
+//   compressed::createQuantizationTables (float)         CompressionLib/src/CompressedImage.cpp:168-210
+// The per-symbol work (frequency counting, code emission) runs on the GPU; this file never sees the symbols.
+//
+// Huffman tie-breaking in the reference is a property of libstdc++'s std::unordered_map iteration order and
+// std::priority_queue sift order. The same containers are therefore driven with the same
+// operation sequence: keys inserted in first-occurrence order then the pseudo-EOF, leaves pushed in map
+// iteration order, pop-two/push-merged. Only (frequency) takes part in heap comparisons, so light nodes with
+// parent links replace the reference's child vectors (O(n log n) instead of O(n * depth) vector churn).
+#include <algorithm>
+#include <bit>
+#include <cmath>
+#include <numeric>
+#include <queue>
+#include <unordered_map>
+
+#include "mnenc_internal.h"
+#include "quant_data.h"
+
+namespace mnenc {
+
+void BitString::put(uint64_t value, int width) {
+    for (int i = width - 1; i >= 0; --i) {
+        if ((nbits & 7) == 0) bytes.push_back(0);
+        if ((value >> i) & 1ULL) bytes.back() |= static_cast<uint8_t>(0x80u >> (nbits & 7));
+        ++nbits;
+    }
+}
+
+namespace {
+
+constexpr uint32_t kEof = 0xFFFFFFFFu;  // Huffman.cpp:38
+
+inline uint32_t golombLen(uint32_t v, uint32_t M) {
+    const uint32_t q = v / M, rem = v % M;
+    const uint32_t b = std::bit_width(M);
+    const uint32_t limit = (1u << (b + 1)) - M;
+    return rem < limit ? b + q + 1 : b + q + 2;
+}
+
+struct HeapNode {
+    uint64_t freq;
+    uint32_t id;
+    uint32_t depth;
+};
+struct HeapGreater {
+    bool operator()(const HeapNode& a, const HeapNode& b) const { return a.freq > b.freq; }
+};
+
+struct Sym {
+    uint32_t symbol;
+    uint32_t len;
+    uint32_t code;
+    int origin;  // index in the caller's stats vector, -1 for EOF
+};
+
+}  // namespace
+
+void planSequence(const std::vector<SymbolStat>& stats, SequencePlan& plan) {
+    const size_t n = stats.size();
+    std::vector<int> order(n);
+    std::iota(order.begin(), order.end(), 0);
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return stats[a].firstPos < stats[b].firstPos; });
+
+    // --- frequency map in the reference's insertion order (Huffman.cpp:47-71) ---
+    std::unordered_map<uint32_t, uint32_t> slot;  // symbol -> leaf id
+    uint32_t symWidth = 1;
+    uint64_t dataCount = 0;
+    std::vector<uint64_t> leafFreq;
+    leafFreq.reserve(n + 1);
+    for (int i : order) {
+        symWidth = std::max<uint32_t>(symWidth, std::bit_width(stats[i].symbol));
+        slot[stats[i].symbol] = static_cast<uint32_t>(leafFreq.size());
+        leafFreq.push_back(stats[i].freq);
+        dataCount += stats[i].freq;
+    }
+    slot[kEof] = static_cast<uint32_t>(leafFreq.size());
+    leafFreq.push_back(0);
+    const size_t nLeaves = leafFreq.size();
+
+    // --- code lengths (Huffman.cpp:72-103) ---
+    std::vector<int32_t> parent(nLeaves, -1);
+    parent.reserve(2 * nLeaves);
+    std::priority_queue<HeapNode, std::vector<HeapNode>, HeapGreater> heap;
+    for (const auto& kv : slot) heap.push(HeapNode{leafFreq[kv.second], kv.second, 0});
+    while (heap.size() > 1) {
+        const HeapNode a = heap.top();
+        heap.pop();
+        const HeapNode b = heap.top();
+        heap.pop();
+        const uint32_t id = static_cast<uint32_t>(parent.size());
+        parent.push_back(-1);
+        parent[a.id] = static_cast<int32_t>(id);
+        parent[b.id] = static_cast<int32_t>(id);
+        heap.push(HeapNode{a.freq + b.freq, id, std::max(a.depth, b.depth) + 1});
+    }
+    const uint32_t maxLen = std::max<uint32_t>(heap.top().depth, 1);  // :110
+    // depth of every node from the root down (ids are created bottom-up, so parents have larger ids)
+    std::vector<uint32_t> depth(parent.size(), 0);
+    for (size_t i = parent.size(); i-- > 0;)
+        if (parent[i] >= 0) depth[i] = depth[parent[i]] + 1;
+
+    std::vector<Sym> sorted(nLeaves);
+    for (size_t k = 0; k < n; ++k) sorted[k] = Sym{stats[order[k]].symbol, depth[k], 0, order[k]};
+    sorted[n] = Sym{kEof, dataCount == 0 ? 1u : depth[n], 0, -1};  // empty input: EOF gets length 1 (:66-71)
+    std::sort(sorted.begin(), sorted.end(), [](const Sym& a, const Sym& b) {  // :28-36
+        return a.len == b.len ? a.symbol < b.symbol : a.len < b.len;
+    });
+
+    // --- canonical codes + header (Huffman.cpp:107-156) ---
+    BitString huff;
+    huff.put(maxLen, 8);
+    std::vector<uint32_t> counts;
+    uint32_t prevLen = 0, code = 0, count = 0;
+    for (Sym& e : sorted) {
+        if (e.len != prevLen) {
+            if (prevLen != 0) counts.push_back(count);
+            for (uint32_t l = prevLen + 1; l < e.len; ++l) counts.push_back(0);
+            count = 0;
+            code = (e.len - prevLen) >= 32 ? 0u : code << (e.len - prevLen);
+        }
+        e.code = code++;
+        ++count;
+        prevLen = e.len;
+    }
+    counts.push_back(count);
+    for (uint32_t c : counts) huff.put(c & 0xFFFFu, 16);
+    huff.put(symWidth, 8);
+    const uint32_t mask = (1u << symWidth) - 1u;
+    size_t pos = 0;
+    for (uint32_t c : counts) {
+        const uint32_t rangeLen = c & 0xFFFFu;
+        if (rangeLen == 0) continue;
+        // Elias-Fano iff its *upper bound* beats raw symbols (Huffman.cpp:148; BitBuffer.cpp:345-354)
+        const uint32_t m = std::bit_width(mask);
+        const uint32_t nb = std::bit_width(rangeLen);
+        const uint32_t lb = (m >= nb) ? m - nb : 0;
+        const uint32_t bound = rangeLen * (1 + lb) + (1u << (m - lb)) - 1;
+        if (bound < rangeLen * symWidth) {
+            uint32_t bucket = 0;
+            for (uint32_t k = 0; k < rangeLen; ++k) {  // BitBuffer.cpp:301-313
+                const uint32_t want = (sorted[pos + k].symbol & mask & 0xFFFFu) >> lb;
+                while (bucket != want) {
+                    huff.put(0, 1);
+                    ++bucket;
+                }
+                huff.put(1, 1);
+            }
+            for (uint32_t k = 0; k < rangeLen; ++k) huff.put(sorted[pos + k].symbol & mask & 0xFFFFu, static_cast<int>(lb));
+        } else {
+            for (uint32_t k = 0; k < rangeLen; ++k) huff.put(sorted[pos + k].symbol & mask & 0xFFFFu, static_cast<int>(symWidth));
+        }
+        pos += rangeLen;
+    }
+
+    plan.code.assign(n, 0);
+    plan.len.assign(n, 0);
+    uint64_t huffPayload = 0;
+    uint32_t longest = 0;
+    for (const Sym& e : sorted) {
+        longest = std::max(longest, e.len);
+        if (e.origin >= 0) {
+            plan.code[e.origin] = e.code;
+            plan.len[e.origin] = static_cast<uint8_t>(e.len);
+            huffPayload += static_cast<uint64_t>(stats[e.origin].freq) * e.len;
+        } else {
+            plan.eofCode = e.code;
+            plan.eofLen = static_cast<uint8_t>(e.len);
+        }
+    }
+    plan.maxCodeLen = longest;
+    const uint64_t huffBits = huff.nbits + huffPayload + plan.eofLen;
+
+    // --- Huffman vs Golomb (CompressedImage.cpp:362-379): first strictly smaller estimate wins ---
+    uint64_t best = huffBits;
+    int bestM = -1;
+    uint64_t bestPayload = 0;
+    for (int m = 1; m < 2048;) {
+        uint64_t est = 16;
+        for (const SymbolStat& s : stats) est += static_cast<uint64_t>(s.freq) * golombLen(s.symbol, static_cast<uint32_t>(m));
+        if (est < best) {
+            best = est;
+            bestM = m;
+            bestPayload = est - 16;
+        }
+        m = (m & 1) ? m + 1 : (m << 1) - 1;
+    }
+    plan.header = BitString();
+    if (bestM < 0) {
+        plan.golomb = false;
+        plan.golombM = 0;
+        plan.header.put(0, 1);
+        for (uint64_t i = 0; i < huff.nbits; ++i) plan.header.put((huff.bytes[i >> 3] >> (7 - (i & 7))) & 1u, 1);
+        plan.payloadBits = huffPayload;
+    } else {
+        plan.golomb = true;
+        plan.golombM = static_cast<uint32_t>(bestM);
+        plan.header.put(1, 1);
+        plan.header.put(static_cast<uint32_t>(bestM), 16);
+        plan.payloadBits = bestPayload;
+    }
+}
+
+int quantTables(int K, int blockSize, double bpp, float* out) {
+    if (K < 1 || K > 32 || blockSize < 1) return -1;
+    float allocated = 0.0f;
+    std::vector<float> alloc(3 * K), variances(3 * K);
+    for (int i = 0; i < K; ++i) {
+        variances[i] = static_cast<float>(kVarY[i]);
+        variances[i + K] = static_cast<float>(kVarU[i]);
+        variances[i + 2 * K] = static_cast<float>(kVarV[i]);
+    }
+    const float bs = static_cast<float>(blockSize);
+    while ((allocated / static_cast<double>(blockSize * blockSize)) < bpp) {
+        const ptrdiff_t index = std::max_element(variances.cbegin(), variances.cend()) - variances.cbegin();
+        alloc[index] += 1.0f;
+        variances[index] /= 2.0f;
+        allocated += 1.0f;
+        const float floorQ = (index == 0 || index == K || index == 2 * K) ? bs : 1.0f;
+        if (255.0f * bs * std::pow(0.5f, alloc[index]) < floorQ) variances[index] = 0.0f;
+    }
+    const float decay[3] = {static_cast<float>(kDecayY), static_cast<float>(kDecayU), static_cast<float>(kDecayV)};
+    for (int c = 0; c < 3; ++c)
+        for (int i = 0; i < K; ++i) {
+            const float floorQ = i == 0 ? bs : 1.0f;
+            out[c * K + i] = std::max(std::ceil(255.0f * bs * std::pow(decay[c], static_cast<float>(i)) * std::pow(0.5f, alloc[i + c * K])), floorQ);
+        }
+    return 0;
+}
+
+}  // namespace mnenc

@@ -1,0 +1,624 @@
+// C-ABI layer (include/mnenc.h) and the per-image orchestration of the encoder:
+//   H2D pixels -> matching-pursuit kernel -> stream scatter / DC delta / RLE -> histogram -> (host) code
+//   tables -> bit packing -> D2H -> header merge.
+// The host work between the two GPU phases is the table build of entropy_host.cpp (alphabet-sized, never
+// symbol-sized). Buffers are grow-only and live in the context, so steady-state encodes allocate nothing.
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/mnenc.h"
+#include "backend_kernels.cuh"
+#include "mnenc_internal.h"
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int code, const std::string& msg) {
+    g_error = msg;
+    return code;
+}
+
+#define CU(expr)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (expr);                                                                          \
+        if (e_ != cudaSuccess) return fail(MNENC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+double nowMs() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    template <class T>
+    T* as() const { return static_cast<T*>(p); }
+    ~DevBuf() {
+        if (p) cudaFree(p);
+    }
+};
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMallocHost(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    template <class T>
+    T* as() const { return static_cast<T*>(p); }
+    ~PinBuf() {
+        if (p) cudaFreeHost(p);
+    }
+};
+
+struct Overlay {  // host-written bits (headers, EOF codes) OR-ed into the packed payload
+    uint64_t bitPos;
+    mnenc::BitString bits;
+};
+
+}  // namespace
+
+struct mnenc_ctx {
+    int device = 0, K = 0, nBase = 0, numSMs = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[8] = {};
+    bool quantSet = false;
+    float hQuant[3 * mnenc::kMaxK] = {};
+    // dictionary
+    DevBuf baseT, detT, detRows, quant;
+    // image + symbols
+    DevBuf rgb, counts, pairs, mpScratch;
+    size_t lastW = 0, lastH = 0;
+    bool haveSymbols = false;
+    // back end
+    DevBuf tileCounts, totals, arena, dcTmp, flags, runIdx, startPos, outOff, rleArena, sums32, sums64, seqTable, hist, firstPos, maxSym,
+        entries, nEntries, entryCodes, codeTable, outWords;
+    uint32_t entryCap = 0;
+    bool histReady = false;
+    PinBuf hTotals, hSeqTable, hEntries, hNEntries, hEntryCodes, hCodeTable, hOut, hStats, hRgb;
+    // accounting
+    float ms[8] = {};
+    int launches = 0;
+    double mpFlops = 0;
+    uint64_t nSymbols = 0, nBits = 0;
+};
+
+namespace {
+
+using namespace mnenc;
+
+int ensureHistogram(mnenc_ctx* c) {
+    if (c->histReady) return MNENC_OK;
+    const size_t bins = static_cast<size_t>(kMaxSeq) * kHistBins;
+    CU(c->hist.ensure(bins * 4));
+    CU(c->firstPos.ensure(bins * 4));
+    CU(c->maxSym.ensure(kMaxSeq * 4));
+    CU(c->nEntries.ensure(4));
+    CU(cudaMemsetAsync(c->hist.p, 0, bins * 4, c->stream));
+    CU(cudaMemsetAsync(c->firstPos.p, 0xFF, bins * 4, c->stream));
+    CU(cudaMemsetAsync(c->maxSym.p, 0, kMaxSeq * 4, c->stream));
+    CU(cudaMemsetAsync(c->nEntries.p, 0, 4, c->stream));
+    if (c->entryCap == 0) {
+        c->entryCap = 1u << 16;
+        CU(c->entries.ensure(static_cast<size_t>(c->entryCap) * sizeof(HistEntry)));
+    }
+    c->histReady = true;
+    return MNENC_OK;
+}
+
+// Everything after the matching pursuit: counts/pairs (device) -> .mn bytes.
+int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t* outBytes) {
+    const int K = c->K;
+    const int nStreams = 6 * K, nSeq = nStreams + 1;
+    const uint32_t nbx = static_cast<uint32_t>((width + 7) / 8), nby = static_cast<uint32_t>((height + 7) / 8);
+    const uint32_t nblocks = nbx * nby;
+    const uint32_t ntiles = (nblocks + kTileBlocks - 1) / kTileBlocks;
+    cudaStream_t st = c->stream;
+
+    BackendBuffers b{};
+    b.counts = c->counts.as<uint16_t>();
+    b.pairs = c->pairs.as<uint32_t>();
+    b.K = K;
+    b.nblocks = nblocks;
+    b.ntiles = ntiles;
+    CU(c->tileCounts.ensure(static_cast<size_t>(ntiles) * 3 * K * 4 + 4));
+    CU(c->totals.ensure(3 * K * 4));
+    CU(c->dcTmp.ensure(static_cast<size_t>(nblocks) * 3 * 2 + 2));
+    CU(c->hTotals.ensure(3 * K * 4));
+    b.tileCounts = c->tileCounts.as<uint32_t>();
+    b.totals = c->totals.as<uint32_t>();
+    b.dcTmp = c->dcTmp.as<uint16_t>();
+
+    // ---- phase 1: stream sizes ----
+    CU(cudaEventRecord(c->ev[2], st));
+    c->launches += launchTileCounts(b, st);
+    CU(cudaMemcpyAsync(c->hTotals.p, b.totals, 3 * K * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    StreamOffsets so{};
+    uint64_t N64 = 0;
+    for (int ch = 0; ch < 3; ++ch)
+        for (int d = 0; d < K; ++d) {
+            const uint32_t n = c->hTotals.as<uint32_t>()[ch * K + d];
+            so.off[2 * (ch * K + d)] = static_cast<uint32_t>(N64);
+            so.off[2 * (ch * K + d) + 1] = static_cast<uint32_t>(N64 + n);
+            N64 += 2ull * n;
+        }
+    if (N64 + 3ull * nblocks >= 0xFFFFFFF0ull) return fail(MNENC_ERR_ARG, "image too large: more than 2^32 symbols");
+    const uint32_t N = static_cast<uint32_t>(N64);
+    so.off[nStreams] = N;
+
+    // ---- phase 2: scatter, DC delta, RLE, decision, histogram ----
+    const uint32_t upperM = N + 3 * nblocks;
+    CU(c->arena.ensure(static_cast<size_t>(N) * 2 + 16));
+    CU(c->flags.ensure(static_cast<size_t>(N) + 16));
+    CU(c->runIdx.ensure((static_cast<size_t>(N) + 2) * 4));
+    CU(c->startPos.ensure((static_cast<size_t>(N) + 2) * 4));
+    CU(c->outOff.ensure((static_cast<size_t>(N) + 2) * 4));
+    CU(c->rleArena.ensure((static_cast<size_t>(N) + N / 2 + 16) * 2));
+    CU(c->sums32.ensure((static_cast<size_t>(upperM) / 2048 + 4) * 4));
+    CU(c->sums64.ensure((static_cast<size_t>(upperM) / 2048 + 4) * 8));
+    CU(c->seqTable.ensure(sizeof(SeqTable)));
+    CU(c->hSeqTable.ensure(sizeof(SeqTable)));
+    CU(c->hNEntries.ensure(4));
+    if (int rc = ensureHistogram(c)) return rc;
+    b.arena = c->arena.as<uint16_t>();
+    b.flags = c->flags.as<uint8_t>();
+    b.runIdx = c->runIdx.as<uint32_t>();
+    b.startPos = c->startPos.as<uint32_t>();
+    b.outOff = c->outOff.as<uint32_t>();
+    b.rleArena = c->rleArena.as<uint16_t>();
+    b.blockSums32 = c->sums32.as<uint32_t>();
+    b.blockSums64 = c->sums64.as<unsigned long long>();
+    b.seqTable = c->seqTable.as<SeqTable>();
+    b.hist = c->hist.as<uint32_t>();
+    b.firstPos = c->firstPos.as<uint32_t>();
+    b.maxSym = c->maxSym.as<uint32_t>();
+    b.entries = c->entries.as<HistEntry>();
+    b.nEntries = c->nEntries.as<uint32_t>();
+    b.entryCap = c->entryCap;
+
+    c->launches += launchScatter(b, so, st);
+    c->launches += launchRleAndDecide(b, so, N, st);
+    c->launches += launchDecide(b, so, nullptr, st);
+    CU(cudaEventRecord(c->ev[3], st));
+    c->launches += launchHistogram(b, upperM, nSeq, st);
+    CU(cudaEventRecord(c->ev[4], st));
+    const uint32_t firstChunk = 1u << 16;
+    CU(c->hEntries.ensure(static_cast<size_t>(firstChunk) * sizeof(HistEntry)));
+    CU(cudaMemcpyAsync(c->hSeqTable.p, b.seqTable, sizeof(SeqTable), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(c->hNEntries.p, b.nEntries, 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(c->hEntries.p, b.entries, static_cast<size_t>(firstChunk) * sizeof(HistEntry), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    uint32_t nEntries = *c->hNEntries.as<uint32_t>();
+    if (nEntries > c->entryCap) {
+        // Rare: more distinct (sequence, symbol) pairs than the list holds. Grow and redo the histogram.
+        c->entryCap = nEntries + nEntries / 4;
+        CU(c->entries.ensure(static_cast<size_t>(c->entryCap) * sizeof(HistEntry)));
+        c->histReady = false;
+        if (int rc = ensureHistogram(c)) return rc;
+        b.entries = c->entries.as<HistEntry>();
+        b.entryCap = c->entryCap;
+        c->launches += launchHistogram(b, upperM, nSeq, st);
+        CU(cudaMemcpyAsync(c->hNEntries.p, b.nEntries, 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        nEntries = *c->hNEntries.as<uint32_t>();
+        if (nEntries > c->entryCap) return fail(MNENC_ERR_INTERNAL, "histogram entry list overflow");
+    }
+    if (nEntries > firstChunk || c->hEntries.cap < static_cast<size_t>(nEntries) * sizeof(HistEntry)) {
+        CU(c->hEntries.ensure(static_cast<size_t>(nEntries) * sizeof(HistEntry)));
+        CU(cudaMemcpyAsync(c->hEntries.p, b.entries, static_cast<size_t>(nEntries) * sizeof(HistEntry), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+
+    // ---- host: code tables, Huffman-vs-Golomb choice, bit layout ----
+    const double tHost0 = nowMs();
+    const SeqTable& seq = *c->hSeqTable.as<SeqTable>();
+    const HistEntry* ent = c->hEntries.as<HistEntry>();
+    std::vector<std::vector<SymbolStat>> stats(nSeq);
+    std::vector<std::vector<uint32_t>> entryOf(nSeq);
+    for (uint32_t e = 0; e < nEntries; ++e) {
+        if (ent[e].seq >= static_cast<uint32_t>(nSeq)) return fail(MNENC_ERR_INTERNAL, "bad histogram entry");
+        stats[ent[e].seq].push_back(SymbolStat{ent[e].symbol, ent[e].freq, ent[e].firstPos});
+        entryOf[ent[e].seq].push_back(e);
+    }
+    std::vector<SequencePlan> plans(nSeq);
+    for (int q = 0; q < nSeq; ++q) planSequence(stats[q], plans[q]);
+
+    CU(c->hEntryCodes.ensure(static_cast<size_t>(nEntries) * 8 + 8));
+    CU(c->hCodeTable.ensure(sizeof(CodeTable)));
+    CU(c->entryCodes.ensure(static_cast<size_t>(nEntries) * 8 + 8));
+    CU(c->codeTable.ensure(sizeof(CodeTable)));
+    unsigned long long* hCodes = c->hEntryCodes.as<unsigned long long>();
+    CodeTable& hTable = *c->hCodeTable.as<CodeTable>();
+    std::memset(&hTable, 0, sizeof(hTable));
+
+    std::vector<Overlay> overlays;
+    overlays.reserve(2 * nSeq + 1);
+    uint64_t cursor = 0;
+    {  // file header (CompressedImage.cpp:472-486)
+        Overlay h;
+        h.bitPos = 0;
+        h.bits.put(0x4D4E3234u, 32);
+        h.bits.put(static_cast<uint32_t>(width), 32);
+        h.bits.put(static_cast<uint32_t>(height), 32);
+        h.bits.put(static_cast<uint32_t>(K) & 0xFF, 8);
+        h.bits.put(8, 8);
+        for (int i = 0; i < 3 * K; ++i) h.bits.put(static_cast<uint16_t>(c->hQuant[(i / K) * kMaxK + (i % K)]), 16);
+        cursor = h.bits.nbits;
+        overlays.push_back(std::move(h));
+    }
+    uint64_t scanPrefix = 0;  // device exclusive scan value at the first symbol of sequence q
+    uint64_t totalPayload = 0;
+    for (int q = 0; q < nSeq; ++q) {
+        SequencePlan& p = plans[q];
+        if (!p.golomb && p.maxCodeLen > 32) return fail(MNENC_ERR_INTERNAL, "Huffman code longer than 32 bits");
+        Overlay h;
+        h.bitPos = cursor;
+        if (q > 0) {  // RLE flag (+ RLE length) precedes every symbol stream (CompressedImage.cpp:509-515)
+            if (seq.desc[q].src == 2) {
+                h.bits.put(1, 1);
+                h.bits.put(seq.desc[q].len, 32);
+            } else {
+                h.bits.put(0, 1);
+            }
+        }
+        for (uint64_t i = 0; i < p.header.nbits; ++i) h.bits.put((p.header.bytes[i >> 3] >> (7 - (i & 7))) & 1u, 1);
+        cursor += h.bits.nbits;
+        overlays.push_back(std::move(h));
+        hTable.seq[q].bitBase = cursor - scanPrefix;  // modular arithmetic: position = bitBase + scan value
+        hTable.seq[q].golombM = p.golomb ? p.golombM : 0;
+        cursor += p.payloadBits;
+        scanPrefix += p.payloadBits;
+        totalPayload += p.payloadBits;
+        if (!p.golomb) {
+            Overlay e;
+            e.bitPos = cursor;
+            e.bits.put(p.eofCode, p.eofLen);
+            cursor += p.eofLen;
+            overlays.push_back(std::move(e));
+            for (size_t k = 0; k < entryOf[q].size(); ++k)
+                hCodes[entryOf[q][k]] = static_cast<unsigned long long>(p.code[k]) | (static_cast<unsigned long long>(p.len[k]) << 32);
+        } else {
+            for (size_t k = 0; k < entryOf[q].size(); ++k) hCodes[entryOf[q][k]] = 0;
+        }
+    }
+    const uint64_t totalBits = cursor;
+    const size_t totalBytes = static_cast<size_t>((totalBits + 7) / 8);
+    const uint32_t M = seq.start[nSeq];
+    c->ms[4] = static_cast<float>(nowMs() - tHost0);
+
+    // ---- phase 3: bit packing ----
+    const size_t outAlloc = (totalBytes + 16 + 3) / 4 * 4;
+    CU(c->outWords.ensure(outAlloc));
+    CU(c->hOut.ensure(outAlloc));
+    CU(cudaMemcpyAsync(c->entryCodes.p, hCodes, static_cast<size_t>(nEntries) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(c->codeTable.p, &hTable, sizeof(CodeTable), cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(c->outWords.p, 0, outAlloc, st));
+    b.entryCodes = c->entryCodes.as<unsigned long long>();
+    b.codeTable = c->codeTable.as<CodeTable>();
+    b.outWords = c->outWords.as<uint32_t>();
+    CU(cudaEventRecord(c->ev[5], st));
+    c->launches += launchPack(b, M, nSeq, st);
+    c->launches += launchResetHistogram(b, nEntries, st);
+    CU(cudaEventRecord(c->ev[6], st));
+    CU(cudaMemcpyAsync(c->hOut.p, c->outWords.p, totalBytes, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const double tMerge0 = nowMs();
+
+    // ---- merge host-written bits ----
+    uint8_t* res = static_cast<uint8_t*>(std::malloc(totalBytes ? totalBytes : 1));
+    if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
+    std::memcpy(res, c->hOut.p, totalBytes);
+    for (const Overlay& o : overlays) {
+        const uint64_t shift = o.bitPos & 7;
+        size_t byte = static_cast<size_t>(o.bitPos >> 3);
+        if (shift == 0) {
+            for (size_t i = 0; i < o.bits.bytes.size(); ++i) res[byte + i] |= o.bits.bytes[i];
+        } else {
+            for (size_t i = 0; i < o.bits.bytes.size(); ++i) {
+                res[byte + i] |= static_cast<uint8_t>(o.bits.bytes[i] >> shift);
+                const uint8_t spill = static_cast<uint8_t>(o.bits.bytes[i] << (8 - shift));
+                if (spill) res[byte + i + 1] |= spill;
+            }
+        }
+    }
+    *out = res;
+    *outBytes = totalBytes;
+    c->nSymbols = M;
+    c->nBits = totalPayload;
+    float t;
+    cudaEventElapsedTime(&t, c->ev[2], c->ev[3]);
+    c->ms[2] = t;
+    cudaEventElapsedTime(&t, c->ev[3], c->ev[4]);
+    c->ms[3] = t;
+    cudaEventElapsedTime(&t, c->ev[5], c->ev[6]);
+    c->ms[5] = t;
+    c->ms[6] = static_cast<float>(nowMs() - tMerge0);
+    return MNENC_OK;
+}
+
+int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride) {
+    const uint32_t nbx = static_cast<uint32_t>((width + 7) / 8), nby = static_cast<uint32_t>((height + 7) / 8);
+    const uint64_t nbc64 = 3ull * nbx * nby;
+    if (nbc64 >= 0x7FFFFFFFull) return fail(MNENC_ERR_ARG, "image too large");
+    const uint32_t nbc = static_cast<uint32_t>(nbc64);
+    CU(c->counts.ensure(static_cast<size_t>(nbc) * 2 + 16));
+    CU(c->pairs.ensure(static_cast<size_t>(nbc) * c->K * 4 + 16));
+    CU(c->mpScratch.ensure(64));
+    CU(c->hStats.ensure(64));
+    CU(cudaMemsetAsync(c->mpScratch.p, 0, 64, c->stream));
+    MpParams p{};
+    p.rgb = rgbDev;
+    p.stride = stride;
+    p.width = static_cast<int>(width);
+    p.height = static_cast<int>(height);
+    p.nbx = static_cast<int>(nbx);
+    p.nby = static_cast<int>(nby);
+    p.K = c->K;
+    p.nBase = c->nBase;
+    p.baseT = c->baseT.as<float>();
+    p.detT = c->detT.as<float>();
+    p.detRows = c->detRows.as<uint8_t>();
+    p.quant = c->quant.as<float>();
+    p.counts = c->counts.as<uint16_t>();
+    p.pairs = c->pairs.as<uint32_t>();
+    p.workCounter = c->mpScratch.as<unsigned int>();
+    p.stats = reinterpret_cast<unsigned long long*>(c->mpScratch.as<unsigned char>() + 16);
+    p.nbc = nbc;
+    CU(cudaEventRecord(c->ev[0], c->stream));
+    CU(launchMatchingPursuit(p, c->numSMs, c->stream));
+    c->launches += nbc ? 1 : 0;
+    CU(cudaEventRecord(c->ev[1], c->stream));
+    CU(cudaMemcpyAsync(c->hStats.p, c->mpScratch.as<unsigned char>() + 16, 16, cudaMemcpyDeviceToHost, c->stream));
+    c->lastW = width;
+    c->lastH = height;
+    c->haveSymbols = true;
+    return MNENC_OK;
+}
+
+void finishMpAccounting(mnenc_ctx* c) {
+    float t = 0;
+    cudaEventElapsedTime(&t, c->ev[0], c->ev[1]);
+    c->ms[1] = t;
+    const unsigned long long* s = c->hStats.as<unsigned long long>();
+    // F = sum over iterations of 2*64*D_r  +  2*64*count   
+    c->mpFlops = 2.0 * kN * static_cast<double>(s[0]) + 2.0 * kN * static_cast<double>(s[1]);
+}
+
+int checkEncodeArgs(mnenc_ctx* c, const void* rgb, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes) {
+    if (!c || !rgb || !out || !outBytes) return fail(MNENC_ERR_ARG, "null argument");
+    if (w == 0 || h == 0 || stride < 3 * w) return fail(MNENC_ERR_ARG, "bad image geometry");
+    if (w > 0xFFFFFFFFull || h > 0xFFFFFFFFull) return fail(MNENC_ERR_ARG, "image too large");
+    if (!c->quantSet) return fail(MNENC_ERR_STATE, "mnenc_set_quant has not been called");
+    return MNENC_OK;
+}
+
+}  // namespace
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+extern "C" {
+
+const char* mnenc_last_error(void) { return g_error.c_str(); }
+
+void mnenc_free(uint8_t* p) { std::free(p); }
+
+int mnenc_quant_tables(int K, int block_size, double bpp_allocation, float* out_3K) {
+    if (!out_3K) return fail(MNENC_ERR_ARG, "null argument");
+    if (mnenc::quantTables(K, block_size, bpp_allocation, out_3K) != 0) return fail(MNENC_ERR_ARG, "unsupported K / block size");
+    return MNENC_OK;
+}
+
+int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* base, int n_base, const int32_t* detail_rows,
+                 const float* detailY, const float* detailU, const float* detailV) {
+    using namespace mnenc;
+    if (!out || !base || !detail_rows || !detailY || !detailU || !detailV) return fail(MNENC_ERR_ARG, "null argument");
+    if (block_size != 8) return fail(MNENC_ERR_ARG, "only block_size 8 is supported");
+    if (K < 1 || K > kMaxK) return fail(MNENC_ERR_ARG, "K must be in [1,32]");
+    if (n_base < 1 || n_base > kRowsPad) return fail(MNENC_ERR_ARG, "n_base must be in [1,512]");
+    for (int i = 0; i < n_base; ++i)
+        if (detail_rows[i] < 32 || detail_rows[i] > 64) return fail(MNENC_ERR_ARG, "detail groups must have 32..64 rows");
+    int ndev = 0;
+    CU(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(MNENC_ERR_CUDA, "no such CUDA device");
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(MNENC_ERR_CUDA, "mnenc is built for sm_100a (B200) only");
+    mnenc_ctx* c = new mnenc_ctx;
+    c->device = device;
+    c->K = K;
+    c->nBase = n_base;
+    c->numSMs = prop.multiProcessorCount;
+    auto bail = [&](int rc) {
+        mnenc_destroy(c);
+        return rc;
+    };
+#define CUB(expr)                                                                                              \
+    do {                                                                                                       \
+        cudaError_t e_ = (expr);                                                                               \
+        if (e_ != cudaSuccess) return bail(fail(MNENC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_))); \
+    } while (0)
+    CUB(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (auto& e : c->ev) CUB(cudaEventCreate(&e));
+    // base atoms transposed + zero padded: baseT[j*512 + atom]
+    std::vector<float> baseT(static_cast<size_t>(kN) * kRowsPad, 0.0f);
+    for (int a = 0; a < n_base; ++a)
+        for (int j = 0; j < kN; ++j) baseT[static_cast<size_t>(j) * kRowsPad + a] = base[static_cast<size_t>(a) * kN + j];
+    CUB(c->baseT.ensure(baseT.size() * 4));
+    CUB(cudaMemcpy(c->baseT.p, baseT.data(), baseT.size() * 4, cudaMemcpyHostToDevice));
+    // detail groups transposed per group: detT[((ch*nBase + atom)*64 + j)*64 + row], rows padded with zeros
+    std::vector<uint8_t> rows(kRowsPad, 0);
+    std::vector<float> detT(static_cast<size_t>(3) * n_base * kN * 64, 0.0f);
+    const float* det[3] = {detailY, detailU, detailV};
+    for (int ch = 0; ch < 3; ++ch) {
+        size_t rowOff = 0;
+        for (int a = 0; a < n_base; ++a) {
+            rows[a] = static_cast<uint8_t>(detail_rows[a]);
+            float* g = detT.data() + (static_cast<size_t>(ch) * n_base + a) * kN * 64;
+            for (int r = 0; r < detail_rows[a]; ++r)
+                for (int j = 0; j < kN; ++j) g[j * 64 + r] = det[ch][(rowOff + r) * kN + j];
+            rowOff += detail_rows[a];
+        }
+    }
+    CUB(c->detT.ensure(detT.size() * 4));
+    CUB(cudaMemcpy(c->detT.p, detT.data(), detT.size() * 4, cudaMemcpyHostToDevice));
+    CUB(c->detRows.ensure(kRowsPad));
+    CUB(cudaMemcpy(c->detRows.p, rows.data(), kRowsPad, cudaMemcpyHostToDevice));
+    CUB(c->quant.ensure(3 * kMaxK * 4));
+#undef CUB
+    *out = c;
+    return MNENC_OK;
+}
+
+void mnenc_destroy(mnenc_t* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (auto& e : c->ev)
+        if (e) cudaEventDestroy(e);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int mnenc_set_quant(mnenc_t* c, const float* q) {
+    if (!c || !q) return fail(MNENC_ERR_ARG, "null argument");
+    for (int i = 0; i < 3 * c->K; ++i)
+        if (!(q[i] >= 1.0f) || q[i] > 65535.0f) return fail(MNENC_ERR_ARG, "quantisers must be in [1,65535]");
+    std::memset(c->hQuant, 0, sizeof(c->hQuant));
+    for (int ch = 0; ch < 3; ++ch)
+        for (int i = 0; i < mnenc::kMaxK; ++i) c->hQuant[ch * mnenc::kMaxK + i] = i < c->K ? q[ch * c->K + i] : 1.0f;
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(c->quant.p, c->hQuant, sizeof(c->hQuant), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->quantSet = true;
+    return MNENC_OK;
+}
+
+static int encodeDevice(mnenc_t* c, const uint8_t* rgbDev, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes,
+                        double t0) {
+    if (int rc = runMatchingPursuit(c, rgbDev, w, h, stride)) return rc;
+    if (int rc = runBackend(c, w, h, out, outBytes)) return rc;
+    finishMpAccounting(c);
+    c->ms[7] = static_cast<float>(nowMs() - t0);
+    return MNENC_OK;
+}
+
+int mnenc_encode_rgb8_device(mnenc_t* c, const uint8_t* rgb_dev, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes) {
+    if (int rc = checkEncodeArgs(c, rgb_dev, w, h, stride, out, outBytes)) return rc;
+    CU(cudaSetDevice(c->device));
+    const double t0 = nowMs();
+    c->launches = 0;
+    c->ms[0] = 0;
+    return encodeDevice(c, rgb_dev, w, h, stride, out, outBytes, t0);
+}
+
+int mnenc_encode_rgb8(mnenc_t* c, const uint8_t* rgb, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes) {
+    if (int rc = checkEncodeArgs(c, rgb, w, h, stride, out, outBytes)) return rc;
+    CU(cudaSetDevice(c->device));
+    const double t0 = nowMs();
+    c->launches = 0;
+    CU(c->rgb.ensure(3 * w * h + 16));
+    // tightly packed on the device; pinned or pageable host memory both work (pinned is the fast path)
+    CU(cudaMemcpy2DAsync(c->rgb.p, 3 * w, rgb, stride, 3 * w, h, cudaMemcpyHostToDevice, c->stream));
+    c->ms[0] = 0;
+    int rc = encodeDevice(c, c->rgb.as<uint8_t>(), w, h, 3 * w, out, outBytes, t0);
+    return rc;
+}
+
+int mnenc_get_symbols(mnenc_t* c, uint16_t* counts, uint16_t* pairs) {
+    if (!c || !counts || !pairs) return fail(MNENC_ERR_ARG, "null argument");
+    if (!c->haveSymbols) return fail(MNENC_ERR_STATE, "no encode has run on this context");
+    CU(cudaSetDevice(c->device));
+    const size_t nbc = 3 * ((c->lastW + 7) / 8) * ((c->lastH + 7) / 8);
+    CU(cudaMemcpyAsync(counts, c->counts.p, nbc * 2, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(pairs, c->pairs.p, nbc * c->K * 4, cudaMemcpyDeviceToHost, c->stream));  // u32 = {deltaId, intCoeff} little-endian
+    CU(cudaStreamSynchronize(c->stream));
+    return MNENC_OK;
+}
+
+int mnenc_pack_symbols(mnenc_t* c, size_t w, size_t h, const uint16_t* counts, const uint16_t* pairs, uint8_t** out, size_t* outBytes) {
+    if (!c || !counts || !pairs || !out || !outBytes) return fail(MNENC_ERR_ARG, "null argument");
+    if (w == 0 || h == 0) return fail(MNENC_ERR_ARG, "bad image geometry");
+    if (!c->quantSet) return fail(MNENC_ERR_STATE, "mnenc_set_quant has not been called");
+    CU(cudaSetDevice(c->device));
+    const double t0 = nowMs();
+    c->launches = 0;
+    const size_t nbc = 3 * ((w + 7) / 8) * ((h + 7) / 8);
+    for (size_t i = 0; i < nbc; ++i)
+        if (counts[i] > c->K) return fail(MNENC_ERR_ARG, "count exceeds K");
+    CU(c->counts.ensure(nbc * 2 + 16));
+    CU(c->pairs.ensure(nbc * c->K * 4 + 16));
+    CU(cudaMemcpyAsync(c->counts.p, counts, nbc * 2, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->pairs.p, pairs, nbc * c->K * 4, cudaMemcpyHostToDevice, c->stream));
+    c->lastW = w;
+    c->lastH = h;
+    c->haveSymbols = true;
+    c->ms[0] = c->ms[1] = 0;
+    c->mpFlops = 0;
+    int rc = runBackend(c, w, h, out, outBytes);
+    c->ms[7] = static_cast<float>(nowMs() - t0);
+    return rc;
+}
+
+int mnenc_last_timing(mnenc_t* c, float* ms8) {
+    if (!c || !ms8) return fail(MNENC_ERR_ARG, "null argument");
+    std::memcpy(ms8, c->ms, sizeof(c->ms));
+    return c->launches;
+}
+
+int mnenc_last_work(mnenc_t* c, double* mp_flops, uint64_t* n_symbols, uint64_t* n_bits) {
+    if (!c) return fail(MNENC_ERR_ARG, "null argument");
+    if (mp_flops) *mp_flops = c->mpFlops;
+    if (n_symbols) *n_symbols = c->nSymbols;
+    if (n_bits) *n_bits = c->nBits;
+    return MNENC_OK;
+}
+
+int mnenc_debug_plan_sequence(const uint32_t* symbols, const uint32_t* freqs, const uint32_t* first_pos, size_t n, uint32_t* golomb_m,
+                              uint32_t* codes, uint8_t* lens, uint32_t* eof_code, uint8_t* eof_len, uint8_t* header_bytes,
+                              size_t header_cap, uint64_t* header_bits, uint64_t* payload_bits) {
+    if (!golomb_m || !eof_code || !eof_len || !header_bits || !payload_bits || (n && (!symbols || !freqs || !first_pos || !codes || !lens)))
+        return fail(MNENC_ERR_ARG, "null argument");
+    std::vector<mnenc::SymbolStat> stats(n);
+    for (size_t i = 0; i < n; ++i) stats[i] = mnenc::SymbolStat{symbols[i], freqs[i], first_pos[i]};
+    mnenc::SequencePlan plan;
+    mnenc::planSequence(stats, plan);
+    *golomb_m = plan.golomb ? plan.golombM : 0;
+    for (size_t i = 0; i < n; ++i) {
+        codes[i] = plan.code[i];
+        lens[i] = plan.len[i];
+    }
+    *eof_code = plan.eofCode;
+    *eof_len = plan.eofLen;
+    *header_bits = plan.header.nbits;
+    *payload_bits = plan.payloadBits;
+    if (plan.header.bytes.size() > header_cap) return fail(MNENC_ERR_ARG, "header buffer too small");
+    if (header_bytes) std::memcpy(header_bytes, plan.header.bytes.data(), plan.header.bytes.size());
+    return MNENC_OK;
+}
+
+}  // extern "C"

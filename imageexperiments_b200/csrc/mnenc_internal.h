@@ -1,0 +1,89 @@
+// Internal declarations shared by the CUDA kernels, the host entropy-table builder and the C-ABI layer.
+// Not installed; the public boundary is include/mnenc.h.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#ifdef __CUDACC__
+#include <cuda_runtime.h>
+#endif
+
+namespace mnenc {
+
+constexpr int kN = 64;        // pixels per 8x8 block (only block_size 8 is supported)
+constexpr int kMaxK = 32;     // greedy iterations per block-channel (Compression.cpp:28)
+constexpr int kRowsPad = 512; // base dictionary rows padded (510 real atoms)
+constexpr int kSlots = 32;    // block-channels in flight per CTA of the matching-pursuit kernel
+constexpr int kMpThreads = 512;
+constexpr int kMaxSeq = 6 * kMaxK + 1;  // coded sequences: `lengths` + 6K symbol streams
+
+// ------------------------------------------------------------------------------------------------
+// Matching pursuit kernel parameters (kernel: mp_kernel.cu)
+// ------------------------------------------------------------------------------------------------
+struct MpParams {
+    const uint8_t* rgb;      // device, packed RGB8
+    size_t stride;           // bytes per image row
+    int width, height;
+    int nbx, nby;            // blocks per row / column; block index = bx*nby + by (column-major walk)
+    int K;
+    int nBase;               // 510
+    const float* baseT;      // [64][512]  base atoms transposed: baseT[j*512 + atom], zero padded
+    const float* detT;       // [3][nBase][64][64]: detT[((ch*nBase+atom)*64 + j)*64 + row], zero padded rows
+    const uint8_t* detRows;  // [nBase] rows of each detail group (62 or 63)
+    const float* quant;      // [3][32]
+    uint16_t* counts;        // [nbc] out: atoms per block-channel == the `lengths` stream
+    uint32_t* pairs;         // [nbc][K] out: deltaId | intCoeff << 16 (0 beyond count)
+    unsigned int* workCounter;      // zeroed before launch
+    unsigned long long* stats;      // [2]: sum of dictionary heights over all iterations, sum of counts
+    unsigned int nbc;        // 3 * nbx * nby
+};
+
+#ifdef __CUDACC__
+cudaError_t launchMatchingPursuit(const MpParams& p, int numSMs, cudaStream_t stream);
+size_t matchingPursuitSmemBytes();
+#endif
+
+// ------------------------------------------------------------------------------------------------
+// Host side of the entropy back end (entropy_host.cpp). Everything here is computed from per-sequence
+// histograms + first-occurrence positions only.
+// ------------------------------------------------------------------------------------------------
+struct SymbolStat {
+    uint32_t symbol;
+    uint32_t freq;
+    uint32_t firstPos;
+};
+
+// MSB-first bit string builder for the (small) header parts written on the host.
+struct BitString {
+    std::vector<uint8_t> bytes;
+    uint64_t nbits = 0;
+    void put(uint64_t value, int width);
+};
+
+struct SequencePlan {
+    // decision
+    bool golomb = false;
+    uint32_t golombM = 0;
+    // Huffman table in the order of the `stats` vector passed in: code/len per entry
+    std::vector<uint32_t> code;
+    std::vector<uint8_t> len;
+    uint32_t eofCode = 0;
+    uint8_t eofLen = 0;
+    uint32_t maxCodeLen = 0; // longest Huffman code (the device packer handles <= 32 bits)
+    BitString header;        // everything before the first payload code: mode flag, table / m
+    uint64_t payloadBits = 0;  // sum of code lengths of the data symbols (without EOF)
+    uint64_t totalBits() const { return header.nbits + payloadBits + (golomb ? 0 : eofLen); }
+};
+
+// Builds the plan of one coded sequence (compressed::writeHuffmanOrGolomb, CompressedImage.cpp:359-390).
+// `stats` may be in any order; it is sorted by firstPos internally and code/len are returned in the
+// caller's original order.
+void planSequence(const std::vector<SymbolStat>& stats, SequencePlan& plan);
+
+// compressed::createQuantizationTables, float overload (CompressedImage.cpp:168-210).
+int quantTables(int K, int blockSize, double bpp, float* out3K);
+
+}  // namespace mnenc
