@@ -25,7 +25,7 @@ def main():
             bad = np.argwhere(~bc_ok)[:5]
             for b, c in bad:
                 print("  mismatch blk", b, "ch", c, "gpu", counts[b, c], pairs[b, c, :4].tolist(), "oracle", oc_counts[b, c], oc_pairs[b, c, :4].tolist())
-        ref = oc.write_file(32, 8, w, h, ctx.Quant, counts, pairs)
+        ref = oc.lib.write_file(32, 8, w, h, ctx.Quant, counts, pairs)
         print("   back end bit-exact given GPU symbols:", ref == data, len(ref), len(data))
         if ref != data:
             n = min(len(ref), len(data)); a = np.frombuffer(ref[:n], np.uint8); b = np.frombuffer(data[:n], np.uint8)
@@ -42,7 +42,7 @@ def main():
             fl, ns, nb = ctx.last_work()
             print(f"C2 iter {it}: {dt*1e3:.1f} ms -> {w*h/1e6/dt:.1f} MP/s; {len(data)} B; stage ms {np.round(ms,3).tolist()} launches {launches} flops {fl/1e9:.1f} G symbols {ns}")
         counts, pairs = mn.lastSymbols(ctx, w, h)
-        ref = oc.write_file(32, 8, w, h, ctx.Quant, counts, pairs)
+        ref = oc.lib.write_file(32, 8, w, h, ctx.Quant, counts, pairs)
         print("C2 back end bit-exact given GPU symbols:", ref == data)
         # oracle symbols on a sample of block columns
         nbx = w // 8
