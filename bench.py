@@ -1,0 +1,288 @@
+#!/usr/bin/env python
+"""Benchmark of the `.mn` encoder hot path (BASELINE.json: encode megapixels/sec at quality 3.5).
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (torchrun launches N ranks for N > 1)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU encoder on the host cores
+
+A step = one complete encode (encodeImageFast) of one 4928x3264 synthetic RGB image at quality 3.5
+(BASELINE.json configs[1]) per GPU. `value` is measured with the pixels already resident in HBM, `e2e` through the
+same public call with pinned HOST pixels (H2D and D2H inside the timed region). N > 1: every rank encodes its own
+images (image-parallel replicas, no data-path collective) => weak scaling.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H, QUALITY, K_ATOMS = 4928, 3264, 3.5, 32
+METRIC = "encode megapixels/sec at quality 3.5"
+RING = 4  # distinct input images per rank: 4 x 48.3 MB = 193 MB > 126 MB L2
+
+
+def make_ring(rank: int):
+    from imageexperiments_b200.synth import synthetic_rgb
+    base = synthetic_rgb(W, H, seed=12345 + rank)
+    ring = [base]
+    for i in range(1, RING):  # same statistics, different bytes (shifted by whole blocks so block content is preserved)
+        ring.append(np.ascontiguousarray(np.roll(base, (8 * 37 * i, 8 * 53 * i), axis=(0, 1))))
+    return ring
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed regions (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                                          str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, windows):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, line in self.rows:
+            if not any(a <= t <= b for a, b in windows):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0]))
+                smax = float(f[1])
+            except Exception:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline_sample():
+    """The reference's own encodeImageFast (oracle/_ref, unmodified sources) on one core, bounded sample."""
+    from imageexperiments_b200.synth import synthetic_rgb
+    from oracle.bindings import RefLib, ref_available
+    if not ref_available():
+        return {"value": None, "unit": "MP/s", "cores": 1, "kind": "reference", "sample": "oracle/_ref missing"}
+    R = RefLib()
+    ctx = R.create(K_ATOMS, 8, QUALITY)
+    sw, sh = 1536, 1024
+    img = np.ascontiguousarray(synthetic_rgb(W, H, seed=12345)[:sh, :sw])
+    t = time.perf_counter()
+    data = R.encode(ctx, img)
+    dt = time.perf_counter() - t
+    R.destroy(ctx)
+    return {"value": round(sw * sh / 1e6 / dt, 4), "unit": "MP/s", "cores": 1, "kind": "reference",
+            "sample": f"top-left {sw}x{sh} crop of the workload image, encodeImageFast of the unmodified reference (g++ -O2), "
+                      f"1 thread, {dt:.1f} s, {len(data)} B", "host_cores": os.cpu_count()}
+
+
+_REF = {}
+
+
+def _ref_tile(i):
+    R, ctx, tiles = _REF["R"], _REF["ctx"], _REF["tiles"]
+    return len(R.encode(ctx, tiles[i]))
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU encoder on all host cores. The reference is single-threaded and its
+    per-iteration dictionary copies serialise threads of one process on the allocator, so the cores are used as
+    forked worker processes. Each step = every worker encodes one 512x512 tile of the workload image (bounded sample)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    from imageexperiments_b200.synth import synthetic_rgb
+    from oracle.bindings import RefLib, ref_available
+    if not ref_available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libmnref.so missing (build() needs /root/reference)"}))
+        return
+    R = RefLib()
+    ctx = R.create(K_ATOMS, 8, QUALITY)
+    try:
+        workers = len(os.sched_getaffinity(0))
+    except Exception:
+        workers = os.cpu_count() or 1
+    tile = 512
+    img = synthetic_rgb(W, H, seed=12345)
+    per_row = W // tile
+    tiles = []
+    for i in range(workers):
+        x0 = (i % per_row) * tile
+        y0 = ((i // per_row) % (H // tile)) * tile
+        tiles.append(np.ascontiguousarray(img[y0:y0 + tile, x0:x0 + tile]))
+    _REF.update(R=R, ctx=ctx, tiles=tiles)
+    pool = mp.get_context("fork").Pool(workers)
+
+    def step():
+        pool.map(_ref_tile, range(workers), chunksize=1)
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    pool.close()
+    mp_done = workers * tile * tile / 1e6 * args.steps
+    value = mp_done / dt
+    sample = (f"each step: {workers} worker processes x one {tile}x{tile} tile of the workload image through the unmodified "
+              "reference encodeImageFast (g++ -O2 -ffp-contract=off)")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": "MP/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{W}x{H} RGB synthetic, quality {QUALITY}, K={K_ATOMS}, block 8 (BASELINE.json configs[1])", "sample": sample},
+        "cpu_baseline": {"value": round(value, 4), "unit": "MP/s", "cores": workers, "kind": "reference", "sample": sample},
+        "e2e": {"value": round(value, 4), "unit": "MP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import imageexperiments_b200 as mn
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: there is no CPU fallback for the encoder")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    ctx = mn.createCompressionContextFast(K_ATOMS, 8, QUALITY, device=local)
+    ring = make_ring(rank)
+    dev = [torch.from_numpy(a).cuda() for a in ring]
+    pinned = []
+    for a in ring:
+        p = torch.empty(a.shape, dtype=torch.uint8, pin_memory=True)
+        p.numpy()[...] = a
+        pinned.append(p)
+    sampler = ClockSampler(local) if rank == 0 else None
+    windows = []
+
+    def timed(inputs):
+        out_bytes = mp_ms = flops = launches = 0
+        for i in range(args.warmup):
+            mn.encodeImageFast(inputs[i % RING], ctx)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.time()
+        e0.record()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            data = mn.encodeImageFast(inputs[i % RING], ctx)
+            out_bytes += len(data)
+            ms, n = ctx.last_timing()
+            mp_ms += float(ms[1])
+            launches += n
+            flops += ctx.last_work()[0]
+        e1.record()
+        torch.cuda.synchronize()
+        dt = max(time.perf_counter() - t0, e0.elapsed_time(e1) / 1e3)  # the call is host-synchronous: both clocks agree
+        barrier()
+        windows.append((w0, time.time()))
+        return max_over_ranks(dt), out_bytes / args.steps, mp_ms / args.steps, flops / args.steps, launches
+
+    dt_dev, out_b, mp_ms, flops, launches = timed(dev)
+    dt_e2e, out_b2, _, _, _ = timed(pinned)
+    mp_total = world * args.steps * W * H / 1e6
+    value = mp_total / dt_dev
+    e2e = mp_total / dt_e2e
+
+    if rank == 0:
+        clocks = sampler.stop(windows)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+        # Dominant kernel = matchingPursuitKernel. Its arithmetic must reproduce the oracle's UNFUSED f32 mul+add, so one
+        # flop occupies one FP32 issue slot: peak = SMs x 128 lanes x max SM clock (half the FFMA figure).
+        fp32_peak = 148 * 128 * sm_max * 1e6 / 1e12
+        achieved = flops / (mp_ms / 1e3) / 1e12 if mp_ms > 0 else 0.0
+        control_d2h = 65536 * 16 + 4096
+        line = {
+            "metric": METRIC, "value": round(value, 2), "unit": "MP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(dt_dev / args.steps * 1e3, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{W}x{H} RGB synthetic, quality {QUALITY}, K={K_ATOMS}, block 8 (BASELINE.json configs[1]), one image per GPU per step",
+                       "parallelism": f"image-parallel replicas x{world}, no data-path collective",
+                       "l2": f"ring of {RING} distinct {W * H * 3 / 1e6:.1f} MB inputs per GPU ({RING * W * H * 3 / 1e6:.0f} MB > 126 MB L2)",
+                       "timed": "value: pixels resident in HBM, stream returned to host; e2e: pinned host pixels, H2D+D2H inside"},
+            "clocks": clocks,
+            "e2e": {"value": round(e2e, 2), "unit": "MP/s", "h2d_bytes_per_step": W * H * 3, "d2h_bytes_per_step": int(out_b2) + control_d2h,
+                    "ms_per_step": round(dt_e2e / args.steps * 1e3, 3)},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "matchingPursuitKernel", "bound": "fp32", "achieved": round(achieved, 3), "peak": round(fp32_peak, 2),
+                         "unit": "TFLOP/s", "frac": round(achieved / fp32_peak, 4), "traffic": None,
+                         "note": "algorithmic flops (SURVEY.md 8d, counted by the kernel) / CUDA-event time of the kernel on its own stream; "
+                                 f"peak = 148 SMs x 128 FP32 lanes x {sm_max:.0f} MHz (MEASURED_PEAKS.json sm_max_mhz) issue slots: "
+                                 "oracle-exact arithmetic is unfused mul+add, 1 flop per slot",
+                         "ms_per_launch": round(mp_ms, 3), "gflop_per_launch": round(flops / 1e9, 2)},
+            "bytes_out_per_step": int(out_b),
+        }
+        if world == 1:
+            line["cpu_baseline"] = cpu_baseline_sample()
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

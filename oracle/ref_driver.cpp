@@ -23,6 +23,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <mutex>
 #include <sstream>
 #include <stdexcept>
 #include <string>
@@ -42,12 +43,18 @@ namespace {
 
 thread_local std::string g_err;
 
-// The reference prints a progress line per block column (CompressedImage.cpp:593,852).
+// The reference prints a progress line per block column (CompressedImage.cpp:593,852). std::cout is switched once,
+// process-wide, to a stateless discarding buffer (safe when several threads encode at the same time).
+struct NullBuf : std::streambuf {
+    int overflow(int c) override { return traits_type::not_eof(c); }
+    std::streamsize xsputn(const char*, std::streamsize n) override { return n; }
+};
 struct CoutMute {
-    std::streambuf* old;
-    std::ostringstream sink;
-    CoutMute() : old(std::cout.rdbuf(sink.rdbuf())) {}
-    ~CoutMute() { std::cout.rdbuf(old); }
+    CoutMute() {
+        static NullBuf sink;
+        static std::once_flag once;
+        std::call_once(once, [] { std::cout.rdbuf(&sink); });
+    }
 };
 
 template <class F>

@@ -1,0 +1,66 @@
+"""CPU-only: the C-ABI library loads and exports every symbol include/mnenc.h declares; host-only entry points work;
+GPU entry points fail loudly (no CPU fallback) when no device is present."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from imageexperiments_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "mnenc.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(mnenc_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported():
+    L = _lib.load()
+    names = declared_symbols()
+    assert len(names) >= 12
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/mnenc.h but not exported"
+    assert sorted(_lib.EXPORTS) == names
+
+
+def test_no_torch_or_oracle_in_abi_library():
+    out = os.popen(f"ldd {_lib.LIB_PATH}").read()
+    assert "torch" not in out and "mnoracle" not in out and "mnref" not in out
+
+
+def test_quant_tables_bad_args():
+    L = _lib.load()
+    q = np.zeros(96, np.float32)
+    assert L.mnenc_quant_tables(64, 8, 3.5, q.ctypes.data_as(C.c_void_p)) < 0
+    assert b"K" in L.mnenc_last_error() or L.mnenc_last_error()
+
+
+def test_create_rejects_bad_arguments():
+    L = _lib.load()
+    h = C.c_void_p()
+    base = np.zeros((510, 64), np.float32)
+    rows = np.full(510, 62, np.int32)
+    det = np.zeros((62 * 510, 64), np.float32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    assert L.mnenc_create(C.byref(h), 0, 32, 16, p(base), 510, p(rows), p(det), p(det), p(det)) == -1  # block size
+    assert L.mnenc_create(C.byref(h), 0, 33, 8, p(base), 510, p(rows), p(det), p(det), p(det)) == -1   # K
+    assert L.mnenc_create(C.byref(h), 0, 32, 8, None, 510, p(rows), p(det), p(det), p(det)) == -1        # null
+
+
+def test_gpu_entry_points_fail_loudly_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    L = _lib.load()
+    h = C.c_void_p()
+    base = np.zeros((510, 64), np.float32)
+    rows = np.full(510, 62, np.int32)
+    det = np.zeros((62 * 510, 64), np.float32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    rc = L.mnenc_create(C.byref(h), 0, 32, 8, p(base), 510, p(rows), p(det), p(det), p(det))
+    assert rc == -2, "must report MNENC_ERR_CUDA, never fall back to a CPU path"
+    assert L.mnenc_last_error()

@@ -1,0 +1,72 @@
+"""Host table builder of the product (csrc/entropy_host.cpp via mnenc_debug_plan_sequence): from (symbol, frequency,
+first occurrence) only, it must reproduce compressed::writeHuffmanOrGolomb bit for bit (golden vectors + reference)."""
+import numpy as np
+
+import imageexperiments_b200 as mn
+from conftest import bits_of
+
+
+def code_with_plan(data: np.ndarray) -> np.ndarray:
+    """Header bits from the host planner + payload emitted here from its code table / Golomb parameter."""
+    data = np.asarray(data, np.uint16)
+    syms, first, freq = np.unique(data, return_index=True, return_counts=True)
+    p = mn.planSequenceHost(syms, freq, first)
+    out = [bits_of(p["header"], p["header_bits"])]
+    payload = []
+    if p["golomb_m"] == 0:
+        lut = {int(s): (int(c), int(l)) for s, c, l in zip(syms, p["codes"], p["lens"])}
+        for s in data:
+            c, l = lut[int(s)]
+            payload.append(format(c, "b").zfill(l) if l else "")
+        payload.append(format(p["eof_code"], "b").zfill(p["eof_len"]))
+    else:
+        M = p["golomb_m"]
+        b = M.bit_length()
+        lim = (1 << (b + 1)) - M
+        for s in data:
+            q, r = divmod(int(s), M)
+            payload.append("1" * q + "0" + (format(r, "b").zfill(b) if r < lim else format(r + lim, "b").zfill(b + 1)))
+    s = "".join(payload)
+    assert p["golomb_m"] != 0 or len(s) == p["payload_bits"] + p["eof_len"]
+    assert p["golomb_m"] == 0 or len(s) == p["payload_bits"]
+    out.append(np.frombuffer(s.encode(), np.uint8) - ord("0"))
+    return np.concatenate(out).astype(np.uint8)
+
+
+def test_golden(golden):
+    for i in range(int(golden["ent_count"])):
+        data = golden[f"ent_{i}_in"]
+        if data.size > 6000:
+            data = data  # long cases still run: python emission is linear
+        got = code_with_plan(data)
+        nbits = int(golden[f"ent_{i}_nbits"])
+        assert got.size == nbits, i
+        assert (got == bits_of(golden[f"ent_{i}_bits"].tobytes(), nbits)).all(), i
+
+
+def test_vs_reference_random(reflib):
+    rng = np.random.default_rng(8)
+    for t in range(80):
+        n = int(rng.integers(0, 2500))
+        kind = t % 5
+        d = [rng.integers(0, 4, n), rng.geometric(0.05, n) - 1, rng.integers(0, 2000, n), np.minimum(rng.pareto(1.0, n) * 50, 60000),
+             rng.integers(0, 65536, n)][kind]
+        d = np.asarray(d).astype(np.uint16)
+        blob, nbits = reflib.huffman_or_golomb(d)
+        got = code_with_plan(d)
+        assert got.size == nbits and (got == bits_of(blob, nbits)).all(), (t, n)
+
+
+def test_first_occurrence_order_matters(reflib):
+    """the same histogram with another first-occurrence order may give another table; the planner must
+    follow the order it is given."""
+    rng = np.random.default_rng(9)
+    base = np.repeat(np.arange(40, dtype=np.uint16) * 7, rng.integers(1, 4, 40))
+    seen = set()
+    for _ in range(30):
+        d = rng.permutation(base)
+        blob, nbits = reflib.huffman_or_golomb(d)
+        got = code_with_plan(d)
+        assert got.size == nbits and (got == bits_of(blob, nbits)).all()
+        seen.add(blob[:12])
+    assert len(seen) > 1
