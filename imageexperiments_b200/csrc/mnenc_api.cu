@@ -5,7 +5,9 @@
 // symbol-sized). Buffers are grow-only and live in the context, so steady-state encodes allocate nothing.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <chrono>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -87,7 +89,9 @@ struct mnenc_ctx {
     bool quantSet = false;
     float hQuant[3 * mnenc::kMaxK] = {};
     // dictionary
-    DevBuf baseT, detT, detRows, quant;
+    DevBuf baseT, baseUm, detT, detRows, quant;
+    float epsRel = 0.0f;
+    bool useTensorCores = true;  // MNENC_MP=fp32 selects the exact full-scan kernel (A/B validation only)
     // image + symbols
     DevBuf rgb, counts, pairs, mpScratch;
     size_t lastW = 0, lastH = 0;
@@ -379,6 +383,8 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     p.K = c->K;
     p.nBase = c->nBase;
     p.baseT = c->baseT.as<float>();
+    p.baseUm = c->baseUm.as<float>();
+    p.epsRel = c->epsRel;
     p.detT = c->detT.as<float>();
     p.detRows = c->detRows.as<uint8_t>();
     p.quant = c->quant.as<float>();
@@ -388,7 +394,8 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     p.stats = reinterpret_cast<unsigned long long*>(c->mpScratch.as<unsigned char>() + 16);
     p.nbc = nbc;
     CU(cudaEventRecord(c->ev[0], c->stream));
-    CU(launchMatchingPursuit(p, c->numSMs, c->stream));
+    if (c->useTensorCores) CU(launchMatchingPursuitTc(p, c->numSMs, c->stream));
+    else CU(launchMatchingPursuit(p, c->numSMs, c->stream));
     c->launches += nbc ? 1 : 0;
     CU(cudaEventRecord(c->ev[1], c->stream));
     CU(cudaMemcpyAsync(c->hStats.p, c->mpScratch.as<unsigned char>() + 16, 16, cudaMemcpyDeviceToHost, c->stream));
@@ -470,6 +477,21 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
         for (int j = 0; j < kN; ++j) baseT[static_cast<size_t>(j) * kRowsPad + a] = base[static_cast<size_t>(a) * kN + j];
     CUB(c->baseT.ensure(baseT.size() * 4));
     CUB(cudaMemcpy(c->baseT.p, baseT.data(), baseT.size() * 4, cudaMemcpyHostToDevice));
+    // the same atoms as the canonical K-major UMMA operand image for the tensor-core pre-filter
+    std::vector<float> baseUm(static_cast<size_t>(kN) * kRowsPad);
+    buildUmmaImage(base, n_base, baseUm.data());
+    CUB(c->baseUm.ensure(baseUm.size() * 4));
+    CUB(cudaMemcpy(c->baseUm.p, baseUm.data(), baseUm.size() * 4, cudaMemcpyHostToDevice));
+    {   // pre-filter error bound: |tf32 score - oracle fp32 score| <= (2*2^-10 + 2^-20 + 6e-6) * ||d|| * ||r||, 15 % margin
+        double maxNorm = 0.0;
+        for (int a = 0; a < n_base; ++a) {
+            double ss = 0.0;
+            for (int j = 0; j < kN; ++j) ss += static_cast<double>(base[static_cast<size_t>(a) * kN + j]) * base[static_cast<size_t>(a) * kN + j];
+            maxNorm = std::max(maxNorm, std::sqrt(ss));
+        }
+        c->epsRel = static_cast<float>((2.0 / 1024.0 + 1.0 / 1048576.0 + 6e-6) * maxNorm * 1.15);
+    }
+    if (const char* mode = std::getenv("MNENC_MP")) c->useTensorCores = std::string(mode) != "fp32";
     // detail groups transposed per group: detT[((ch*nBase + atom)*64 + j)*64 + row], rows padded with zeros
     std::vector<uint8_t> rows(kRowsPad, 0);
     std::vector<float> detT(static_cast<size_t>(3) * n_base * kN * 64, 0.0f);

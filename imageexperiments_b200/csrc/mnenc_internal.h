@@ -30,7 +30,9 @@ struct MpParams {
     int nbx, nby;            // blocks per row / column; block index = bx*nby + by (column-major walk)
     int K;
     int nBase;               // 510
-    const float* baseT;      // [64][512]  base atoms transposed: baseT[j*512 + atom], zero padded
+    const float* baseT;      // [64][512]  base atoms transposed: baseT[j*512 + atom], zero padded (FP32 kernel)
+    const float* baseUm;     // [512][64] base atoms in the canonical UMMA K-major image (tensor-core kernel)
+    float epsRel;            // pre-filter error bound relative to ||r||_2 (tensor-core kernel)
     const float* detT;       // [3][nBase][64][64]: detT[((ch*nBase+atom)*64 + j)*64 + row], zero padded rows
     const uint8_t* detRows;  // [nBase] rows of each detail group (62 or 63)
     const float* quant;      // [3][32]
@@ -41,9 +43,11 @@ struct MpParams {
     unsigned int nbc;        // 3 * nbx * nby
 };
 
+void buildUmmaImage(const float* baseRowMajor, int nBase, float* image);  // host
 #ifdef __CUDACC__
 cudaError_t launchMatchingPursuit(const MpParams& p, int numSMs, cudaStream_t stream);
 size_t matchingPursuitSmemBytes();
+cudaError_t launchMatchingPursuitTc(const MpParams& p, int numSMs, cudaStream_t stream);
 #endif
 
 // ------------------------------------------------------------------------------------------------
