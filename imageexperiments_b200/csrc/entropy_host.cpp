@@ -25,10 +25,25 @@
 namespace mnenc {
 
 void BitString::put(uint64_t value, int width) {
-    for (int i = width - 1; i >= 0; --i) {
-        if ((nbits & 7) == 0) bytes.push_back(0);
-        if ((value >> i) & 1ULL) bytes.back() |= static_cast<uint8_t>(0x80u >> (nbits & 7));
-        ++nbits;
+    // MSB-first, byte at a time: the first chunk fills the open byte, the rest start fresh ones
+    if (width < 64) value &= (1ULL << width) - 1ULL;
+    while (width > 0) {
+        const int used = static_cast<int>(nbits & 7);
+        if (used == 0) bytes.push_back(0);
+        const int take = std::min(8 - used, width);
+        const uint8_t chunk = static_cast<uint8_t>((value >> (width - take)) & ((1u << take) - 1u));
+        bytes.back() |= static_cast<uint8_t>(chunk << (8 - used - take));
+        nbits += take;
+        width -= take;
+    }
+}
+
+void BitString::append(const BitString& other) {
+    uint64_t left = other.nbits;
+    for (size_t i = 0; left > 0; ++i) {
+        const int take = static_cast<int>(std::min<uint64_t>(8, left));
+        put(other.bytes[i] >> (8 - take), take);
+        left -= take;
     }
 }
 
@@ -146,8 +161,9 @@ void planSequence(const std::vector<SymbolStat>& stats, SequencePlan& plan) {
             for (uint32_t k = 0; k < rangeLen; ++k) {  // BitBuffer.cpp:301-313
                 const uint32_t want = (sorted[pos + k].symbol & mask & 0xFFFFu) >> lb;
                 while (bucket != want) {
-                    huff.put(0, 1);
-                    ++bucket;
+                    const uint32_t z = std::min<uint32_t>(want - bucket, 32);
+                    huff.put(0, static_cast<int>(z));
+                    bucket += z;
                 }
                 huff.put(1, 1);
             }
@@ -195,7 +211,7 @@ void planSequence(const std::vector<SymbolStat>& stats, SequencePlan& plan) {
         plan.golomb = false;
         plan.golombM = 0;
         plan.header.put(0, 1);
-        for (uint64_t i = 0; i < huff.nbits; ++i) plan.header.put((huff.bytes[i >> 3] >> (7 - (i & 7))) & 1u, 1);
+        plan.header.append(huff);
         plan.payloadBits = huffPayload;
     } else {
         plan.golomb = true;

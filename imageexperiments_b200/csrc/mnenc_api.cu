@@ -288,7 +288,7 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
                 h.bits.put(0, 1);
             }
         }
-        for (uint64_t i = 0; i < p.header.nbits; ++i) h.bits.put((p.header.bytes[i >> 3] >> (7 - (i & 7))) & 1u, 1);
+        h.bits.append(p.header);
         cursor += h.bits.nbits;
         overlays.push_back(std::move(h));
         hTable.seq[q].bitBase = cursor - scanPrefix;  // modular arithmetic: position = bitBase + scan value

@@ -64,7 +64,8 @@ struct SymbolStat {
 struct BitString {
     std::vector<uint8_t> bytes;
     uint64_t nbits = 0;
-    void put(uint64_t value, int width);
+    void put(uint64_t value, int width);   // width <= 64
+    void append(const BitString& other);
 };
 
 struct SequencePlan {
