@@ -15,6 +15,7 @@
 #include <algorithm>
 #include <bit>
 #include <cmath>
+#include <memory_resource>
 #include <numeric>
 #include <queue>
 #include <unordered_map>
@@ -51,13 +52,6 @@ namespace {
 
 constexpr uint32_t kEof = 0xFFFFFFFFu;  // Huffman.cpp:38
 
-inline uint32_t golombLen(uint32_t v, uint32_t M) {
-    const uint32_t q = v / M, rem = v % M;
-    const uint32_t b = std::bit_width(M);
-    const uint32_t limit = (1u << (b + 1)) - M;
-    return rem < limit ? b + q + 1 : b + q + 2;
-}
-
 struct HeapNode {
     uint64_t freq;
     uint32_t id;
@@ -83,7 +77,10 @@ void planSequence(const std::vector<SymbolStat>& stats, SequencePlan& plan) {
     std::sort(order.begin(), order.end(), [&](int a, int b) { return stats[a].firstPos < stats[b].firstPos; });
 
     // --- frequency map in the reference's insertion order (Huffman.cpp:47-71) ---
-    std::unordered_map<uint32_t, uint32_t> slot;  // symbol -> leaf id
+    // Same libstdc++ hashtable as the reference's std::unordered_map (only the node allocator differs: one arena per
+    // call instead of one malloc per symbol; the allocator has no influence on bucket or iteration order).
+    std::pmr::monotonic_buffer_resource arena((n + 2) * 48 + 1024);
+    std::pmr::unordered_map<uint32_t, uint32_t> slot(&arena);  // symbol -> leaf id
     uint32_t symWidth = 1;
     uint64_t dataCount = 0;
     std::vector<uint64_t> leafFreq;
@@ -197,8 +194,18 @@ void planSequence(const std::vector<SymbolStat>& stats, SequencePlan& plan) {
     int bestM = -1;
     uint64_t bestPayload = 0;
     for (int m = 1; m < 2048;) {
+        // golombCodeLength (BitBuffer.cpp:260-269) summed over the histogram. v / M by reciprocal multiplication:
+        // exact for v < 2^16, M < 2^11 (27 significant bits needed, 32 available).
+        const uint32_t M = static_cast<uint32_t>(m);
+        const uint32_t b = std::bit_width(M);
+        const uint32_t limit = (1u << (b + 1)) - M;
+        const uint64_t inv = (1ull << 32) / M + 1;
         uint64_t est = 16;
-        for (const SymbolStat& s : stats) est += static_cast<uint64_t>(s.freq) * golombLen(s.symbol, static_cast<uint32_t>(m));
+        for (const SymbolStat& s : stats) {
+            const uint32_t q = s.symbol < 65536u ? static_cast<uint32_t>((s.symbol * inv) >> 32) : s.symbol / M;
+            const uint32_t rem = s.symbol - q * M;
+            est += static_cast<uint64_t>(s.freq) * (b + q + 1 + (rem >= limit ? 1u : 0u));
+        }
         if (est < best) {
             best = est;
             bestM = m;

@@ -4,17 +4,22 @@
 // The host work between the two GPU phases is the table build of entropy_host.cpp (alphabet-sized, never
 // symbol-sized). Buffers are grow-only and live in the context, so steady-state encodes allocate nothing.
 #include <cuda_runtime.h>
+#include <sched.h>
 
 #include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
+#include <numeric>
+#include <thread>
 #include <string>
 #include <vector>
 
 #include "../../include/mnenc.h"
 #include "backend_kernels.cuh"
+#include "host_pool.h"
 #include "mnenc_internal.h"
 
 namespace {
@@ -89,9 +94,10 @@ struct mnenc_ctx {
     bool quantSet = false;
     float hQuant[3 * mnenc::kMaxK] = {};
     // dictionary
-    DevBuf baseT, baseUm, detT, detRows, quant;
-    float epsRel = 0.0f;
-    bool useTensorCores = true;  // MNENC_MP=fp32 selects the exact full-scan kernel (A/B validation only)
+    DevBuf baseT, baseUm, detT, detRows, quant, baseUm16, detUm16, rows32;
+    float epsRel = 0.0f, epsRel16 = 0.0f, epsAbs16 = 0.0f;
+    int mpMode = 2;  // 2 = fp16 tensor-core pre-filter for base + detail (default); MNENC_MP=tf32 / fp32 select the
+                     // earlier kernels (base-only TF32 pre-filter / exact full scan) for A/B validation
     // image + symbols
     DevBuf rgb, counts, pairs, mpScratch;
     size_t lastW = 0, lastH = 0;
@@ -102,6 +108,7 @@ struct mnenc_ctx {
     uint32_t entryCap = 0;
     bool histReady = false;
     PinBuf hTotals, hSeqTable, hEntries, hNEntries, hEntryCodes, hCodeTable, hOut, hStats, hRgb;
+    std::unique_ptr<mnenc::HostPool> pool;  // code-table builds of one image run on these threads
     // accounting
     float ms[8] = {};
     int launches = 0;
@@ -248,7 +255,12 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
         entryOf[ent[e].seq].push_back(e);
     }
     std::vector<SequencePlan> plans(nSeq);
-    for (int q = 0; q < nSeq; ++q) planSequence(stats[q], plans[q]);
+    {   // largest alphabets first so the dynamic distribution over the pool ends evenly
+        std::vector<int> byLoad(nSeq);
+        std::iota(byLoad.begin(), byLoad.end(), 0);
+        std::sort(byLoad.begin(), byLoad.end(), [&](int a, int b) { return stats[a].size() > stats[b].size(); });
+        c->pool->parallelFor(nSeq, [&](int i) { planSequence(stats[byLoad[i]], plans[byLoad[i]]); });
+    }
 
     CU(c->hEntryCodes.ensure(static_cast<size_t>(nEntries) * 8 + 8));
     CU(c->hCodeTable.ensure(sizeof(CodeTable)));
@@ -394,7 +406,13 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     p.stats = reinterpret_cast<unsigned long long*>(c->mpScratch.as<unsigned char>() + 16);
     p.nbc = nbc;
     CU(cudaEventRecord(c->ev[0], c->stream));
-    if (c->useTensorCores) CU(launchMatchingPursuitTc(p, c->numSMs, c->stream));
+    p.baseUm16 = c->baseUm16.as<uint16_t>();
+    p.detUm16 = c->detUm16.as<uint16_t>();
+    p.rows32 = c->rows32.as<float>();
+    p.epsRel16 = c->epsRel16;
+    p.epsAbs16 = c->epsAbs16;
+    if (c->mpMode == 2) CU(launchMatchingPursuitF16(p, c->numSMs, c->stream));
+    else if (c->mpMode == 1) CU(launchMatchingPursuitTc(p, c->numSMs, c->stream));
     else CU(launchMatchingPursuit(p, c->numSMs, c->stream));
     c->launches += nbc ? 1 : 0;
     CU(cudaEventRecord(c->ev[1], c->stream));
@@ -491,7 +509,32 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
         }
         c->epsRel = static_cast<float>((2.0 / 1024.0 + 1.0 / 1048576.0 + 6e-6) * maxNorm * 1.15);
     }
-    if (const char* mode = std::getenv("MNENC_MP")) c->useTensorCores = std::string(mode) != "fp32";
+    if (const char* mode = std::getenv("MNENC_MP")) c->mpMode = std::string(mode) == "fp32" ? 0 : (std::string(mode) == "tf32" ? 1 : 2);
+    {   // fp16 operand images + exact row table of the fp16 tensor-core kernel, and its rigorous pre-filter bound:
+        //   |p~ - p_oracle| <= ||d - fp16(d)|| ||r||  (dictionary rounding, Cauchy-Schwarz)
+        //                    + ||d|| ||r|| (2^-22 residual hi/lo split + 4e-5 tensor-core accumulation + 64 * 2^-24 oracle rounding)
+        //                    + 5e-7 (fp16 subnormal residual parts), 15 % margin on the relative part
+        std::vector<uint16_t> b16(static_cast<size_t>(kRowsPad) * kN), d16(static_cast<size_t>(3) * n_base * 64 * kN);
+        std::vector<float> rows(f16Rows32Count(n_base) * kN);
+        const float* det3[3] = {detailY, detailU, detailV};
+        double roundNorm = 0.0, maxNorm = 0.0;
+        buildF16Images(base, n_base, detail_rows, det3, b16.data(), d16.data(), rows.data(), &roundNorm, &maxNorm);
+        c->epsRel16 = static_cast<float>((roundNorm + maxNorm * (1.0 / 4194304.0 + 4e-5 + 64.0 / 16777216.0)) * 1.15);
+        c->epsAbs16 = 5e-7f;
+        CUB(c->baseUm16.ensure(b16.size() * 2));
+        CUB(cudaMemcpy(c->baseUm16.p, b16.data(), b16.size() * 2, cudaMemcpyHostToDevice));
+        CUB(c->detUm16.ensure(d16.size() * 2));
+        CUB(cudaMemcpy(c->detUm16.p, d16.data(), d16.size() * 2, cudaMemcpyHostToDevice));
+        CUB(c->rows32.ensure(rows.size() * 4));
+        CUB(cudaMemcpy(c->rows32.p, rows.data(), rows.size() * 4, cudaMemcpyHostToDevice));
+    }
+    {
+        int threads = static_cast<int>(std::thread::hardware_concurrency());
+        cpu_set_t set;
+        if (sched_getaffinity(0, sizeof(set), &set) == 0) threads = CPU_COUNT(&set);
+        if (const char* t = std::getenv("MNENC_HOST_THREADS")) threads = std::atoi(t);
+        c->pool = std::make_unique<HostPool>(std::clamp(threads, 1, 16));
+    }
     // detail groups transposed per group: detT[((ch*nBase + atom)*64 + j)*64 + row], rows padded with zeros
     std::vector<uint8_t> rows(kRowsPad, 0);
     std::vector<float> detT(static_cast<size_t>(3) * n_base * kN * 64, 0.0f);

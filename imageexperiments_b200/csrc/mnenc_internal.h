@@ -32,7 +32,11 @@ struct MpParams {
     int nBase;               // 510
     const float* baseT;      // [64][512]  base atoms transposed: baseT[j*512 + atom], zero padded (FP32 kernel)
     const float* baseUm;     // [512][64] base atoms in the canonical UMMA K-major image (tensor-core kernel)
-    float epsRel;            // pre-filter error bound relative to ||r||_2 (tensor-core kernel)
+    float epsRel;            // pre-filter error bound relative to ||r||_2 (TF32 tensor-core kernel)
+    const uint16_t* baseUm16; // [512][64] fp16 base atoms, canonical UMMA K-major image (fp16 tensor-core kernel)
+    const uint16_t* detUm16;  // [3][nBase] fp16 images of the detail groups, 64 rows x 64, 8 KB each, zero padded rows
+    const float* rows32;      // [512 + 3*nBase*64][64] exact FP32 rows: base atoms, then detail rows (64 per group)
+    float epsRel16, epsAbs16; // pre-filter error bound of the fp16 kernel: eps = epsRel16 * ||r||_2 + epsAbs16
     const float* detT;       // [3][nBase][64][64]: detT[((ch*nBase+atom)*64 + j)*64 + row], zero padded rows
     const uint8_t* detRows;  // [nBase] rows of each detail group (62 or 63)
     const float* quant;      // [3][32]
@@ -44,10 +48,15 @@ struct MpParams {
 };
 
 void buildUmmaImage(const float* baseRowMajor, int nBase, float* image);  // host
+// host: fp16 operand images + exact row table of the fp16 kernel; returns max ||d - fp16(d)||_2 and max ||d||_2 over all atoms
+void buildF16Images(const float* baseRowMajor, int nBase, const int32_t* detailRows, const float* const detail[3], uint16_t* baseUm16,
+                    uint16_t* detUm16, float* rows32, double* maxRoundingNorm, double* maxNorm);
+size_t f16Rows32Count(int nBase);
 #ifdef __CUDACC__
 cudaError_t launchMatchingPursuit(const MpParams& p, int numSMs, cudaStream_t stream);
 size_t matchingPursuitSmemBytes();
 cudaError_t launchMatchingPursuitTc(const MpParams& p, int numSMs, cudaStream_t stream);
+cudaError_t launchMatchingPursuitF16(const MpParams& p, int numSMs, cudaStream_t stream);
 #endif
 
 // ------------------------------------------------------------------------------------------------
