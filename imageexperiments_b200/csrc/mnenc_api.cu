@@ -411,6 +411,7 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     p.rows32 = c->rows32.as<float>();
     p.epsRel16 = c->epsRel16;
     p.epsAbs16 = c->epsAbs16;
+    p.debugTiming = std::getenv("MNENC_MP_TIMING") != nullptr;
     if (c->mpMode == 2) CU(launchMatchingPursuitF16(p, c->numSMs, c->stream));
     else if (c->mpMode == 1) CU(launchMatchingPursuitTc(p, c->numSMs, c->stream));
     else CU(launchMatchingPursuit(p, c->numSMs, c->stream));

@@ -45,6 +45,7 @@ struct MpParams {
     unsigned int* workCounter;      // zeroed before launch
     unsigned long long* stats;      // [2]: sum of dictionary heights over all iterations, sum of counts
     unsigned int nbc;        // 3 * nbx * nby
+    int debugTiming;         // fp16 kernel: CTA 0 prints its per-phase cycle counts (MNENC_MP_TIMING=1)
 };
 
 void buildUmmaImage(const float* baseRowMajor, int nBase, float* image);  // host

@@ -26,6 +26,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 
 namespace mnenc {
 
@@ -35,19 +36,21 @@ constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr int kConsumerThreads = 512;
 constexpr int kTmaWarp = 16, kMmaWarp = 17;
 constexpr int kThreadsF16 = 576;
-constexpr int kStages = 6;   // ring stages of 16 KB = two group images
-constexpr int kAccs = 12;    // pair accumulators (32 TMEM columns each)
+constexpr int kStages = 4;   // ring stages of 16 KB = two group images
+constexpr int kAccs = 9;     // pair accumulators (32 TMEM columns each)
 constexpr uint32_t kGroupImgBytes = 8192;
 constexpr uint32_t kSbo = 1024, kLbo = 128, kKStepBytes = 256;  // one MMA consumes K = 16 = two 128-byte chunks
 constexpr int kMaxItems = kSlots * kMaxK;
-constexpr int kCandCap = 1024;
+constexpr int kCandCap = 512;
 constexpr int kRStride = 68;  // floats per slot in the FP32 residual array (272 B: float4 reads of 8 slots are conflict free)
-constexpr uint32_t kDetAccCol = 128;
+constexpr uint32_t kDcAccCol = 128;   // 3 resident-group tiles (one per channel) x 32 slots
+constexpr uint32_t kDetAccCol = 224;  // streamed pair accumulators
 
 struct __align__(1024) SmemF16 {
     __half D16[kRowsPad * kN];                                      // 64 KB base dictionary image
     __half R16[2 * kSlots * kN];                                    // 8 KB residual image: rows 0-31 hi, 32-63 lo
-    alignas(1024) unsigned char ring[kStages][2 * kGroupImgBytes];  // 96 KB
+    alignas(1024) unsigned char dc[3][2 * kGroupImgBytes];          // 48 KB resident KLT groups of atoms 0 and nBase-1 (Y, U, V)
+    alignas(1024) unsigned char ring[kStages][2 * kGroupImgBytes];  // 64 KB
     alignas(16) float R32[kSlots * kRStride];                       // exact residuals
     unsigned long long best[kSlots];                                // exact arg-max key per slot
     unsigned long long mbarDict, mbarBase;
@@ -56,9 +59,10 @@ struct __align__(1024) SmemF16 {
     alignas(16) uint32_t approxMax[kSlots];  // max |p~| per slot, float bits
     alignas(16) float twoEps[kSlots];
     uint32_t tmemBase;
-    uint32_t nItems[2];
+    uint32_t nItems[2], nDc[2];
     uint32_t nCand;
-    uint16_t items[2][kMaxItems];  // slot | group position << 5
+    uint16_t items[2][kMaxItems];    // streamed groups: slot | group position << 5
+    uint16_t dcItems[2][kMaxItems];  // resident groups: slot | group position << 5 | (atom != 0) << 10
     uint2 cand[kCandCap];          // {slot | dictionary index << 8, row id in rows32}
     uint32_t pairs[kSlots * kMaxK];
     uint16_t groupAtom[kSlots * kMaxK];
@@ -72,6 +76,8 @@ struct __align__(1024) SmemF16 {
     uint8_t zeroRes[kSlots];
     uint8_t detRows[kRowsPad];
 };
+
+static_assert(sizeof(SmemF16) + 1024 <= 232448, "shared memory of the fp16 matching-pursuit kernel exceeds 227 KB");
 
 __device__ __forceinline__ unsigned long long makeKey(float p, int idx) {
     const unsigned int b = __float_as_uint(p);
@@ -173,8 +179,8 @@ __device__ __forceinline__ float exactDot(const float* row, const float* r) {
 namespace {
 
 __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const MpParams p) {
-    extern __shared__ unsigned char smemRaw[];
-    SmemF16& s = *reinterpret_cast<SmemF16*>((reinterpret_cast<uintptr_t>(smemRaw) + 1023) & ~static_cast<uintptr_t>(1023));
+    extern __shared__ __align__(1024) unsigned char smemRaw[];
+    SmemF16& s = *reinterpret_cast<SmemF16*>(smemRaw);  // no pointer arithmetic on integers: accesses stay LDS/STS/ATOMS
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
@@ -186,6 +192,7 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
         for (int i = 0; i < kStages; ++i) mbarInit(&s.full[i], 1), mbarInit(&s.empty[i], 1);
         for (int i = 0; i < kAccs; ++i) mbarInit(&s.accFull[i], 1), mbarInit(&s.accEmpty[i], 4);
         s.nItems[0] = s.nItems[1] = 0;
+        s.nDc[0] = s.nDc[1] = 0;
         s.nCand = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -201,9 +208,14 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
     const uint32_t tmemBase = s.tmemBase;
     if (tid == 0) {
         constexpr uint32_t total = kRowsPad * kN * sizeof(__half);
-        mbarExpectTx(&s.mbarDict, total);
+        mbarExpectTx(&s.mbarDict, total + 6 * kGroupImgBytes);
         for (uint32_t o = 0; o < total; o += 32768)
             bulkCopy(reinterpret_cast<unsigned char*>(s.D16) + o, reinterpret_cast<const unsigned char*>(p.baseUm16) + o, 32768, &s.mbarDict);
+        for (int ch = 0; ch < 3; ++ch)  // resident groups: atom 0 -> rows 0-63 of the channel's tile, atom nBase-1 -> rows 64-127
+            for (int h = 0; h < 2; ++h)
+                bulkCopy(s.dc[ch] + h * kGroupImgBytes,
+                         reinterpret_cast<const unsigned char*>(p.detUm16) + (static_cast<size_t>(ch) * p.nBase + (h ? p.nBase - 1 : 0)) * kGroupImgBytes,
+                         kGroupImgBytes, &s.mbarDict);
     }
 
     // ---- consumer-thread geometry (step C: half-warp `slot` owns slot `slot`; thread l16 owns pixels 4*l16 .. 4*l16+3) ----
@@ -296,6 +308,18 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
     const uint32_t laneBase = static_cast<uint32_t>(quarter * 32) << 16;
     const uint32_t dAddr = smemAddr(s.D16), rAddr = smemAddr(s.R16);
     uint32_t pairBase = 0, trip = 0;
+    // optional phase timing (MNENC_MP_TIMING=1): cycles of consumer thread 0 of CTA 0 per phase, printed at the end
+    long long tPhase[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tLast = 0;
+    unsigned long long nItemsSum = 0, nDcSum = 0, nCandSum = 0;
+    const bool timing = p.debugTiming && tid == 0 && blockIdx.x == 0;
+#define MNENC_TICK(k)                     \
+    if (timing) {                         \
+        const long long now_ = clock64(); \
+        tPhase[k] += now_ - tLast;        \
+        tLast = now_;                     \
+    }
+    if (timing) tLast = clock64();
 
     while (true) {
         // ---- trip barrier: residual images, slot state and the item list of this trip are complete ----
@@ -304,6 +328,9 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
         fenceAfter();
         const uint32_t cur = trip & 1u;
         const uint32_t nItems = s.nItems[cur];
+        const uint32_t nDc = s.nDc[cur];
+        MNENC_TICK(0)  // trip barrier
+        if (timing) nItemsSum += nItems, nDcSum += nDc;
         const uint32_t nPairs = (nItems + 1u) >> 1;
 
         if (warp == kMmaWarp) {
@@ -318,6 +345,17 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
                         for (int ks = 0; ks < 4; ++ks)
                             ummaF16(tmemBase + t * 32, umDesc(dAddr + t * 16 * kSbo + ks * kKStepBytes),
                                     umDesc(rAddr + h * (kSlots * kN * 2) + ks * kKStepBytes), kIdescF16, (h | ks) ? 1u : 0u);
+                if (nDc) {
+                    const uint32_t cAddr = smemAddr(s.dc[0]);
+#pragma unroll
+                    for (int t = 0; t < 3; ++t)
+#pragma unroll
+                        for (int h = 0; h < 2; ++h)
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks)
+                                ummaF16(tmemBase + kDcAccCol + t * 32, umDesc(cAddr + t * 2 * kGroupImgBytes + ks * kKStepBytes),
+                                        umDesc(rAddr + h * (kSlots * kN * 2) + ks * kKStepBytes), kIdescF16, (h | ks) ? 1u : 0u);
+                }
                 ummaCommit(&s.mbarBase);
                 for (uint32_t q = 0; q < nPairs; ++q) {
                     const uint32_t ctr = pairBase + q;
@@ -360,6 +398,7 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
             // ================= consumers =================
             if (tid == 0) {
                 s.nItems[cur ^ 1u] = 0;
+                s.nDc[cur ^ 1u] = 0;
                 s.nCand = 0;
             }
             const unsigned liveMask = __ballot_sync(kFull, s.bc[lane] >= 0 && !s.zeroRes[lane]);
@@ -374,6 +413,7 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
                 for (int i = 0; i < 32; ++i) v[i] = fabsf(__uint_as_float(raw[i]));
             }
             fenceBefore();
+            MNENC_TICK(1)  // wait for the base MMA + TMEM load
             {   // per-slot maximum over the warp's 32 atoms: transposed butterfly, lane L ends with slot L
                 float w16[16], w8[8], w4[4], w2[2];
                 const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
@@ -389,6 +429,7 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
                 atomicMax(&s.approxMax[lane], __float_as_uint(m));
             }
             consumerBarrier();
+            MNENC_TICK(2)  // butterfly + barrier
             // ---- (b) base atoms that can still be the exact maximum -> candidate list ----
             if (myAtom < p.nBase) {
                 unsigned cand = 0;
@@ -404,12 +445,37 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
                     cand |= (v[4 * i4 + 3] + e4.w >= m4.w ? 1u : 0u) << (4 * i4 + 3);
                 }
                 cand &= liveMask;
-                while (cand) {
+                while (cand) {  // re-scored on the spot: this time is otherwise spent waiting for the streamed groups
                     const int sl = __ffs(cand) - 1;
                     cand &= cand - 1;
-                    pushCandidate(sl, myAtom, static_cast<uint32_t>(myAtom));
+                    const float a = exactDot(p.rows32 + static_cast<size_t>(myAtom) * kN, s.R32 + sl * kRStride);
+                    atomicMax(&s.best[sl], makeKey(a, myAtom));
                 }
             }
+            MNENC_TICK(3)  // base filter + inline re-score
+            // ---- (c0) resident groups (atoms 0 / nBase-1): scores of ALL slots come from one shared tile per channel ----
+            for (uint32_t i = static_cast<uint32_t>(tile); i < nDc; i += 4) {
+                const uint32_t it = s.dcItems[cur][i];
+                if (static_cast<int>(it >> 10) != (quarter >> 1)) continue;  // warp-uniform: lanes 0-63 atom 0, 64-127 atom nBase-1
+                const int sl = static_cast<int>(it & 31u), gi = static_cast<int>((it >> 5) & 31u);
+                const int ch = s.bc[sl] % 3;
+                const uint32_t raw = tmemLoad1(tmemBase + laneBase + kDcAccCol + static_cast<uint32_t>(ch * 32 + sl));
+                const int atom = s.groupAtom[sl * kMaxK + gi];
+                const int first = s.groupFirst[sl * kMaxK + gi];
+                const int row = (quarter & 1) * 32 + lane;
+                const bool rowOk = row < s.detRows[atom];
+                const float a = rowOk ? fabsf(__uint_as_float(raw)) : 0.0f;
+                float wmax = a;
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) wmax = fmaxf(wmax, __shfl_xor_sync(kFull, wmax, off));
+                uint32_t seen = 0;
+                if (lane == 0) seen = max(atomicMax(&s.approxMax[sl], __float_as_uint(wmax)), __float_as_uint(wmax));
+                seen = __shfl_sync(kFull, seen, 0);
+                if (rowOk && ((liveMask >> sl) & 1u) && a + s.twoEps[sl] >= __uint_as_float(seen))
+                    pushCandidate(sl, first + row, static_cast<uint32_t>(kRowsPad + (ch * p.nBase + atom) * 64 + row));
+            }
+            fenceBefore();
+            MNENC_TICK(4)  // resident groups
             // ---- (c) detail pairs: warpgroup g takes pairs g, g+4, ...; quarters 0,1 -> first item, 2,3 -> second ----
             for (uint32_t q = static_cast<uint32_t>(tile); q < nPairs; q += 4) {
                 const uint32_t ctr = pairBase + q;
@@ -443,9 +509,11 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
                 }
             }
             consumerBarrier();
+            MNENC_TICK(5)  // streamed pairs + barrier
             // ---- (d) exact re-score of the candidates, one per thread ----
             {
                 const uint32_t n = min(s.nCand, static_cast<uint32_t>(kCandCap));
+                if (timing) nCandSum += s.nCand;
                 for (uint32_t i = tid; i < n; i += kConsumerThreads) {
                     const uint2 c = s.cand[i];
                     const int sl = static_cast<int>(c.x & 31u);
@@ -454,6 +522,7 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
                 }
             }
             consumerBarrier();
+            MNENC_TICK(6)  // candidate re-score + barrier
             // ================= step C: select, quantise, update (MatchingPursuit.cpp:86-104) =================
             active = 0;
             const int bc = s.bc[slot];
@@ -510,11 +579,28 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
                     }
                     if (reps + 1 == p.K) {
                         count = p.K;
-                    } else if (ngNew > 0) {  // this slot's (slot, group) items of the next trip
-                        uint32_t at = 0;
-                        if (l16 == 0) at = atomicAdd(&s.nItems[cur ^ 1u], static_cast<uint32_t>(ngNew));
-                        at = __shfl_sync(halfMask, at, lane & 16);
-                        for (int gi = l16; gi < ngNew; gi += 16) s.items[cur ^ 1u][at + gi] = static_cast<uint16_t>(slot | (gi << 5));
+                    } else if (ngNew > 0) {  // this slot's (slot, group) items of the next trip: resident or streamed
+                        __syncwarp(halfMask);
+                        for (int g0 = 0; g0 < ngNew; g0 += 16) {
+                            const int gi = g0 + l16;
+                            const bool valid = gi < ngNew;
+                            const int atom = valid ? s.groupAtom[slot * kMaxK + gi] : -1;
+                            const bool isDc = valid && (atom == 0 || atom == p.nBase - 1);
+                            const unsigned mDc = (__ballot_sync(halfMask, isDc) & halfMask) >> (lane & 16);
+                            const unsigned mSt = (__ballot_sync(halfMask, valid && !isDc) & halfMask) >> (lane & 16);
+                            uint32_t atDc = 0, atSt = 0;
+                            if (l16 == 0) {
+                                if (mDc) atDc = atomicAdd(&s.nDc[cur ^ 1u], static_cast<uint32_t>(__popc(mDc)));
+                                if (mSt) atSt = atomicAdd(&s.nItems[cur ^ 1u], static_cast<uint32_t>(__popc(mSt)));
+                            }
+                            atDc = __shfl_sync(halfMask, atDc, lane & 16);
+                            atSt = __shfl_sync(halfMask, atSt, lane & 16);
+                            const unsigned below = (1u << l16) - 1u;
+                            if (isDc)
+                                s.dcItems[cur ^ 1u][atDc + __popc(mDc & below)] = static_cast<uint16_t>(slot | (gi << 5) | ((atom != 0 ? 1 : 0) << 10));
+                            else if (valid)
+                                s.items[cur ^ 1u][atSt + __popc(mSt & below)] = static_cast<uint16_t>(slot | (gi << 5));
+                        }
                     }
                 }
                 if (count >= 0) {
@@ -529,6 +615,7 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            MNENC_TICK(7)  // step C
         }
         pairBase += nPairs;
         ++trip;
@@ -544,6 +631,12 @@ __global__ void __launch_bounds__(kThreadsF16, 1) matchingPursuitF16Kernel(const
             atomicAdd(&p.stats[1], statPicks);
         }
     }
+    if (timing)
+        printf("mp f16 timing, CTA 0: trips %u; cycles per trip: barrier %lld, baseMMA+ld %lld, max+bar %lld, base filter %lld, resident %lld, "
+               "streamed+bar %lld, cand+bar %lld, stepC %lld; per trip: streamed items %.1f, resident items %.1f, listed candidates %.1f\n",
+               trip, tPhase[0] / trip, tPhase[1] / trip, tPhase[2] / trip, tPhase[3] / trip, tPhase[4] / trip, tPhase[5] / trip, tPhase[6] / trip,
+               tPhase[7] / trip, double(nItemsSum) / trip, double(nDcSum) / trip, double(nCandSum) / trip);
+#undef MNENC_TICK
     fenceBefore();
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmemBase), "r"(512u) : "memory");
