@@ -96,8 +96,8 @@ struct mnenc_ctx {
     // dictionary
     DevBuf baseT, baseUm, detT, detRows, quant, baseUm16, detUm16, rows32;
     float epsRel = 0.0f, epsRel16 = 0.0f, epsAbs16 = 0.0f;
-    int mpMode = 2;  // 2 = fp16 tensor-core pre-filter for base + detail (default); MNENC_MP=tf32 / fp32 select the
-                     // earlier kernels (base-only TF32 pre-filter / exact full scan) for A/B validation
+    int mpMode = 3;  // 3 = two-team fp16 tensor-core kernel (default); MNENC_MP=f16 / tf32 / fp32 select the earlier
+                     // kernels (single team / base-only TF32 pre-filter / exact full scan) for A/B validation
     // image + symbols
     DevBuf rgb, counts, pairs, mpScratch;
     size_t lastW = 0, lastH = 0;
@@ -412,7 +412,8 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     p.epsRel16 = c->epsRel16;
     p.epsAbs16 = c->epsAbs16;
     p.debugTiming = std::getenv("MNENC_MP_TIMING") != nullptr;
-    if (c->mpMode == 2) CU(launchMatchingPursuitF16(p, c->numSMs, c->stream));
+    if (c->mpMode == 3) CU(launchMatchingPursuitTeams(p, c->numSMs, c->stream));
+    else if (c->mpMode == 2) CU(launchMatchingPursuitF16(p, c->numSMs, c->stream));
     else if (c->mpMode == 1) CU(launchMatchingPursuitTc(p, c->numSMs, c->stream));
     else CU(launchMatchingPursuit(p, c->numSMs, c->stream));
     c->launches += nbc ? 1 : 0;
@@ -510,7 +511,7 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
         }
         c->epsRel = static_cast<float>((2.0 / 1024.0 + 1.0 / 1048576.0 + 6e-6) * maxNorm * 1.15);
     }
-    if (const char* mode = std::getenv("MNENC_MP")) c->mpMode = std::string(mode) == "fp32" ? 0 : (std::string(mode) == "tf32" ? 1 : 2);
+    if (const char* mode = std::getenv("MNENC_MP")) c->mpMode = std::string(mode) == "fp32" ? 0 : (std::string(mode) == "tf32" ? 1 : (std::string(mode) == "f16" ? 2 : 3));
     {   // fp16 operand images + exact row table of the fp16 tensor-core kernel, and its rigorous pre-filter bound:
         //   |p~ - p_oracle| <= ||d - fp16(d)|| ||r||  (dictionary rounding, Cauchy-Schwarz)
         //                    + ||d|| ||r|| (2^-22 residual hi/lo split + 4e-5 tensor-core accumulation + 64 * 2^-24 oracle rounding)

@@ -42,7 +42,7 @@ struct MpParams {
     const float* quant;      // [3][32]
     uint16_t* counts;        // [nbc] out: atoms per block-channel == the `lengths` stream
     uint32_t* pairs;         // [nbc][K] out: deltaId | intCoeff << 16 (0 beyond count)
-    unsigned int* workCounter;      // zeroed before launch
+    unsigned int* workCounter;      // [3] zeroed before launch ([0] only, except the team kernel: one per channel)
     unsigned long long* stats;      // [2]: sum of dictionary heights over all iterations, sum of counts
     unsigned int nbc;        // 3 * nbx * nby
     int debugTiming;         // fp16 kernel: CTA 0 prints its per-phase cycle counts (MNENC_MP_TIMING=1)
@@ -58,6 +58,7 @@ cudaError_t launchMatchingPursuit(const MpParams& p, int numSMs, cudaStream_t st
 size_t matchingPursuitSmemBytes();
 cudaError_t launchMatchingPursuitTc(const MpParams& p, int numSMs, cudaStream_t stream);
 cudaError_t launchMatchingPursuitF16(const MpParams& p, int numSMs, cudaStream_t stream);
+cudaError_t launchMatchingPursuitTeams(const MpParams& p, int numSMs, cudaStream_t stream);
 #endif
 
 // ------------------------------------------------------------------------------------------------
