@@ -237,9 +237,12 @@ def run_ours(args):
         except Exception:
             pass
         sm_max = float(peaks.get("sm_max_mhz", 1965.0))
-        # Dominant kernel = matchingPursuitKernel. Its arithmetic must reproduce the oracle's UNFUSED f32 mul+add, so one
-        # flop occupies one FP32 issue slot: peak = SMs x 128 lanes x max SM clock (half the FFMA figure).
-        fp32_peak = 148 * 128 * sm_max * 1e6 / 1e12
+        # Dominant kernel = matchingPursuitTeamsKernel: every dictionary row is scored on the tensor cores (tcgen05 kind::f16),
+        # the FP32 pipe only re-scores the few near-maximal rows exactly => tensor roofline, measured cuBLAS bf16 burst peak
+        # (fp16 runs at the same rate; the kernel is timed alone with CUDA events on its own stream).
+        tensor_peak = float(peaks.get("bf16_tflops", 1590.0))
+        peak_src = "MEASURED_PEAKS.json bf16_tflops (burst)" if "bf16_tflops" in peaks else "fallback 1.59 PFLOP/s"
+        fp32_peak = 148 * 128 * sm_max * 1e6 / 1e12  # unfused mul+add issue slots: what the exact full-scan kernel is bound by
         achieved = flops / (mp_ms / 1e3) / 1e12 if mp_ms > 0 else 0.0
         control_d2h = 65536 * 16 + 4096
         line = {
@@ -254,11 +257,14 @@ def run_ours(args):
             "e2e": {"value": round(e2e, 2), "unit": "MP/s", "h2d_bytes_per_step": W * H * 3, "d2h_bytes_per_step": int(out_b2) + control_d2h,
                     "ms_per_step": round(dt_e2e / args.steps * 1e3, 3)},
             "gpu_launches": int(launches),
-            "roofline": {"kernel": "matchingPursuitKernel", "bound": "fp32", "achieved": round(achieved, 3), "peak": round(fp32_peak, 2),
-                         "unit": "TFLOP/s", "frac": round(achieved / fp32_peak, 4), "traffic": None,
-                         "note": "algorithmic flops (SURVEY.md 8d, counted by the kernel) / CUDA-event time of the kernel on its own stream; "
-                                 f"peak = 148 SMs x 128 FP32 lanes x {sm_max:.0f} MHz (MEASURED_PEAKS.json sm_max_mhz) issue slots: "
-                                 "oracle-exact arithmetic is unfused mul+add, 1 flop per slot",
+            "roofline": {"kernel": "matchingPursuitTeamsKernel", "bound": "tensor", "achieved": round(achieved, 3), "peak": round(tensor_peak, 1),
+                         "unit": "TFLOP/s", "frac": round(achieved / tensor_peak, 4), "traffic": 234.4e6,
+                         "note": "algorithmic flops (SURVEY.md 8d: 2*64*dictionary height per greedy iteration, counted by the kernel) / "
+                                 f"CUDA-event time of the kernel on its own stream; peak = {peak_src}. The kernel is latency bound "
+                                 "(N = 32 slots per MMA, exact re-score and residual update between MMAs), see "
+                                 "profiles/r01_mp_teams_kernel_ncu.md; traffic = dram read+write bytes of one launch from that ncu capture "
+                                 "(algorithmic: 48.3 MB pixels + 37.5 MB dictionary images + 98 MB symbols)",
+                         "frac_of_fp32_issue_peak": round(achieved / fp32_peak, 4),
                          "ms_per_launch": round(mp_ms, 3), "gflop_per_launch": round(flops / 1e9, 2)},
             "bytes_out_per_step": int(out_b),
         }
