@@ -17,7 +17,7 @@ _vp, _sz = C.c_void_p, C.c_size_t
 EXPORTS = (
     "mnenc_last_error", "mnenc_create", "mnenc_destroy", "mnenc_quant_tables", "mnenc_set_quant", "mnenc_encode_rgb8",
     "mnenc_encode_rgb8_device", "mnenc_free", "mnenc_get_symbols", "mnenc_pack_symbols", "mnenc_last_timing", "mnenc_last_work",
-    "mnenc_debug_plan_sequence",
+    "mnenc_debug_plan_sequence", "mnenc_debug_stitch_runs", "mnenc_debug_rle_chunk_size",
 )
 
 
@@ -53,6 +53,9 @@ def load() -> C.CDLL:
     L.mnenc_last_timing.argtypes = [_vp, _vp]
     L.mnenc_last_work.argtypes = [_vp, _vp, _vp, _vp]
     L.mnenc_debug_plan_sequence.argtypes = [_vp, _vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _vp]
+    L.mnenc_debug_stitch_runs.argtypes = [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp]
+    L.mnenc_debug_rle_chunk_size.argtypes = [C.c_uint32, C.c_uint32, C.c_uint64]
+    L.mnenc_debug_rle_chunk_size.restype = C.c_uint32
     _lib = L
     return L
 

@@ -688,4 +688,14 @@ int mnenc_debug_plan_sequence(const uint32_t* symbols, const uint32_t* freqs, co
     return MNENC_OK;
 }
 
+int mnenc_debug_stitch_runs(const uint32_t* records, int nranks, int n_streams, int rank, uint32_t* carry_in, uint32_t* extend_out) {
+    if (!records || !carry_in || !extend_out || nranks < 1 || n_streams < 0 || rank < 0 || rank >= nranks)
+        return fail(MNENC_ERR_ARG, "bad argument");
+    static_assert(sizeof(mnenc::StripeBoundary) == 5 * sizeof(uint32_t), "record layout");
+    mnenc::stitchRuns(reinterpret_cast<const mnenc::StripeBoundary*>(records), nranks, n_streams, rank, carry_in, extend_out);
+    return MNENC_OK;
+}
+
+uint32_t mnenc_debug_rle_chunk_size(uint32_t carry, uint32_t len, uint64_t total) { return mnenc::rleChunkedSize(carry, len, total); }
+
 }  // extern "C"

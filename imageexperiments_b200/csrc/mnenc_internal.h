@@ -99,6 +99,20 @@ struct SequencePlan {
 // caller's original order.
 void planSequence(const std::vector<SymbolStat>& stats, SequencePlan& plan);
 
+// ------------------------------------------------------------------------------------------------
+// Multi-GPU stripe path, host logic (stripe_host.cpp)
+// ------------------------------------------------------------------------------------------------
+struct StripeBoundary {   // one per (rank, symbol stream), all-gathered
+    uint32_t n;           // entries of the stream held by the rank
+    uint32_t first, firstRun;  // first value and length of the run it starts (n if the slice is one run)
+    uint32_t last, lastRun;    // last value and length of the run it ends
+};
+// For `rank`: carryIn[s] = length of the equal-valued run that ends right before its slice of stream s,
+// extendOut[s] = length by which its last run continues on later ranks.
+void stitchRuns(const StripeBoundary* rec, int nranks, int nStreams, int rank, uint32_t* carryIn, uint32_t* extendOut);
+// RLE symbols a slice emits for `len` elements of a run that has `carry` elements before it and `total` overall.
+uint32_t rleChunkedSize(uint32_t carry, uint32_t len, uint64_t total);
+
 // compressed::createQuantizationTables, float overload (CompressedImage.cpp:168-210).
 int quantTables(int K, int blockSize, double bpp, float* out3K);
 

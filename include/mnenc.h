@@ -104,6 +104,17 @@ int mnenc_debug_plan_sequence(const uint32_t* symbols, const uint32_t* freqs, co
                               uint32_t* golomb_m, uint32_t* codes, uint8_t* lens, uint32_t* eof_code, uint8_t* eof_len,
                               uint8_t* header_bytes, size_t header_cap, uint64_t* header_bits, uint64_t* payload_bits);
 
+/*
+ * Host-logic test hook of the multi-GPU stripe path (used by the CPU-only world_size-2 gloo tests): run stitching
+ * of huffman::runLengthEncode (Huffman.cpp:246-279) across ranks. records = [nranks][n_streams][5] u32
+ * {n, first value, first run length, last value, last run length} as all-gathered by the ranks; outputs for `rank`:
+ * carry_in[s] / extend_out[s] = elements of its first / last run that live on earlier / later ranks.
+ * mnenc_debug_rle_chunk_size = RLE symbols a rank emits for `len` elements of a run with `carry` elements before them
+ * and `total` elements overall (chunks of 32 769 counted from the run's global start).
+ */
+int mnenc_debug_stitch_runs(const uint32_t* records, int nranks, int n_streams, int rank, uint32_t* carry_in, uint32_t* extend_out);
+uint32_t mnenc_debug_rle_chunk_size(uint32_t carry, uint32_t len, uint64_t total);
+
 #ifdef __cplusplus
 }
 #endif

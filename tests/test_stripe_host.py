@@ -1,0 +1,118 @@
+"""Multi-GPU stripe path, host logic, on the CPU with world_size 2 and 3 (gloo): every rank holds a contiguous slice of
+each symbol stream, all-gathers boundary records, stitches runs with the product's host code (mnenc_debug_stitch_runs)
+and run-length codes its slice alone; the concatenation over ranks must equal the oracle's RLE of the whole stream
+(huffman::runLengthEncode, Huffman.cpp:246-279), including runs that cross ranks and the 32 769 chunk rule."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CHUNK = 32769
+
+
+def make_streams():
+    rng = np.random.default_rng(42)
+    streams = [
+        np.zeros(0, np.uint16),
+        np.full(7, 5, np.uint16),
+        np.full(100000, 9, np.uint16),                                  # one run over all ranks, three chunks
+        np.concatenate([rng.integers(0, 3, 50), np.full(70000, 2), rng.integers(0, 3, 50)]).astype(np.uint16),
+        rng.integers(0, 2, 4000).astype(np.uint16),                     # many short runs
+        np.repeat(rng.integers(0, 50, 300), rng.integers(1, 400, 300)).astype(np.uint16),
+        np.concatenate([np.full(32769, 1), np.full(32770, 1)]).astype(np.uint16),
+        np.array([0, 0, 0, 1], np.uint16),                              # leading zeros are a normal run
+    ]
+    return streams
+
+
+def cuts(n, world, rng):
+    """Slice boundaries, deliberately ragged (empty slices, cuts inside runs)."""
+    c = np.sort(rng.integers(0, n + 1, world - 1)) if n else np.zeros(world - 1, int)
+    return [0] + [int(x) for x in c] + [n]
+
+
+def boundary(v):
+    if v.size == 0:
+        return [0, 0, 0, 0, 0]
+    ch = np.nonzero(v[1:] != v[:-1])[0]
+    first_run = int(ch[0] + 1) if ch.size else v.size
+    last_run = int(v.size - (ch[-1] + 1)) if ch.size else v.size
+    return [v.size, int(v[0]), first_run, int(v[-1]), last_run]
+
+
+def rle_slice(v, carry, ext):
+    """What the stripe RLE kernels emit for one slice: a chunk [v, v, len-2] / [v] belongs to the rank holding its first
+    element; chunks are counted from the run's global start."""
+    out = []
+    if v.size == 0:
+        return out
+    starts = np.concatenate([[0], np.nonzero(v[1:] != v[:-1])[0] + 1, [v.size]])
+    for i in range(len(starts) - 1):
+        s0, s1 = int(starts[i]), int(starts[i + 1])
+        c = carry if s0 == 0 else 0
+        total = c + (s1 - s0) + (ext if s1 == v.size else 0)
+        k = (c + CHUNK - 1) // CHUNK
+        while k * CHUNK < c + (s1 - s0):
+            ln = min(CHUNK, total - k * CHUNK)
+            out += [int(v[s0])] if ln == 1 else [int(v[s0]), int(v[s0]), ln - 2]
+            k += 1
+    return out
+
+
+def worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from imageexperiments_b200 import _lib
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    L = _lib.load()
+    streams = make_streams()
+    rng = np.random.default_rng(7)
+    ns = len(streams)
+    slices = []
+    for v in streams:
+        c = cuts(v.size, world, rng)
+        slices.append(v[c[rank]:c[rank + 1]])
+    rec = torch.tensor([boundary(v) for v in slices], dtype=torch.int64)
+    allrec = [torch.zeros_like(rec) for _ in range(world)]
+    dist.all_gather(allrec, rec)
+    records = np.ascontiguousarray(torch.stack(allrec).numpy().astype(np.uint32))
+    carry = np.zeros(ns, np.uint32)
+    ext = np.zeros(ns, np.uint32)
+    rc = L.mnenc_debug_stitch_runs(records.ctypes.data, world, ns, rank, carry.ctypes.data, ext.ctypes.data)
+    assert rc == 0
+    mine = [rle_slice(v, int(carry[i]), int(ext[i])) for i, v in enumerate(slices)]
+    # the size the device scan would use must agree with what is emitted
+    for i, v in enumerate(slices):
+        if v.size and (v == v[0]).all():
+            want = L.mnenc_debug_rle_chunk_size(int(carry[i]), int(v.size), int(carry[i]) + int(v.size) + int(ext[i]))
+            assert want == len(mine[i]), (i, want, len(mine[i]))
+    gathered = [None] * world
+    dist.all_gather_object(gathered, mine)
+    if rank == 0:
+        q.put([sum((g[i] for g in gathered), []) for i in range(ns)])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_rle_stitching_matches_oracle(world, oraclelib):
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = q.get(timeout=120)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    for v, g in zip(make_streams(), got):
+        want = oraclelib.rle(v)
+        assert np.array_equal(np.asarray(g, np.uint16), want), (v.size, len(g), want.size)
