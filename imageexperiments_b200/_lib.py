@@ -17,7 +17,8 @@ _vp, _sz = C.c_void_p, C.c_size_t
 EXPORTS = (
     "mnenc_last_error", "mnenc_create", "mnenc_destroy", "mnenc_quant_tables", "mnenc_set_quant", "mnenc_encode_rgb8",
     "mnenc_encode_rgb8_device", "mnenc_free", "mnenc_get_symbols", "mnenc_pack_symbols", "mnenc_last_timing", "mnenc_last_work",
-    "mnenc_debug_plan_sequence", "mnenc_debug_stitch_runs", "mnenc_debug_rle_chunk_size",
+    "mnenc_debug_plan_sequence", "mnenc_debug_stitch_runs", "mnenc_debug_rle_chunk_size", "mnenc_debug_plan_stripes",
+    "mnenc_stripe_begin", "mnenc_stripe_rle", "mnenc_stripe_histogram", "mnenc_stripe_plan", "mnenc_stripe_pack", "mnenc_stripe_finish",
 )
 
 
@@ -56,6 +57,13 @@ def load() -> C.CDLL:
     L.mnenc_debug_stitch_runs.argtypes = [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp]
     L.mnenc_debug_rle_chunk_size.argtypes = [C.c_uint32, C.c_uint32, C.c_uint64]
     L.mnenc_debug_rle_chunk_size.restype = C.c_uint32
+    L.mnenc_debug_plan_stripes.argtypes = [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp]
+    L.mnenc_stripe_begin.argtypes = [_vp, _vp, C.c_int, _sz, _sz, _sz, C.c_int, C.c_int, C.c_uint32, C.c_uint32, _vp]
+    L.mnenc_stripe_rle.argtypes = [_vp, _vp, _vp]
+    L.mnenc_stripe_histogram.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp, _vp]
+    L.mnenc_stripe_plan.argtypes = [_vp, _vp]
+    L.mnenc_stripe_pack.argtypes = [_vp, _vp, _vp, _vp, _vp]
+    L.mnenc_stripe_finish.argtypes = [_vp, _vp, _vp]
     _lib = L
     return L
 

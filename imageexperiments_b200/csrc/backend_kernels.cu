@@ -3,6 +3,8 @@
 // the data (a few MB per image), no tensor-core shaping.
 #include "backend_kernels.cuh"
 
+#include <algorithm>
+
 namespace mnenc {
 
 namespace {
@@ -217,13 +219,14 @@ __global__ void __launch_bounds__(kTileBlocks) scatterKernel(const uint16_t* cou
 
 // DC delta + zig-zag of the three depth-0 coefficient streams (CompressedImage.cpp:487-505), two steps so the
 // update can be written back in place.
-__global__ void dcDeltaKernel(const uint16_t* arena, const __grid_constant__ StreamOffsets so, int K, uint16_t* tmp, uint32_t tmpStride) {
+__global__ void dcDeltaKernel(const uint16_t* arena, const __grid_constant__ StreamOffsets so, int K, uint16_t* tmp, uint32_t tmpStride,
+                              DcPrev dcPrev) {
     const int ch = blockIdx.y;
     const uint32_t off = so.off[2 * ch * K + 1], n = so.off[2 * ch * K + 2] - off;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int32_t cur = arena[off + i];
-    const int32_t prev = i ? arena[off + i - 1] : 0;
+    const int32_t prev = i ? arena[off + i - 1] : static_cast<int32_t>(dcPrev.v[ch]);
     const int32_t d = cur - prev;
     tmp[static_cast<size_t>(ch) * tmpStride + i] = static_cast<uint16_t>((static_cast<uint32_t>(d) << 1) ^ static_cast<uint32_t>(d >> 31));
 }
@@ -268,35 +271,102 @@ struct RunStartOut {
     }
 };
 
+// A maximal run of v is coded in chunks of 32 769 elements counted from the run's start: [v, v, len-2], or [v] for a
+// chunk of one element. When the image is stripe-sharded a run may begin on an earlier rank (`carry` elements there)
+// and continue on later ranks (`ext` elements); a slice emits the chunks whose first element it holds.
+constexpr uint32_t kRleChunk = 32769u;
 __device__ __forceinline__ uint32_t rleOutSize(uint32_t L) {
-    const uint32_t full = L / 32769u, rem = L - full * 32769u;
+    const uint32_t full = L / kRleChunk, rem = L - full * kRleChunk;
     return 3u * full + (rem == 0 ? 0u : (rem == 1 ? 1u : 3u));
+}
+__device__ __forceinline__ uint32_t rleOutSizeStitched(uint32_t carry, uint32_t L, uint32_t ext) {
+    const unsigned long long total = static_cast<unsigned long long>(carry) + L + ext;
+    uint32_t out = 0;
+    for (unsigned long long k = (carry + static_cast<unsigned long long>(kRleChunk) - 1) / kRleChunk; k * kRleChunk < static_cast<unsigned long long>(carry) + L; ++k)
+        out += (total - k * kRleChunk == 1) ? 1u : 3u;
+    return out;
+}
+// carry / ext of run [s0, s1): non-zero only for the first / last run of a stream
+__device__ __forceinline__ void stitchOf(const StripeStitch* st, int nStreams, uint32_t s0, uint32_t s1, uint32_t* carry, uint32_t* ext) {
+    int lo = 0, hi = nStreams;  // largest s with off[s] <= s0 (the non-empty stream that contains s0)
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (st->off[mid] <= s0) lo = mid;
+        else hi = mid;
+    }
+    *carry = st->off[lo] == s0 ? st->carry[lo] : 0u;
+    *ext = st->off[lo + 1] == s1 ? st->ext[lo] : 0u;
 }
 struct RunSizeIn {
     const uint32_t* startPos;
-    __device__ uint32_t operator()(uint32_t r) const { return rleOutSize(startPos[r + 1] - startPos[r]); }
+    const StripeStitch* stitch;  // nullptr: the slice is the whole stream
+    int nStreams;
+    __device__ uint32_t operator()(uint32_t r) const {
+        const uint32_t s0 = startPos[r], s1 = startPos[r + 1];
+        if (!stitch) return rleOutSize(s1 - s0);
+        uint32_t carry, ext;
+        stitchOf(stitch, nStreams, s0, s1, &carry, &ext);
+        return (carry | ext) ? rleOutSizeStitched(carry, s1 - s0, ext) : rleOutSize(s1 - s0);
+    }
+};
+struct RunOffsetOut {  // offsets only (stripe path, first pass: sizes of the interior runs for the boundary records)
+    uint32_t* outOff;
+    __device__ void operator()(uint32_t r, uint32_t prefix, uint32_t /*size*/) const { outOff[r] = prefix; }
+    __device__ void total(uint32_t sum, uint32_t nRuns) const { outOff[nRuns] = sum; }
 };
 struct RleWriteOut {
     const uint32_t* startPos;
     const uint16_t* arena;
     uint16_t* rle;
     uint32_t* outOff;  // [nRuns+1]
+    const StripeStitch* stitch;
+    int nStreams;
     __device__ void operator()(uint32_t r, uint32_t prefix, uint32_t /*size*/) const {
         outOff[r] = prefix;
-        const uint32_t s0 = startPos[r];
-        uint32_t L = startPos[r + 1] - s0;
+        const uint32_t s0 = startPos[r], s1 = startPos[r + 1];
+        uint32_t L = s1 - s0;
         const uint16_t v = arena[s0];
         uint32_t o = prefix;
-        while (L >= 32769u) {
+        uint32_t carry = 0, ext = 0;
+        if (stitch) stitchOf(stitch, nStreams, s0, s1, &carry, &ext);
+        if (carry | ext) {
+            const unsigned long long total = static_cast<unsigned long long>(carry) + L + ext;
+            for (unsigned long long k = (carry + static_cast<unsigned long long>(kRleChunk) - 1) / kRleChunk; k * kRleChunk < static_cast<unsigned long long>(carry) + L; ++k) {
+                const unsigned long long len = min(static_cast<unsigned long long>(kRleChunk), total - k * kRleChunk);
+                if (len == 1) rle[o++] = v;
+                else rle[o] = v, rle[o + 1] = v, rle[o + 2] = static_cast<uint16_t>(len - 2), o += 3;
+            }
+            return;
+        }
+        while (L >= kRleChunk) {
             rle[o] = v, rle[o + 1] = v, rle[o + 2] = 32767;
             o += 3;
-            L -= 32769u;
+            L -= kRleChunk;
         }
         if (L == 1) rle[o] = v;
         else if (L >= 2) rle[o] = v, rle[o + 1] = v, rle[o + 2] = static_cast<uint16_t>(L - 2);
     }
     __device__ void total(uint32_t sum, uint32_t nRuns) const { outOff[nRuns] = sum; }
 };
+
+// Stripe path: boundary record of every stream slice (what the other ranks need to stitch runs).
+__global__ void stripeRecordsKernel(const __grid_constant__ StreamOffsets so, int nStreams, const uint16_t* arena, const uint32_t* runIdx,
+                                    const uint32_t* startPos, const uint32_t* outOff, StripeBoundary* rec) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= nStreams) return;
+    const uint32_t a = so.off[s], b = so.off[s + 1];
+    StripeBoundary r{};
+    if (b > a) {
+        const uint32_t r0 = runIdx[a], r1 = runIdx[b];
+        r.n = b - a;
+        r.first = arena[a];
+        r.firstRun = startPos[r0 + 1] - a;
+        r.last = arena[b - 1];
+        r.lastRun = b - startPos[r1 - 1];
+        r.interior = (r1 - r0 >= 3) ? outOff[r1 - 1] - outOff[r0 + 1] : 0u;
+    }
+    rec[s] = r;
+}
 
 // One CTA: RLE-or-raw decision per stream (CompressedImage.cpp:508-516) and the table of coded sequences.
 __global__ void decideKernel(const __grid_constant__ StreamOffsets so, int nStreams, uint32_t nCounts, const uint32_t* runIdx,
@@ -318,6 +388,7 @@ __global__ void decideKernel(const __grid_constant__ StreamOffsets so, int nStre
         else d.len = raw, d.off = a, d.src = 1;
         t.desc[1 + s] = d;
     }
+    for (int q = threadIdx.x; q < kMaxSeq; q += blockDim.x) t.posBase[q] = 0;
     __syncthreads();
     if (s == 0) {
         uint32_t acc = 0;
@@ -365,10 +436,12 @@ __device__ __forceinline__ uint16_t loadSym(const SeqView& v, const SeqDesc& d, 
 constexpr int kHistChunk = 4096;
 __global__ void __launch_bounds__(256) histogramKernel(SeqView v, int nSeq, uint32_t* hist, uint32_t* firstPos, uint32_t* maxSym) {
     __shared__ uint32_t sStart[kMaxSeq + 1];
+    __shared__ uint32_t sBase[kMaxSeq];
     __shared__ uint32_t sHist[kSmemHistBins];
     __shared__ uint32_t sFirst[kSmemHistBins];
     for (int i = threadIdx.x; i <= nSeq; i += blockDim.x) sStart[i] = v.table->start[i];
-    for (int i = threadIdx.x; i < kSmemHistBins; i += blockDim.x) sHist[i] = 0, sFirst[i] = 0xFFFFFFFFu;
+    for (int i = threadIdx.x; i < nSeq; i += blockDim.x) sBase[i] = v.table->posBase[i];
+    for (int i = threadIdx.x; i < kSmemHistBins; i += blockDim.x) sHist[i] = 0, sFirst[i] = kNoPos;
     __syncthreads();
     const uint32_t M = sStart[nSeq];
     const uint32_t base = blockIdx.x * kHistChunk;
@@ -387,13 +460,14 @@ __global__ void __launch_bounds__(256) histogramKernel(SeqView v, int nSeq, uint
         }
         const uint32_t k = g - sStart[q];
         const uint32_t sym = loadSym(v, d, k);
+        const uint32_t pos = k + sBase[q];  // position in the WHOLE sequence (posBase = 0 unless the image is stripe-sharded)
         localMax = max(localMax, sym);
         if (q == q0 && sym < kSmemHistBins) {
             atomicAdd(&sHist[sym], 1u);
-            atomicMin(&sFirst[sym], k);
+            atomicMin(&sFirst[sym], pos);
         } else {
             atomicAdd(&hist[static_cast<size_t>(q) * kHistBins + sym], 1u);
-            atomicMin(&firstPos[static_cast<size_t>(q) * kHistBins + sym], k);
+            atomicMin(&firstPos[static_cast<size_t>(q) * kHistBins + sym], pos);
         }
     }
     if (qPrev >= 0) atomicMax(&maxSym[qPrev], localMax);
@@ -427,7 +501,7 @@ __global__ void __launch_bounds__(256) compactKernel(uint32_t* hist, uint32_t* f
 }
 __global__ void resetHistogramKernel(const HistEntry* entries, uint32_t n, uint32_t* firstPos, uint32_t* maxSym, uint32_t* nEntries) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) firstPos[static_cast<size_t>(entries[i].seq) * kHistBins + entries[i].symbol] = 0xFFFFFFFFu;
+    if (i < n) firstPos[static_cast<size_t>(entries[i].seq) * kHistBins + entries[i].symbol] = kNoPos;
     if (i < kMaxSeq) maxSym[i] = 0;
     if (i == 0) *nEntries = 0;
 }
@@ -506,6 +580,29 @@ struct PackOut {
     __device__ void total(unsigned long long, uint32_t) const {}
 };
 
+
+// Stripe path: payload bits this rank contributes to every sequence (sum of the code lengths of its slice).
+__global__ void __launch_bounds__(256) seqBitsKernel(CodeLenIn in, uint32_t M, unsigned long long* seqBits) {
+    __shared__ unsigned long long sBits[kMaxSeq];
+    for (int i = threadIdx.x; i < kMaxSeq; i += blockDim.x) sBits[i] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * kHistChunk;
+    const uint32_t* start = in.v.table->start;
+    for (uint32_t g = base + threadIdx.x; g < min(base + kHistChunk, M); g += blockDim.x) {
+        const int q = findSeq(start, in.nSeq, g);
+        atomicAdd(&sBits[q], static_cast<unsigned long long>(in(g)));
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < in.nSeq; i += blockDim.x)
+        if (sBits[i]) atomicAdd(&seqBits[i], sBits[i]);
+}
+
+__global__ void readIndirectKernel(const uint32_t* arr, const uint32_t* idx, uint32_t* out) { *out = arr[*idx]; }
+
+__global__ void fillU32Kernel(uint32_t* p, size_t n, uint32_t v) {
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * blockDim.x) p[i] = v;
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------
@@ -519,15 +616,23 @@ int launchTileCounts(const BackendBuffers& b, cudaStream_t st) {
     return 2;
 }
 
-int launchScatter(const BackendBuffers& b, const StreamOffsets& so, cudaStream_t st) {
+int launchScatterRaw(const BackendBuffers& b, const StreamOffsets& so, cudaStream_t st) {
     scatterKernel<<<b.ntiles, kTileBlocks, 0, st>>>(b.counts, b.pairs, b.nblocks, b.K, b.tileCounts, so, b.arena);
-    const dim3 grid((b.nblocks + 255) / 256, 3);
-    dcDeltaKernel<<<grid, 256, 0, st>>>(b.arena, so, b.K, b.dcTmp, b.nblocks);
-    dcWriteBackKernel<<<grid, 256, 0, st>>>(b.arena, so, b.K, b.dcTmp, b.nblocks);
-    return 3;
+    return 1;
 }
 
-int launchRleAndDecide(const BackendBuffers& b, const StreamOffsets& so, uint32_t N, cudaStream_t st) {
+int launchDcDelta(const BackendBuffers& b, const StreamOffsets& so, const DcPrev& prev, cudaStream_t st) {
+    const dim3 grid((b.nblocks + 255) / 256, 3);
+    dcDeltaKernel<<<grid, 256, 0, st>>>(b.arena, so, b.K, b.dcTmp, b.nblocks, prev);
+    dcWriteBackKernel<<<grid, 256, 0, st>>>(b.arena, so, b.K, b.dcTmp, b.nblocks);
+    return 2;
+}
+
+int launchScatter(const BackendBuffers& b, const StreamOffsets& so, cudaStream_t st) {
+    return launchScatterRaw(b, so, st) + launchDcDelta(b, so, DcPrev{}, st);
+}
+
+int launchRleRuns(const BackendBuffers& b, const StreamOffsets& so, uint32_t N, cudaStream_t st) {
     const int nStreams = 6 * b.K;
     int launches = 0;
     if (N) {
@@ -535,11 +640,25 @@ int launchRleAndDecide(const BackendBuffers& b, const StreamOffsets& so, uint32_
         rleMarkStreamStartsKernel<<<(nStreams + 255) / 256, 256, 0, st>>>(so, nStreams, N, b.flags);
         launches += 2;
     }
-    launches += deviceScan<uint32_t>(FlagIn{b.flags}, RunStartOut{b.runIdx, b.startPos}, N, nullptr, b.blockSums32, st);
+    return launches + deviceScan<uint32_t>(FlagIn{b.flags}, RunStartOut{b.runIdx, b.startPos}, N, nullptr, b.blockSums32, st);
+}
+
+int launchRleWrite(const BackendBuffers& b, uint32_t N, const StripeStitch* stitch, cudaStream_t st) {
     // runs: count lives in device memory (runIdx[N]); launch over the upper bound N, extra tiles exit at once
-    launches += deviceScan<uint32_t>(RunSizeIn{b.startPos}, RleWriteOut{b.startPos, b.arena, b.rleArena, b.outOff}, N, b.runIdx + N,
-                                     b.blockSums32, st);
-    return launches;
+    const int nStreams = 6 * b.K;
+    return deviceScan<uint32_t>(RunSizeIn{b.startPos, stitch, nStreams}, RleWriteOut{b.startPos, b.arena, b.rleArena, b.outOff, stitch, nStreams},
+                                N, b.runIdx + N, b.blockSums32, st);
+}
+
+int launchRleAndDecide(const BackendBuffers& b, const StreamOffsets& so, uint32_t N, cudaStream_t st) {
+    return launchRleRuns(b, so, N, st) + launchRleWrite(b, N, nullptr, st);
+}
+
+int launchStripeRecords(const BackendBuffers& b, const StreamOffsets& so, uint32_t N, StripeBoundary* rec, cudaStream_t st) {
+    const int nStreams = 6 * b.K;
+    int launches = deviceScan<uint32_t>(RunSizeIn{b.startPos, nullptr, nStreams}, RunOffsetOut{b.outOff}, N, b.runIdx + N, b.blockSums32, st);
+    stripeRecordsKernel<<<(nStreams + 255) / 256, 256, 0, st>>>(so, nStreams, b.arena, b.runIdx, b.startPos, b.outOff, rec);
+    return launches + 1;
 }
 
 int launchDecide(const BackendBuffers& b, const StreamOffsets& so, SeqTable* hostMirror, cudaStream_t st) {
@@ -547,12 +666,39 @@ int launchDecide(const BackendBuffers& b, const StreamOffsets& so, SeqTable* hos
     return 1;
 }
 
-int launchHistogram(const BackendBuffers& b, uint32_t upperBoundM, int nSeq, cudaStream_t st) {
+int launchHistogramOnly(const BackendBuffers& b, uint32_t upperBoundM, int nSeq, cudaStream_t st) {
     SeqView v{b.seqTable, b.counts, b.arena, b.rleArena};
     const uint32_t grid = (upperBoundM + kHistChunk - 1) / kHistChunk;
     if (grid) histogramKernel<<<grid, 256, 0, st>>>(v, nSeq, b.hist, b.firstPos, b.maxSym);
+    return grid ? 1 : 0;
+}
+
+int launchCompact(const BackendBuffers& b, int nSeq, cudaStream_t st) {
     compactKernel<<<dim3(kHistBins / 256, nSeq), 256, 0, st>>>(b.hist, b.firstPos, b.maxSym, b.entries, b.nEntries, b.entryCap);
-    return grid ? 2 : 1;
+    return 1;
+}
+
+int launchHistogram(const BackendBuffers& b, uint32_t upperBoundM, int nSeq, cudaStream_t st) {
+    return launchHistogramOnly(b, upperBoundM, nSeq, st) + launchCompact(b, nSeq, st);
+}
+
+int launchSeqBits(const BackendBuffers& b, uint32_t M, int nSeq, unsigned long long* seqBits, cudaStream_t st) {
+    SeqView v{b.seqTable, b.counts, b.arena, b.rleArena};
+    cudaMemsetAsync(seqBits, 0, sizeof(unsigned long long) * kMaxSeq, st);
+    const uint32_t grid = (M + kHistChunk - 1) / kHistChunk;
+    if (grid) seqBitsKernel<<<grid, 256, 0, st>>>(CodeLenIn{v, nSeq, b.codeTable, b.firstPos, b.entryCodes}, M, seqBits);
+    return grid ? 1 : 0;
+}
+
+int launchReadIndirect(const uint32_t* arr, const uint32_t* idx, uint32_t* out, cudaStream_t st) {
+    readIndirectKernel<<<1, 1, 0, st>>>(arr, idx, out);
+    return 1;
+}
+
+int launchFillU32(uint32_t* p, size_t n, uint32_t value, cudaStream_t st) {
+    if (!n) return 0;
+    fillU32Kernel<<<static_cast<unsigned>(std::min<size_t>((n + 255) / 256, 4096)), 256, 0, st>>>(p, n, value);
+    return 1;
 }
 
 int launchPack(const BackendBuffers& b, uint32_t M, int nSeq, cudaStream_t st) {

@@ -19,6 +19,8 @@ namespace mnenc {
 constexpr int kTileBlocks = 256;   // image blocks per scatter tile
 constexpr int kHistBins = 65536;   // u16 symbols
 constexpr int kSmemHistBins = 4096;
+constexpr uint32_t kNoPos = 0x7FFFFFFFu;  // "symbol not seen": first-occurrence sentinel (positive as int32, so that a signed MIN
+                                          // all-reduce over the ranks of a stripe-sharded image is also the unsigned minimum)
 
 // Per coded sequence (0 = `lengths`, 1 + s = symbol stream s), written by decideKernel.
 struct SeqDesc {
@@ -31,6 +33,7 @@ struct SeqDesc {
 struct SeqTable {                 // device + pinned host mirror, filled by decideKernel
     SeqDesc desc[kMaxSeq];
     uint32_t start[kMaxSeq + 1];  // exclusive prefix of desc[].len; start[nSeq] = M
+    uint32_t posBase[kMaxSeq];    // position of the slice's first element in the WHOLE sequence (0 unless stripe-sharded)
     uint32_t nRuns;               // diagnostic
 };
 
@@ -50,6 +53,15 @@ struct HistEntry {
     uint32_t symbol;
     uint32_t freq;
     uint32_t firstPos;
+};
+
+struct DcPrev {        // DC value preceding the slice's first entry of each colour channel (0 at the image's left edge)
+    uint32_t v[3];
+};
+struct StripeStitch {  // device table of the stripe path: stream offsets + run stitching of this rank's slices
+    uint32_t off[6 * kMaxK + 1];
+    uint32_t carry[6 * kMaxK];
+    uint32_t ext[6 * kMaxK];
 };
 
 struct StreamOffsets {
@@ -80,7 +92,7 @@ struct BackendBuffers {
     SeqTable* seqTable;       // device
     // histogram
     uint32_t* hist;           // [kMaxSeq][65536], all zero between encodes
-    uint32_t* firstPos;       // [kMaxSeq][65536], all 0xFFFFFFFF between encodes; holds the entry index after compaction
+    uint32_t* firstPos;       // [kMaxSeq][65536], all kNoPos between encodes; holds the entry index after compaction
     uint32_t* maxSym;         // [kMaxSeq]
     HistEntry* entries;       // [entryCap]
     uint32_t* nEntries;
@@ -93,7 +105,17 @@ struct BackendBuffers {
 
 // All launch wrappers return the number of kernels they launched (for gpu_launches accounting).
 int launchTileCounts(const BackendBuffers& b, cudaStream_t st);
-int launchScatter(const BackendBuffers& b, const StreamOffsets& so, cudaStream_t st);
+int launchScatter(const BackendBuffers& b, const StreamOffsets& so, cudaStream_t st);      // raw scatter + DC delta
+int launchScatterRaw(const BackendBuffers& b, const StreamOffsets& so, cudaStream_t st);
+int launchDcDelta(const BackendBuffers& b, const StreamOffsets& so, const DcPrev& prev, cudaStream_t st);
+int launchRleRuns(const BackendBuffers& b, const StreamOffsets& so, uint32_t N, cudaStream_t st);
+int launchStripeRecords(const BackendBuffers& b, const StreamOffsets& so, uint32_t N, StripeBoundary* rec, cudaStream_t st);
+int launchRleWrite(const BackendBuffers& b, uint32_t N, const StripeStitch* stitch, cudaStream_t st);
+int launchHistogramOnly(const BackendBuffers& b, uint32_t upperBoundM, int nSeq, cudaStream_t st);
+int launchCompact(const BackendBuffers& b, int nSeq, cudaStream_t st);
+int launchSeqBits(const BackendBuffers& b, uint32_t M, int nSeq, unsigned long long* seqBits, cudaStream_t st);
+int launchFillU32(uint32_t* p, size_t n, uint32_t value, cudaStream_t st);
+int launchReadIndirect(const uint32_t* arr, const uint32_t* idx, uint32_t* out, cudaStream_t st);  // *out = arr[*idx]
 int launchRleAndDecide(const BackendBuffers& b, const StreamOffsets& so, uint32_t N, cudaStream_t st);
 int launchDecide(const BackendBuffers& b, const StreamOffsets& so, SeqTable* hostMirror, cudaStream_t st);
 int launchHistogram(const BackendBuffers& b, uint32_t upperBoundM, int nSeq, cudaStream_t st);

@@ -17,108 +17,34 @@
 #include <string>
 #include <vector>
 
-#include "../../include/mnenc.h"
-#include "backend_kernels.cuh"
-#include "host_pool.h"
-#include "mnenc_internal.h"
+#include "mnenc_ctx.cuh"
+
+namespace mnenc {
 
 namespace {
-
 thread_local std::string g_error;
+}
 
 int fail(int code, const std::string& msg) {
     g_error = msg;
     return code;
 }
 
-#define CU(expr)                                                                                          \
-    do {                                                                                                  \
-        cudaError_t e_ = (expr);                                                                          \
-        if (e_ != cudaSuccess) return fail(MNENC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
-    } while (0)
-
-double nowMs() {
-    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+void mergeOverlays(uint8_t* res, const std::vector<Overlay>& overlays) {
+    for (const Overlay& o : overlays) {
+        const uint64_t shift = o.bitPos & 7;
+        size_t byte = static_cast<size_t>(o.bitPos >> 3);
+        if (shift == 0) {
+            for (size_t i = 0; i < o.bits.bytes.size(); ++i) res[byte + i] |= o.bits.bytes[i];
+        } else {
+            for (size_t i = 0; i < o.bits.bytes.size(); ++i) {
+                res[byte + i] |= static_cast<uint8_t>(o.bits.bytes[i] >> shift);
+                const uint8_t spill = static_cast<uint8_t>(o.bits.bytes[i] << (8 - shift));
+                if (spill) res[byte + i + 1] |= spill;
+            }
+        }
+    }
 }
-
-struct DevBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaError_t ensure(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-        size_t want = bytes + bytes / 4 + 256;
-        cudaError_t e = cudaMalloc(&p, want);
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    template <class T>
-    T* as() const { return static_cast<T*>(p); }
-    ~DevBuf() {
-        if (p) cudaFree(p);
-    }
-};
-struct PinBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaError_t ensure(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFreeHost(p);
-        p = nullptr;
-        cap = 0;
-        size_t want = bytes + bytes / 4 + 256;
-        cudaError_t e = cudaMallocHost(&p, want);
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    template <class T>
-    T* as() const { return static_cast<T*>(p); }
-    ~PinBuf() {
-        if (p) cudaFreeHost(p);
-    }
-};
-
-struct Overlay {  // host-written bits (headers, EOF codes) OR-ed into the packed payload
-    uint64_t bitPos;
-    mnenc::BitString bits;
-};
-
-}  // namespace
-
-struct mnenc_ctx {
-    int device = 0, K = 0, nBase = 0, numSMs = 0;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[8] = {};
-    bool quantSet = false;
-    float hQuant[3 * mnenc::kMaxK] = {};
-    // dictionary
-    DevBuf baseT, baseUm, detT, detRows, quant, baseUm16, detUm16, rows32;
-    float epsRel = 0.0f, epsRel16 = 0.0f, epsAbs16 = 0.0f;
-    int mpMode = 3;  // 3 = two-team fp16 tensor-core kernel (default); MNENC_MP=f16 / tf32 / fp32 select the earlier
-                     // kernels (single team / base-only TF32 pre-filter / exact full scan) for A/B validation
-    // image + symbols
-    DevBuf rgb, counts, pairs, mpScratch;
-    size_t lastW = 0, lastH = 0;
-    bool haveSymbols = false;
-    // back end
-    DevBuf tileCounts, totals, arena, dcTmp, flags, runIdx, startPos, outOff, rleArena, sums32, sums64, seqTable, hist, firstPos, maxSym,
-        entries, nEntries, entryCodes, codeTable, outWords;
-    uint32_t entryCap = 0;
-    bool histReady = false;
-    PinBuf hTotals, hSeqTable, hEntries, hNEntries, hEntryCodes, hCodeTable, hOut, hStats, hRgb;
-    std::unique_ptr<mnenc::HostPool> pool;  // code-table builds of one image run on these threads
-    // accounting
-    float ms[8] = {};
-    int launches = 0;
-    double mpFlops = 0;
-    uint64_t nSymbols = 0, nBits = 0;
-};
-
-namespace {
-
-using namespace mnenc;
 
 int ensureHistogram(mnenc_ctx* c) {
     if (c->histReady) return MNENC_OK;
@@ -128,7 +54,7 @@ int ensureHistogram(mnenc_ctx* c) {
     CU(c->maxSym.ensure(kMaxSeq * 4));
     CU(c->nEntries.ensure(4));
     CU(cudaMemsetAsync(c->hist.p, 0, bins * 4, c->stream));
-    CU(cudaMemsetAsync(c->firstPos.p, 0xFF, bins * 4, c->stream));
+    launchFillU32(c->firstPos.as<uint32_t>(), bins, kNoPos, c->stream);
     CU(cudaMemsetAsync(c->maxSym.p, 0, kMaxSeq * 4, c->stream));
     CU(cudaMemsetAsync(c->nEntries.p, 0, 4, c->stream));
     if (c->entryCap == 0) {
@@ -347,19 +273,7 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     uint8_t* res = static_cast<uint8_t*>(std::malloc(totalBytes ? totalBytes : 1));
     if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
     std::memcpy(res, c->hOut.p, totalBytes);
-    for (const Overlay& o : overlays) {
-        const uint64_t shift = o.bitPos & 7;
-        size_t byte = static_cast<size_t>(o.bitPos >> 3);
-        if (shift == 0) {
-            for (size_t i = 0; i < o.bits.bytes.size(); ++i) res[byte + i] |= o.bits.bytes[i];
-        } else {
-            for (size_t i = 0; i < o.bits.bytes.size(); ++i) {
-                res[byte + i] |= static_cast<uint8_t>(o.bits.bytes[i] >> shift);
-                const uint8_t spill = static_cast<uint8_t>(o.bits.bytes[i] << (8 - shift));
-                if (spill) res[byte + i + 1] |= spill;
-            }
-        }
-    }
+    mergeOverlays(res, overlays);
     *out = res;
     *outBytes = totalBytes;
     c->nSymbols = M;
@@ -442,7 +356,9 @@ int checkEncodeArgs(mnenc_ctx* c, const void* rgb, size_t w, size_t h, size_t st
     return MNENC_OK;
 }
 
-}  // namespace
+}  // namespace mnenc
+
+using namespace mnenc;
 
 // ================================================================================================
 // C ABI
@@ -691,7 +607,7 @@ int mnenc_debug_plan_sequence(const uint32_t* symbols, const uint32_t* freqs, co
 int mnenc_debug_stitch_runs(const uint32_t* records, int nranks, int n_streams, int rank, uint32_t* carry_in, uint32_t* extend_out) {
     if (!records || !carry_in || !extend_out || nranks < 1 || n_streams < 0 || rank < 0 || rank >= nranks)
         return fail(MNENC_ERR_ARG, "bad argument");
-    static_assert(sizeof(mnenc::StripeBoundary) == 5 * sizeof(uint32_t), "record layout");
+    static_assert(sizeof(mnenc::StripeBoundary) == 6 * sizeof(uint32_t), "record layout");
     mnenc::stitchRuns(reinterpret_cast<const mnenc::StripeBoundary*>(records), nranks, n_streams, rank, carry_in, extend_out);
     return MNENC_OK;
 }

@@ -1,0 +1,127 @@
+// Private definition of the encoder context, shared by the C-ABI translation units (mnenc_api.cu: one image on one
+// GPU; batch_api.cu: pipelined batches; stripe_api.cu: one image sharded by block columns over the ranks of a process
+// group). Not installed; the public boundary is include/mnenc.h.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cstdlib>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/mnenc.h"
+#include "backend_kernels.cuh"
+#include "host_pool.h"
+#include "mnenc_internal.h"
+
+namespace mnenc {
+
+int fail(int code, const std::string& msg);  // records the thread-local error text and returns `code`
+
+#define CU(expr)                                                                                                          \
+    do {                                                                                                                  \
+        cudaError_t e_ = (expr);                                                                                          \
+        if (e_ != cudaSuccess) return ::mnenc::fail(MNENC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+inline double nowMs() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+struct DevBuf {  // grow-only device buffer
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    template <class T>
+    T* as() const { return static_cast<T*>(p); }
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    ~DevBuf() {
+        if (p) cudaFree(p);
+    }
+};
+struct PinBuf {  // grow-only pinned host buffer
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMallocHost(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    template <class T>
+    T* as() const { return static_cast<T*>(p); }
+    PinBuf() = default;
+    PinBuf(const PinBuf&) = delete;
+    PinBuf& operator=(const PinBuf&) = delete;
+    ~PinBuf() {
+        if (p) cudaFreeHost(p);
+    }
+};
+
+struct Overlay {  // host-written bits (headers, EOF codes) OR-ed into the packed payload
+    uint64_t bitPos;
+    BitString bits;
+};
+// ORs the overlays into the byte stream `res` (MSB-first bit positions).
+void mergeOverlays(uint8_t* res, const std::vector<Overlay>& overlays);
+
+// State of one image sharded over ranks (stripe_api.cu), between the phases of the stripe protocol.
+struct StripeState;
+
+}  // namespace mnenc
+
+struct mnenc_ctx {
+    int device = 0, K = 0, nBase = 0, numSMs = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[8] = {};
+    bool quantSet = false;
+    float hQuant[3 * mnenc::kMaxK] = {};
+    // dictionary
+    mnenc::DevBuf baseT, baseUm, detT, detRows, quant, baseUm16, detUm16, rows32;
+    float epsRel = 0.0f, epsRel16 = 0.0f, epsAbs16 = 0.0f;
+    int mpMode = 3;  // 3 = two-team fp16 tensor-core kernel (default); MNENC_MP=f16 / tf32 / fp32 select the earlier
+                     // kernels (single team / base-only TF32 pre-filter / exact full scan) for A/B validation
+    // image + symbols
+    mnenc::DevBuf rgb, counts, pairs, mpScratch;
+    size_t lastW = 0, lastH = 0;
+    bool haveSymbols = false;
+    // back end
+    mnenc::DevBuf tileCounts, totals, arena, dcTmp, flags, runIdx, startPos, outOff, rleArena, sums32, sums64, seqTable, hist, firstPos,
+        maxSym, entries, nEntries, entryCodes, codeTable, outWords;
+    uint32_t entryCap = 0;
+    bool histReady = false;
+    mnenc::PinBuf hTotals, hSeqTable, hEntries, hNEntries, hEntryCodes, hCodeTable, hOut, hStats, hRgb;
+    std::unique_ptr<mnenc::HostPool> pool;  // code-table builds of one image run on these threads
+    // accounting
+    float ms[8] = {};
+    int launches = 0;
+    double mpFlops = 0;
+    uint64_t nSymbols = 0, nBits = 0;
+    // stripe protocol
+    std::unique_ptr<mnenc::StripeState, void (*)(mnenc::StripeState*)> stripe{nullptr, nullptr};
+};
+
+namespace mnenc {
+// Pieces of the single-GPU encode that the other translation units reuse (mnenc_api.cu).
+int ensureHistogram(mnenc_ctx* c);
+int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride);
+void finishMpAccounting(mnenc_ctx* c);
+int checkEncodeArgs(mnenc_ctx* c, const void* rgb, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes);
+}  // namespace mnenc

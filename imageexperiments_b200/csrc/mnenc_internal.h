@@ -106,12 +106,21 @@ struct StripeBoundary {   // one per (rank, symbol stream), all-gathered
     uint32_t n;           // entries of the stream held by the rank
     uint32_t first, firstRun;  // first value and length of the run it starts (n if the slice is one run)
     uint32_t last, lastRun;    // last value and length of the run it ends
+    uint32_t interior;         // RLE symbols of the runs strictly between the first and the last run of the slice
 };
 // For `rank`: carryIn[s] = length of the equal-valued run that ends right before its slice of stream s,
 // extendOut[s] = length by which its last run continues on later ranks.
 void stitchRuns(const StripeBoundary* rec, int nranks, int nStreams, int rank, uint32_t* carryIn, uint32_t* extendOut);
 // RLE symbols a slice emits for `len` elements of a run that has `carry` elements before it and `total` overall.
 uint32_t rleChunkedSize(uint32_t carry, uint32_t len, uint64_t total);
+
+struct StripePlan {
+    int nranks = 0, nStreams = 0;
+    std::vector<uint32_t> emitted, carry, ext;  // [nranks][nStreams]: RLE symbols emitted by a rank; its run stitching
+    std::vector<uint64_t> rawLen, rleLen;       // [nStreams] totals over the ranks
+    std::vector<uint8_t> useRle;                // [nStreams] decision on the WHOLE stream
+};
+void planStripes(const StripeBoundary* rec, int nranks, int nStreams, StripePlan& plan);
 
 // compressed::createQuantizationTables, float overload (CompressedImage.cpp:168-210).
 int quantTables(int K, int blockSize, double bpp, float* out3K);

@@ -50,3 +50,44 @@ uint32_t rleChunkedSize(uint32_t carry, uint32_t len, uint64_t total) {
 }
 
 }  // namespace mnenc
+
+namespace mnenc {
+
+// Everything every rank derives — identically — from the all-gathered boundary records of one image: how many RLE
+// symbols each rank emits for each stream, the RLE-or-raw decision of compressed::writeCompressed
+// (CompressedImage.cpp:508-516: RLE iff rle.size() + 4 < stream.size(), on the WHOLE stream), and the lengths.
+void planStripes(const StripeBoundary* rec, int nranks, int nStreams, StripePlan& plan) {
+    plan.nranks = nranks;
+    plan.nStreams = nStreams;
+    plan.emitted.assign(static_cast<size_t>(nranks) * nStreams, 0);
+    plan.carry.assign(static_cast<size_t>(nranks) * nStreams, 0);
+    plan.ext.assign(static_cast<size_t>(nranks) * nStreams, 0);
+    plan.rawLen.assign(nStreams, 0);
+    plan.rleLen.assign(nStreams, 0);
+    plan.useRle.assign(nStreams, 0);
+    std::vector<uint32_t> carry(nStreams), ext(nStreams);
+    for (int q = 0; q < nranks; ++q) {
+        stitchRuns(rec, nranks, nStreams, q, carry.data(), ext.data());
+        for (int s = 0; s < nStreams; ++s) {
+            const StripeBoundary& r = rec[static_cast<size_t>(q) * nStreams + s];
+            uint32_t e = 0;
+            if (r.n) {
+                if (r.firstRun >= r.n) {  // the slice is one run
+                    e = rleChunkedSize(carry[s], r.n, static_cast<uint64_t>(carry[s]) + r.n + ext[s]);
+                } else {
+                    e = rleChunkedSize(carry[s], r.firstRun, static_cast<uint64_t>(carry[s]) + r.firstRun) + r.interior +
+                        rleChunkedSize(0, r.lastRun, static_cast<uint64_t>(r.lastRun) + ext[s]);
+                }
+            }
+            const size_t i = static_cast<size_t>(q) * nStreams + s;
+            plan.emitted[i] = e;
+            plan.carry[i] = carry[s];
+            plan.ext[i] = ext[s];
+            plan.rawLen[s] += r.n;
+            plan.rleLen[s] += e;
+        }
+    }
+    for (int s = 0; s < nStreams; ++s) plan.useRle[s] = plan.rleLen[s] + 4 < plan.rawLen[s] ? 1 : 0;
+}
+
+}  // namespace mnenc

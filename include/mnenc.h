@@ -105,15 +105,51 @@ int mnenc_debug_plan_sequence(const uint32_t* symbols, const uint32_t* freqs, co
                               uint8_t* header_bytes, size_t header_cap, uint64_t* header_bits, uint64_t* payload_bits);
 
 /*
- * Host-logic test hook of the multi-GPU stripe path (used by the CPU-only world_size-2 gloo tests): run stitching
- * of huffman::runLengthEncode (Huffman.cpp:246-279) across ranks. records = [nranks][n_streams][5] u32
- * {n, first value, first run length, last value, last run length} as all-gathered by the ranks; outputs for `rank`:
- * carry_in[s] / extend_out[s] = elements of its first / last run that live on earlier / later ranks.
- * mnenc_debug_rle_chunk_size = RLE symbols a rank emits for `len` elements of a run with `carry` elements before them
- * and `total` elements overall (chunks of 32 769 counted from the run's global start).
+ * Stripe protocol: ONE image sharded by block columns over `nranks` contexts (one process per GPU; SURVEY.md §8e,
+ * BASELINE.json configs[3]). Replaces compressed::encodeImageFast (CompressedImage.cpp:578-633) for images too large or
+ * too urgent for one GPU. The reference walks blocks column-major (CompressedImage.cpp:592-594), so the rank holding
+ * block columns [bx0, bx1) owns the matching contiguous slice of every symbol stream. Matching pursuit needs no
+ * exchange; the entropy back end (compressed::writeCompressed, CompressedImage.cpp:462-519) needs the five exchanges
+ * below, which the CALLER performs (torch.distributed / NCCL in imageexperiments_b200/stripes.py, or any transport):
+ *
+ *   mnenc_stripe_begin      -> rec1[3K+3]            all-gather  -> all_rec1[nranks][3K+3]
+ *   mnenc_stripe_rle        -> rec2[6K][6]           all-gather  -> all_rec2[nranks][6K][6]
+ *   mnenc_stripe_histogram  -> device buffers        all-reduce in place over the ranks (as int32): SUM on hist,
+ *                                                    MIN on first_pos, MAX on max_sym
+ *   mnenc_stripe_plan       -> seq_bits[6K+1]        all-gather  -> all_seq_bits[nranks][6K+1]   (offset scan)
+ *   mnenc_stripe_pack       -> device words          reduce SUM to rank 0 in place (as int32; the ranks' bits are
+ *                                                    disjoint, so the sum concatenates the per-GPU bitstream segments)
+ *   mnenc_stripe_finish     -> rank 0: the complete `.mn` stream (mnenc_free it); other ranks: *out = NULL
+ *
+ * rgb_stripe points at pixel (x = 8*bx0, y = 0): host memory (on_device = 0, copied inside the call) or memory of the
+ * context's GPU (on_device = 1). bx0 == bx1 (a rank without blocks) is allowed. Calls out of order return
+ * MNENC_ERR_STATE. The returned device pointers stay valid until the next call on the context; the context's stream is
+ * idle when each call returns, so the caller's collectives need no further ordering.
+ */
+int mnenc_stripe_begin(mnenc_t* ctx, const uint8_t* rgb_stripe, int on_device, size_t width, size_t height, size_t row_stride_bytes,
+                       int rank, int nranks, uint32_t bx0, uint32_t bx1, uint32_t* rec1);
+int mnenc_stripe_rle(mnenc_t* ctx, const uint32_t* all_rec1, uint32_t* rec2);
+int mnenc_stripe_histogram(mnenc_t* ctx, const uint32_t* all_rec2, void** hist_dev, void** first_pos_dev, size_t* hist_elems,
+                           void** max_sym_dev, size_t* max_sym_elems);
+int mnenc_stripe_plan(mnenc_t* ctx, uint64_t* seq_bits);
+int mnenc_stripe_pack(mnenc_t* ctx, const uint64_t* all_seq_bits, void** out_dev, size_t* out_words, size_t* out_bytes);
+int mnenc_stripe_finish(mnenc_t* ctx, uint8_t** out, size_t* out_bytes);
+
+/*
+ * Host-logic test hooks of the stripe path (used by the CPU-only world_size-2/3 gloo tests): run stitching of
+ * huffman::runLengthEncode (Huffman.cpp:246-279) across ranks. records = [nranks][n_streams][6] u32
+ * {n, first value, first run length, last value, last run length, RLE symbols of the interior runs} as all-gathered
+ * by the ranks (rec2 above). mnenc_debug_stitch_runs, for `rank`: carry_in[s] / extend_out[s] = elements of its
+ * first / last run that live on earlier / later ranks. mnenc_debug_rle_chunk_size = RLE symbols a rank emits for `len`
+ * elements of a run with `carry` elements before them and `total` elements overall (chunks of 32 769 counted from the
+ * run's global start). mnenc_debug_plan_stripes = what every rank derives from the records: emitted[nranks][n_streams]
+ * RLE symbols per rank, and per stream the whole-stream sizes and the RLE-or-raw decision of
+ * compressed::writeCompressed (CompressedImage.cpp:508-516).
  */
 int mnenc_debug_stitch_runs(const uint32_t* records, int nranks, int n_streams, int rank, uint32_t* carry_in, uint32_t* extend_out);
 uint32_t mnenc_debug_rle_chunk_size(uint32_t carry, uint32_t len, uint64_t total);
+int mnenc_debug_plan_stripes(const uint32_t* records, int nranks, int n_streams, uint32_t* emitted, uint8_t* use_rle, uint64_t* raw_len,
+                             uint64_t* rle_len);
 
 #ifdef __cplusplus
 }

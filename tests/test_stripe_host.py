@@ -34,13 +34,22 @@ def cuts(n, world, rng):
     return [0] + [int(x) for x in c] + [n]
 
 
+def rle_size(n):
+    """RLE symbols of one run of n elements that lies wholly inside a slice."""
+    full, rem = divmod(n, CHUNK)
+    return 3 * full + (0 if rem == 0 else 1 if rem == 1 else 3)
+
+
 def boundary(v):
+    """The record a rank publishes per stream slice (mnenc_stripe_rle's rec2 row)."""
     if v.size == 0:
-        return [0, 0, 0, 0, 0]
+        return [0, 0, 0, 0, 0, 0]
     ch = np.nonzero(v[1:] != v[:-1])[0]
     first_run = int(ch[0] + 1) if ch.size else v.size
     last_run = int(v.size - (ch[-1] + 1)) if ch.size else v.size
-    return [v.size, int(v[0]), first_run, int(v[-1]), last_run]
+    starts = np.concatenate([[0], ch + 1, [v.size]])
+    interior = sum(rle_size(int(starts[i + 1] - starts[i])) for i in range(1, len(starts) - 2))
+    return [v.size, int(v[0]), first_run, int(v[-1]), last_run, interior]
 
 
 def rle_slice(v, carry, ext):
@@ -90,10 +99,18 @@ def worker(rank, world, port, q):
         if v.size and (v == v[0]).all():
             want = L.mnenc_debug_rle_chunk_size(int(carry[i]), int(v.size), int(carry[i]) + int(v.size) + int(ext[i]))
             assert want == len(mine[i]), (i, want, len(mine[i]))
+    # what every rank derives from the records alone: per-rank emitted sizes, whole-stream sizes, RLE-or-raw decision
+    emitted = np.zeros((world, ns), np.uint32)
+    use_rle = np.zeros(ns, np.uint8)
+    raw_len = np.zeros(ns, np.uint64)
+    rle_len = np.zeros(ns, np.uint64)
+    assert L.mnenc_debug_plan_stripes(records.ctypes.data, world, ns, emitted.ctypes.data, use_rle.ctypes.data, raw_len.ctypes.data,
+                                      rle_len.ctypes.data) == 0
+    assert [int(x) for x in emitted[rank]] == [len(m) for m in mine]
     gathered = [None] * world
     dist.all_gather_object(gathered, mine)
     if rank == 0:
-        q.put([sum((g[i] for g in gathered), []) for i in range(ns)])
+        q.put(([sum((g[i] for g in gathered), []) for i in range(ns)], use_rle.tolist(), raw_len.tolist(), rle_len.tolist()))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -109,10 +126,12 @@ def test_rle_stitching_matches_oracle(world, oraclelib):
     procs = [ctx.Process(target=worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    got = q.get(timeout=120)
+    got, use_rle, raw_len, rle_len = q.get(timeout=120)
     for p in procs:
         p.join(60)
         assert p.exitcode == 0
-    for v, g in zip(make_streams(), got):
+    for i, (v, g) in enumerate(zip(make_streams(), got)):
         want = oraclelib.rle(v)
         assert np.array_equal(np.asarray(g, np.uint16), want), (v.size, len(g), want.size)
+        assert raw_len[i] == v.size and rle_len[i] == want.size
+        assert bool(use_rle[i]) == (want.size + 4 < v.size)   # CompressedImage.cpp:508-516

@@ -1,0 +1,56 @@
+"""torchrun script: the stripe protocol over NCCL, one process per GPU, checked against the single-GPU encode of rank 0.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/stripe_check.py [W H]
+"""
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+
+    import imageexperiments_b200 as mn
+    from imageexperiments_b200.synth import synthetic_rgb
+
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    ctx = mn.createCompressionContextFast(32, 8, 3.5, device=local)
+    comm = mn.TorchComm()
+    sizes = [(512, 512), (1023, 77), (8, 8), (4928, 3264)]
+    if len(sys.argv) >= 3:
+        sizes = [(int(sys.argv[1]), int(sys.argv[2]))]
+    for (w, h) in sizes:
+        img = synthetic_rgb(w, h, 12345) if w * h <= 4928 * 3264 else np.tile(synthetic_rgb(2048, 2048, 12345), ((h + 2047) // 2048, (w + 2047) // 2048, 1))[:h, :w]
+        got = mn.encodeImageStripes(img, ctx, comm)
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        got = mn.encodeImageStripes(img, ctx, comm)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if rank == 0:
+            t1 = time.perf_counter()
+            want = mn.encodeImageFast(img, ctx)
+            d1 = time.perf_counter() - t1
+            assert got == want, f"{w}x{h}: stripe-sharded stream differs from the single-GPU stream"
+            print(f"{w}x{h}: {len(got)} bytes identical over {world} ranks; striped {dt * 1e3:.2f} ms, single GPU {d1 * 1e3:.2f} ms", flush=True)
+        else:
+            assert got is None
+        dist.barrier()
+    if rank == 0:
+        print("stripe_check OK", flush=True)
+    ctx.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
