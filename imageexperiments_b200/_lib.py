@@ -16,7 +16,7 @@ _vp, _sz = C.c_void_p, C.c_size_t
 #: every symbol include/mnenc.h declares (checked by tests/test_abi.py)
 EXPORTS = (
     "mnenc_last_error", "mnenc_create", "mnenc_destroy", "mnenc_quant_tables", "mnenc_set_quant", "mnenc_encode_rgb8",
-    "mnenc_encode_rgb8_device", "mnenc_free", "mnenc_get_symbols", "mnenc_pack_symbols", "mnenc_last_timing", "mnenc_last_work",
+    "mnenc_encode_rgb8_device", "mnenc_encode_batch_rgb8", "mnenc_free", "mnenc_get_symbols", "mnenc_pack_symbols", "mnenc_last_timing", "mnenc_last_work",
     "mnenc_debug_plan_sequence", "mnenc_debug_stitch_runs", "mnenc_debug_rle_chunk_size", "mnenc_debug_plan_stripes",
     "mnenc_stripe_begin", "mnenc_stripe_rle", "mnenc_stripe_histogram", "mnenc_stripe_plan", "mnenc_stripe_pack", "mnenc_stripe_finish",
 )
@@ -47,6 +47,7 @@ def load() -> C.CDLL:
     L.mnenc_set_quant.argtypes = [_vp, _vp]
     L.mnenc_encode_rgb8.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp, _vp]
     L.mnenc_encode_rgb8_device.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp, _vp]
+    L.mnenc_encode_batch_rgb8.argtypes = [_vp, _sz, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp]
     L.mnenc_free.argtypes = [_vp]
     L.mnenc_free.restype = None
     L.mnenc_get_symbols.argtypes = [_vp, _vp, _vp]

@@ -1,0 +1,97 @@
+// Batch mode (BASELINE.json configs[4]: many independent frames per GPU, throughput mode; SURVEY.md §8e "C5"): the
+// reference encodes images one after the other (Compression.cpp:117-123 in a loop); every image is an independent `.mn`
+// file, so a batch is pipelined over LANES — contexts with their own stream, device buffers, pinned buffers and host
+// threads that share one dictionary in HBM. While one lane waits for its host stage (stream sizes, the 193 code tables,
+// D2H + header merge) or for its pixels to arrive, another lane's matching-pursuit kernel owns the SMs, and the copy
+// engines move the next image's pixels and the previous image's stream. Each image goes through exactly the
+// single-image path (mnenc_encode_rgb8*), so every stream is byte-identical to the one-at-a-time result.
+#include <atomic>
+#include <thread>
+
+#include "mnenc_ctx.cuh"
+
+using namespace mnenc;
+
+namespace {
+
+int makeLane(mnenc_ctx* parent, int threads, mnenc_ctx** out) {
+    mnenc_ctx* l = new mnenc_ctx;
+    l->device = parent->device, l->K = parent->K, l->nBase = parent->nBase, l->numSMs = parent->numSMs;
+    l->epsRel = parent->epsRel, l->epsRel16 = parent->epsRel16, l->epsAbs16 = parent->epsAbs16, l->mpMode = parent->mpMode;
+    l->baseT.alias(parent->baseT), l->baseUm.alias(parent->baseUm), l->detT.alias(parent->detT), l->detRows.alias(parent->detRows);
+    l->baseUm16.alias(parent->baseUm16), l->detUm16.alias(parent->detUm16), l->rows32.alias(parent->rows32);
+    l->quant.alias(parent->quant);
+    l->hostThreads = threads;
+    l->pool = std::make_unique<HostPool>(threads);
+    *out = l;
+    CU(cudaStreamCreateWithFlags(&l->stream, cudaStreamNonBlocking));
+    for (auto& e : l->ev) CU(cudaEventCreate(&e));
+    return MNENC_OK;
+}
+
+}  // namespace
+
+extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_t* const* rgb, int on_device, const size_t* width,
+                                       const size_t* height, const size_t* row_stride_bytes, uint8_t** out, size_t* out_bytes) {
+    if (!c || (n_images && (!rgb || !width || !height || !row_stride_bytes || !out || !out_bytes))) return fail(MNENC_ERR_ARG, "null argument");
+    if (!c->quantSet) return fail(MNENC_ERR_STATE, "mnenc_set_quant has not been called");
+    for (size_t i = 0; i < n_images; ++i) out[i] = nullptr, out_bytes[i] = 0;
+    if (n_images == 0) return MNENC_OK;
+    CU(cudaSetDevice(c->device));
+    int want = 4;
+    if (const char* e = std::getenv("MNENC_LANES")) want = std::atoi(e);
+    want = static_cast<int>(std::min<size_t>(static_cast<size_t>(std::clamp(want, 1, 8)), n_images));
+    while (static_cast<int>(c->lanes.size()) + 1 < want) {
+        mnenc_ctx* lane = nullptr;
+        const int rc = makeLane(c, std::max(1, c->hostThreads / 2), &lane);
+        if (lane) c->lanes.push_back(lane);
+        if (rc) return rc;
+    }
+    std::vector<mnenc_ctx*> lanes{c};
+    for (int i = 0; i + 1 < want; ++i) {
+        mnenc_ctx* l = c->lanes[i];
+        std::memcpy(l->hQuant, c->hQuant, sizeof(c->hQuant));  // the device table is shared; the header needs the host copy
+        l->quantSet = true;
+        lanes.push_back(l);
+    }
+    std::atomic<size_t> next{0};
+    std::atomic<int> firstError{MNENC_OK};
+    int launches[8] = {};
+    double flops[8] = {};
+    float mpMs[8] = {};
+    auto work = [&](int li) {
+        mnenc_ctx* l = lanes[li];
+        cudaSetDevice(l->device);
+        while (firstError.load(std::memory_order_relaxed) == MNENC_OK) {
+            const size_t i = next.fetch_add(1);
+            if (i >= n_images) break;
+            const int rc = on_device ? mnenc_encode_rgb8_device(l, rgb[i], width[i], height[i], row_stride_bytes[i], &out[i], &out_bytes[i])
+                                     : mnenc_encode_rgb8(l, rgb[i], width[i], height[i], row_stride_bytes[i], &out[i], &out_bytes[i]);
+            if (rc != MNENC_OK) {
+                int expected = MNENC_OK;
+                if (firstError.compare_exchange_strong(expected, rc)) c->laneError = "image " + std::to_string(i) + ": " + mnenc_last_error();
+                break;
+            }
+            launches[li] += l->launches;
+            flops[li] += l->mpFlops;
+            mpMs[li] += l->ms[1];
+        }
+    };
+    const double t0 = nowMs();
+    std::vector<std::thread> threads;
+    for (int li = 1; li < want; ++li) threads.emplace_back(work, li);
+    work(0);
+    for (auto& t : threads) t.join();
+    if (const int rc = firstError.load()) {
+        for (size_t i = 0; i < n_images; ++i) {
+            std::free(out[i]);
+            out[i] = nullptr, out_bytes[i] = 0;
+        }
+        return fail(rc, c->laneError);
+    }
+    // accounting of the whole batch on the parent context (mnenc_last_timing / mnenc_last_work)
+    c->launches = 0, c->mpFlops = 0, c->ms[1] = 0;
+    for (int li = 0; li < want; ++li) c->launches += launches[li], c->mpFlops += flops[li], c->ms[1] += mpMs[li];
+    c->ms[7] = static_cast<float>(nowMs() - t0);
+    return MNENC_OK;
+}

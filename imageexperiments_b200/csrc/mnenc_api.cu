@@ -272,7 +272,7 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     // ---- merge host-written bits ----
     uint8_t* res = static_cast<uint8_t*>(std::malloc(totalBytes ? totalBytes : 1));
     if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
-    std::memcpy(res, c->hOut.p, totalBytes);
+    parallelCopy(c->pool.get(), res, c->hOut.as<uint8_t>(), totalBytes);
     mergeOverlays(res, overlays);
     *out = res;
     *outBytes = totalBytes;
@@ -450,8 +450,11 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
         int threads = static_cast<int>(std::thread::hardware_concurrency());
         cpu_set_t set;
         if (sched_getaffinity(0, sizeof(set), &set) == 0) threads = CPU_COUNT(&set);
+        if (const char* lw = std::getenv("LOCAL_WORLD_SIZE"))  // one process per GPU (torchrun): share the host cores between the ranks
+            if (std::atoi(lw) > 1) threads = std::max(1, threads / std::atoi(lw));
         if (const char* t = std::getenv("MNENC_HOST_THREADS")) threads = std::atoi(t);
-        c->pool = std::make_unique<HostPool>(std::clamp(threads, 1, 16));
+        c->hostThreads = std::clamp(threads, 1, 16);
+        c->pool = std::make_unique<HostPool>(c->hostThreads);
     }
     // detail groups transposed per group: detT[((ch*nBase + atom)*64 + j)*64 + row], rows padded with zeros
     std::vector<uint8_t> rows(kRowsPad, 0);
@@ -479,6 +482,8 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
 
 void mnenc_destroy(mnenc_t* c) {
     if (!c) return;
+    for (mnenc_ctx* lane : c->lanes) mnenc_destroy(lane);
+    c->lanes.clear();
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (auto& e : c->ev)

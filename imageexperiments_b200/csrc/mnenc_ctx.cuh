@@ -5,8 +5,10 @@
 
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cstdlib>
+#include <cstring>
 #include <memory>
 #include <string>
 #include <vector>
@@ -35,6 +37,7 @@ struct DevBuf {  // grow-only device buffer
     size_t cap = 0;
     cudaError_t ensure(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
+        if (!owned) return cudaErrorInvalidValue;
         if (p) cudaFree(p);
         p = nullptr;
         cap = 0;
@@ -45,11 +48,16 @@ struct DevBuf {  // grow-only device buffer
     }
     template <class T>
     T* as() const { return static_cast<T*>(p); }
+    void alias(const DevBuf& other) {  // non-owning view of another context's buffer (lanes share the dictionary)
+        if (p && owned) cudaFree(p);
+        p = other.p, cap = other.cap, owned = false;
+    }
+    bool owned = true;
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
     ~DevBuf() {
-        if (p) cudaFree(p);
+        if (p && owned) cudaFree(p);
     }
 };
 struct PinBuf {  // grow-only pinned host buffer
@@ -81,6 +89,21 @@ struct Overlay {  // host-written bits (headers, EOF codes) OR-ed into the packe
 };
 // ORs the overlays into the byte stream `res` (MSB-first bit positions).
 void mergeOverlays(uint8_t* res, const std::vector<Overlay>& overlays);
+
+// Copies `n` bytes into freshly malloc'ed (not yet faulted-in) memory on the pool's threads: for a stream of tens of MB the
+// page faults of a single-threaded memcpy cost more than the D2H copy itself.
+inline void parallelCopy(HostPool* pool, uint8_t* dst, const uint8_t* src, size_t n) {
+    const size_t kChunk = size_t(1) << 20;
+    if (!pool || pool->size() == 1 || n <= 2 * kChunk) {
+        std::memcpy(dst, src, n);
+        return;
+    }
+    const int chunks = static_cast<int>((n + kChunk - 1) / kChunk);
+    pool->parallelFor(chunks, [&](int i) {
+        const size_t o = static_cast<size_t>(i) * kChunk;
+        std::memcpy(dst + o, src + o, std::min(kChunk, n - o));
+    });
+}
 
 // State of one image sharded over ranks (stripe_api.cu), between the phases of the stripe protocol.
 struct StripeState;
@@ -116,6 +139,10 @@ struct mnenc_ctx {
     uint64_t nSymbols = 0, nBits = 0;
     // stripe protocol
     std::unique_ptr<mnenc::StripeState, void (*)(mnenc::StripeState*)> stripe{nullptr, nullptr};
+    // batch mode (batch_api.cu): extra lanes = contexts with their own stream and buffers that alias this dictionary
+    std::vector<mnenc_ctx*> lanes;
+    int hostThreads = 1;
+    std::string laneError;
 };
 
 namespace mnenc {

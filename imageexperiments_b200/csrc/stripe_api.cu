@@ -466,7 +466,7 @@ int mnenc_stripe_finish(mnenc_t* c, uint8_t** out, size_t* out_bytes) {
         CU(cudaStreamSynchronize(c->stream));
         uint8_t* res = static_cast<uint8_t*>(std::malloc(s->totalBytes ? s->totalBytes : 1));
         if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
-        std::memcpy(res, c->hOut.p, s->totalBytes);
+        parallelCopy(c->pool.get(), res, c->hOut.as<uint8_t>(), s->totalBytes);
         mergeOverlays(res, s->overlays);
         *out = res;
         *out_bytes = s->totalBytes;

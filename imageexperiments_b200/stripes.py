@@ -23,7 +23,7 @@ from typing import List, Optional, Tuple
 import numpy as np
 
 from . import _lib
-from .compressed import CompressionContextFast, _take
+from .compressed import CompressionContextFast, MnBuffer, _take
 
 _vp = C.c_void_p
 
@@ -134,12 +134,24 @@ class ThreadComm:
         self._device_op(ptr, n, device, fn)
 
 
-def encodeImageStripes(imgIn, context: CompressionContextFast, comm, width: Optional[int] = None) -> Optional[bytes]:
+def encodeImageStripes(imgIn, context: CompressionContextFast, comm, width: Optional[int] = None,
+                       timings: Optional[dict] = None, zero_copy: bool = False):
     """compressed::encodeImageFast (CompressedImage.cpp:578-633) of ONE image over all ranks of ``comm``.
 
     ``imgIn``: the full HxWx3 uint8 image in host memory (numpy array or CPU torch tensor; every rank copies only its own
     block columns to its GPU), or — with ``width`` = full image width — a CUDA uint8 tensor [H, stripe width, 3] holding
-    just this rank's stripe (columns 8*bx0 .. min(8*bx1, width)). Returns the `.mn` bytes on rank 0, None elsewhere."""
+    just this rank's stripe (columns 8*bx0 .. min(8*bx1, width)). Returns the `.mn` bytes on rank 0, None elsewhere.
+    ``zero_copy``: return an MnBuffer over the library's own memory instead of copying it into ``bytes``.
+    ``timings`` (optional dict) accumulates host wall seconds per phase / exchange of the protocol."""
+    import time
+    tl = [time.perf_counter()]
+
+    def lap(name):
+        if timings is not None:
+            t = time.perf_counter()
+            timings[name] = timings.get(name, 0.0) + t - tl[0]
+            tl[0] = t
+
     L = _lib.load()
     K = context.K
     rank, world, dev = comm.rank, comm.world, context.device
@@ -170,24 +182,37 @@ def encodeImageStripes(imgIn, context: CompressionContextFast, comm, width: Opti
 
     rec1 = np.zeros(3 * K + 3, np.uint32)
     _lib.check(L.mnenc_stripe_begin(context._h, _vp(ptr), int(on_device), w, h, stride, rank, world, bx0, bx1, rec1.ctypes.data_as(_vp)))
+    lap("begin")
     all1 = comm.all_gather(rec1, dev)
+    lap("x_gather1")
     rec2 = np.zeros((6 * K, 6), np.uint32)
     _lib.check(L.mnenc_stripe_rle(context._h, all1.ctypes.data_as(_vp), rec2.ctypes.data_as(_vp)))
+    lap("rle")
     all2 = comm.all_gather(rec2, dev)
+    lap("x_gather2")
     hist, first, msym, nh, nm = _vp(), _vp(), _vp(), C.c_size_t(), C.c_size_t()
     _lib.check(L.mnenc_stripe_histogram(context._h, all2.ctypes.data_as(_vp), C.byref(hist), C.byref(first), C.byref(nh), C.byref(msym),
                                         C.byref(nm)))
+    lap("histogram")
     if world > 1:
         comm.all_reduce_device(msym.value, nm.value, "max", dev)
         comm.all_reduce_device(hist.value, nh.value, "sum", dev)
         comm.all_reduce_device(first.value, nh.value, "min", dev)
+    lap("x_allreduce")
     bits = np.zeros(6 * K + 1, np.uint64)
     _lib.check(L.mnenc_stripe_plan(context._h, bits.ctypes.data_as(_vp)))
+    lap("plan")
     allb = comm.all_gather(bits, dev)
+    lap("x_gather3")
     outp, nw, nb = _vp(), C.c_size_t(), C.c_size_t()
     _lib.check(L.mnenc_stripe_pack(context._h, allb.ctypes.data_as(_vp), C.byref(outp), C.byref(nw), C.byref(nb)))
+    lap("pack")
     if world > 1:
         comm.reduce_device(outp.value, nw.value, dev)
+    lap("x_reduce")
     out, n = _vp(), C.c_size_t()
     _lib.check(L.mnenc_stripe_finish(context._h, C.byref(out), C.byref(n)))
-    return _take(out, n.value) if rank == 0 else None
+    lap("finish")
+    if rank != 0:
+        return None
+    return MnBuffer(out, n.value) if zero_copy else _take(out, n.value)

@@ -68,6 +68,18 @@ int mnenc_encode_rgb8_device(mnenc_t* ctx, const uint8_t* rgb_dev, size_t width,
 void mnenc_free(uint8_t* p);
 
 /*
+ * Batch / throughput mode (BASELINE.json configs[4]): n_images independent images -> n_images independent `.mn` streams,
+ * what a caller of the reference gets from encodeImageFast in a loop (Compression.cpp:117-123), each stream byte-identical
+ * to the one-at-a-time result. Inside, the images are pipelined over lanes (own stream + buffers, one shared dictionary in
+ * HBM; MNENC_LANES, default 4) so that host stages, H2D and D2H of one image overlap the matching pursuit of another.
+ * rgb[i]: host pointers (on_device = 0) or pointers into the context's GPU (on_device = 1); out[i] from mnenc_free().
+ * On error every out[i] is NULL. mnenc_last_timing/work afterwards describe the whole batch (ms[1] = summed kernel time,
+ * ms[7] = wall time of the batch).
+ */
+int mnenc_encode_batch_rgb8(mnenc_t* ctx, size_t n_images, const uint8_t* const* rgb, int on_device, const size_t* width,
+                            const size_t* height, const size_t* row_stride_bytes, uint8_t** out, size_t* out_bytes);
+
+/*
  * Debug taps for parity tests (the reference has no equivalent call; they expose the intermediates of
  * encodeImageFast, CompressedImage.cpp:588-631):
  *   counts[3*blk + ch]                         = return value of CalcMPDynamicFast (MatchingPursuit.cpp:76)

@@ -157,3 +157,26 @@ def test_psnr_delta_vs_reference_encoder(ctx, reflib):
     assert abs(p_ref - p_got) <= 0.01
     assert got == ref_bytes
     reflib.destroy(rctx)
+
+
+def test_batch_equals_one_at_a_time(ctx, oracle_ctx_factory):
+    """BASELINE.json configs[4] (throughput mode): a batch of independent frames through the pipelined lanes gives, per
+    frame, the very stream of encodeImageFast == the oracle's; mixed sizes, host and device inputs."""
+    import torch
+    set_quality(ctx, 3.5)
+    oc = oracle_ctx_factory(ctx.Quant)
+    frames = [synthetic_rgb(w, h, 100 + i) for i, (w, h) in enumerate([(320, 240), (200, 136), (8, 8), (512, 512), (320, 240), (1023, 77), (64, 64)])]
+    want = [oc.encode(f) for f in frames]
+    assert mn.encodeImageBatch(frames, ctx) == want
+    assert mn.encodeImageBatch([torch.from_numpy(f).cuda() for f in frames], ctx) == want
+    assert mn.encodeImageBatch(frames[:1], ctx) == want[:1]
+    assert mn.encodeImageBatch([], ctx) == []
+    ms, launches = ctx.last_timing()
+    assert launches > 0
+    # the context still works one image at a time, and a new quality reaches every lane
+    set_quality(ctx, 8.0)
+    oc8 = oracle_ctx_factory(ctx.Quant)
+    assert mn.encodeImageBatch(frames[:4], ctx) == [oc8.encode(f) for f in frames[:4]]
+    assert mn.encodeImageFast(frames[0], ctx) == oc8.encode(frames[0])
+    oc.close()
+    oc8.close()
