@@ -55,7 +55,10 @@ struct TeamSmem {
     unsigned long long accFull[kTAccs], accEmpty[kTAccs];
     alignas(16) uint32_t approxMax[kSlots];                  // max |p~| per slot (float bits)
     alignas(16) float twoEps[kSlots];
-    uint32_t nItems[2], nDc[2], nActive[2];
+    uint32_t nItems[2], nActive[2];
+    uint16_t dcFirst[2][kSlots];                             // dictionary index of row 0 of the slot's FIRST group of atom 0 / atom nBase-1
+                                                             // (0xFFFF: none). A repeated group has identical rows, so on the exact
+                                                             // ties it produces the lower index - the first occurrence - always wins.
     uint32_t nCand;
     uint32_t fifoHead, fifoTail;
     uint32_t fifo[kFifo];
@@ -111,7 +114,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             mbarInit(&X.mbarDcLoad, 1);
             for (int i = 0; i < kTStages; ++i) mbarInit(&X.full[i], 1), mbarInit(&X.empty[i], 1);
             for (int i = 0; i < kTAccs; ++i) mbarInit(&X.accFull[i], 1), mbarInit(&X.accEmpty[i], 4);
-            X.nItems[0] = X.nItems[1] = X.nDc[0] = X.nDc[1] = X.nActive[0] = X.nActive[1] = 0;
+            X.nItems[0] = X.nItems[1] = X.nActive[0] = X.nActive[1] = 0;
             X.nCand = 0;
             X.fifoHead = X.fifoTail = 0;
         }
@@ -128,6 +131,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
         const int sl = i % kSlots;
         X.bc[sl] = -1, X.reps[sl] = 0, X.prev[sl] = 0, X.ngroups[sl] = 0, X.height[sl] = p.nBase;
         X.best[sl] = 0ULL, X.approxMax[sl] = 0u, X.twoEps[sl] = 0.0f, X.zeroRes[sl] = 1;
+        X.dcFirst[0][sl] = X.dcFirst[1][sl] = 0xFFFFu;
     }
     fenceBefore();
     __syncthreads();
@@ -222,6 +226,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             T.approxMax[slot] = 0u;
             T.twoEps[slot] = epsOf(ss);
             T.zeroRes[slot] = nonZero ? 0 : 1;
+            T.dcFirst[0][slot] = T.dcFirst[1][slot] = 0xFFFFu;
         }
     };
     auto idleSlot = [&]() {
@@ -235,6 +240,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             T.approxMax[slot] = 0u;
             T.twoEps[slot] = 0.0f;
             T.zeroRes[slot] = 1;
+            T.dcFirst[0][slot] = T.dcFirst[1][slot] = 0xFFFFu;
         }
     };
     // next block index of this team's channel (shared-memory FIFO kept full by the TMA warp)
@@ -255,12 +261,12 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
     auto teamBarrier = [&]() { namedBarrier(1 + team, kTeamThreads); };
     auto consumerBarrier = [&]() { namedBarrier(3 + team, kTeamConsumers); };
 
-    uint32_t trip = 0, normalTrips = 0, dcUses = 0, dcLoads = 0, pairBase = 0;
+    uint32_t trip = 0, normalTrips = 0, dcLoads = 0, pairBase = 0;
     bool dcLoadPending = false, dictReady = false, exhausted = false;
     // optional phase timing (MNENC_MP_TIMING=1): cycles of consumer thread 0 of CTA 0 per phase
     long long tPhase[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     long long tLast = 0;
-    unsigned long long nItemsSum = 0, nDcSum = 0, nCandSum = 0;
+    unsigned long long nItemsSum = 0, nCandSum = 0;
     const bool timing = p.debugTiming && tid == 0 && blockIdx.x == 0;
 #define MNENC_TICK(k)                     \
     if (timing) {                         \
@@ -309,7 +315,6 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                     T.fifoTail = T.fifoHead;  // whatever is left holds only kNone
                     T.nActive[cur ^ 1u] = 0;
                     T.nItems[cur ^ 1u] = 0;
-                    T.nDc[cur ^ 1u] = 0;
                 }
                 __syncwarp();
                 topUpFifo();
@@ -335,9 +340,8 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             continue;
         }
         const uint32_t nItems = T.nItems[cur];
-        const uint32_t nDc = T.nDc[cur];
         const uint32_t nPairs = (nItems + 1u) >> 1;
-        if (timing) nItemsSum += nItems, nDcSum += nDc;
+        if (timing) nItemsSum += nItems;
 
         if (isMma) {
             // ================= MMA issuer =================
@@ -352,8 +356,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                         for (int ks = 0; ks < 4; ++ks)
                             ummaF16(tmemT + t * 32, umDesc(dAddr + t * 16 * kSbo + ks * kKStep, kLbo, kSbo),
                                     umDesc(rAddr + h * (kSlots * kN * 2) + ks * kKStep, kLbo, kSbo), kIdescF16M128N32, (h | ks) ? 1u : 0u);
-                ummaCommit(&T.mbarBase);
-                if (nDc) {
+                {   // resident tile: KLT groups of atoms 0 and nBase-1 of the team's channel against every slot
                     if (dcLoadPending) mbarWait(&T.mbarDcLoad, (dcLoads - 1u) & 1u), dcLoadPending = false;
                     const uint32_t cAddr = smemAddr(s.dc[team]);
 #pragma unroll
@@ -362,8 +365,8 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                         for (int ks = 0; ks < 4; ++ks)
                             ummaF16(tmemT + kColDc, umDesc(cAddr + ks * kKStep, kLbo, kSbo),
                                     umDesc(rAddr + h * (kSlots * kN * 2) + ks * kKStep, kLbo, kSbo), kIdescF16M128N32, (h | ks) ? 1u : 0u);
-                    ummaCommit(&T.mbarDc);
                 }
+                ummaCommit(&T.mbarBase);
                 for (uint32_t q = 0; q < nPairs; ++q) {
                     const uint32_t ctr = pairBase + q;
                     const uint32_t stage = ctr % kTStages, su = ctr / kTStages, acc = ctr % kTAccs, au = ctr / kTAccs;
@@ -405,7 +408,6 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             // ================= consumers =================
             if (tidT == 0) {
                 T.nItems[cur ^ 1u] = 0;
-                T.nDc[cur ^ 1u] = 0;
                 T.nActive[cur ^ 1u] = 0;
                 T.nCand = 0;
             }
@@ -437,6 +439,31 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                 const float m = fmaxf(b0 ? w2[1] : w2[0], __shfl_xor_sync(kFullMask, b0 ? w2[0] : w2[1], 1));
                 atomicMax(&T.approxMax[lane], __float_as_uint(m));
             }
+            // resident tile: this warp's 32 rows (quarter) x 16 slots (warp set); rows 0-63 atom 0, 64-127 atom nBase-1
+            const int dcK = quarter >> 1, dcRow = (quarter & 1) * 32 + lane;
+            const int dcAtom = dcK ? p.nBase - 1 : 0;
+            const bool dcRowOk = dcRow < s.detRows[dcAtom];
+            const unsigned dcHas = __ballot_sync(kFullMask, lane < 16 && T.dcFirst[dcK][wset * 16 + (lane & 15)] != 0xFFFFu) & 0xFFFFu &
+                                   (liveMask >> (wset * 16));
+            if (dcHas) {
+                uint32_t raw[16];
+                tmemLoad16(tmemT + laneBase + kColDc + static_cast<uint32_t>(wset * 16), raw);
+                float u[16], w8[8], w4[4], w2[2];
+                const bool b3 = lane & 8, b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float a = (dcRowOk && ((dcHas >> i) & 1u)) ? fabsf(__uint_as_float(raw[i])) : 0.0f;
+                    u[i] = fmaxf(a, __shfl_xor_sync(kFullMask, a, 16));
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) w8[i] = fmaxf(b3 ? u[i + 8] : u[i], __shfl_xor_sync(kFullMask, b3 ? u[i] : u[i + 8], 8));
+#pragma unroll
+                for (int i = 0; i < 4; ++i) w4[i] = fmaxf(b2 ? w8[i + 4] : w8[i], __shfl_xor_sync(kFullMask, b2 ? w8[i] : w8[i + 4], 4));
+#pragma unroll
+                for (int i = 0; i < 2; ++i) w2[i] = fmaxf(b1 ? w4[i + 2] : w4[i], __shfl_xor_sync(kFullMask, b1 ? w4[i] : w4[i + 2], 2));
+                const float m = fmaxf(b0 ? w2[1] : w2[0], __shfl_xor_sync(kFullMask, b0 ? w2[0] : w2[1], 1));
+                if (lane < 16 && ((dcHas >> lane) & 1u)) atomicMax(&T.approxMax[wset * 16 + lane], __float_as_uint(m));
+            }
             consumerBarrier();
             MNENC_TICK(2)
             // ---- (b) base atoms that can still be the exact maximum -> candidate list (second TMEM pass) ----
@@ -466,6 +493,24 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                     pushCandidate(sl, atom, static_cast<uint32_t>(atom));
                 }
             }
+            if (dcHas) {  // rows of the resident groups that can still be the exact maximum
+                uint32_t raw[16];
+                tmemLoad16(tmemT + laneBase + kColDc + static_cast<uint32_t>(wset * 16), raw);
+                unsigned cand = 0;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int sl = wset * 16 + i;
+                    cand |= (fabsf(__uint_as_float(raw[i])) + T.twoEps[sl] >= __uint_as_float(T.approxMax[sl]) ? 1u : 0u) << i;
+                }
+                cand &= dcHas;
+                if (!dcRowOk) cand = 0;
+                while (cand) {
+                    const int i = __ffs(cand) - 1;
+                    cand &= cand - 1;
+                    const int sl = wset * 16 + i;
+                    pushCandidate(sl, static_cast<int>(T.dcFirst[dcK][sl]) + dcRow, static_cast<uint32_t>(kRowsPad + (ch * p.nBase + dcAtom) * 64 + dcRow));
+                }
+            }
             fenceBefore();
             MNENC_TICK(3)
             // One (slot, group) item whose 64 scores sit in TMEM column `col`: lanes of this warp hold rows rowBase + lane.
@@ -484,18 +529,6 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                 if (rowOk && ((liveMask >> sl) & 1u) && a + T.twoEps[sl] >= __uint_as_float(seen))
                     pushCandidate(sl, first + row, static_cast<uint32_t>(kRowsPad + (ch * p.nBase + atom) * 64 + row));
             };
-            // ---- (c0) resident groups: one shared tile, lanes 0-63 atom 0, lanes 64-127 atom nBase-1 ----
-            if (nDc) {
-                mbarWait(&T.mbarDc, dcUses & 1u);
-                fenceAfter();
-                for (uint32_t i = static_cast<uint32_t>(wset); i < nDc; i += 2) {
-                    const uint32_t it = T.items[cur][kItemCap - 1 - i];
-                    const int atom = T.groupAtom[(it & 31u) * kMaxK + (it >> 5)];
-                    if ((atom != 0 ? 1 : 0) != (quarter >> 1)) continue;  // warp-uniform
-                    scoreItem(it, kColDc, (quarter & 1) * 32);
-                }
-                fenceBefore();
-            }
             MNENC_TICK(4)
             // ---- (c) streamed pairs: warp set w takes pairs w, w+2, ...; quarters 0,1 -> first item, 2,3 -> second ----
             for (uint32_t q = static_cast<uint32_t>(wset); q < nPairs; q += 2) {
@@ -575,6 +608,8 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                         T.twoEps[slot] = epsOf(ss);
                         T.zeroRes[slot] = nonZero ? 0 : 1;
                         if (idx < p.nBase) {
+                            if (idx == 0 && T.dcFirst[0][slot] == 0xFFFFu) T.dcFirst[0][slot] = static_cast<uint16_t>(height);
+                            if (idx == p.nBase - 1 && T.dcFirst[1][slot] == 0xFFFFu) T.dcFirst[1][slot] = static_cast<uint16_t>(height);
                             T.groupAtom[slot * kMaxK + ng] = static_cast<uint16_t>(idx);
                             T.groupFirst[slot * kMaxK + ng] = static_cast<uint16_t>(height);
                             T.ngroups[slot] = ngNew;
@@ -583,26 +618,19 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                     }
                     if (reps + 1 == p.K) {
                         count = p.K;
-                    } else if (ngNew > 0) {  // this slot's (slot, group) items of the next trip: resident (from the top) or streamed
+                    } else if (ngNew > 0) {  // this slot's streamed (slot, group) items of the next trip (resident groups need no list)
                         __syncwarp(groupMask);
                         for (int g0 = 0; g0 < ngNew; g0 += 8) {
                             const int gi = g0 + l8;
                             const bool valid = gi < ngNew;
                             const int atom = valid ? T.groupAtom[slot * kMaxK + gi] : -1;
                             const bool isDc = valid && (atom == 0 || atom == p.nBase - 1);
-                            const unsigned mDc = (__ballot_sync(groupMask, isDc) & groupMask) >> leaderLane;
                             const unsigned mSt = (__ballot_sync(groupMask, valid && !isDc) & groupMask) >> leaderLane;
-                            uint32_t atDc = 0, atSt = 0;
-                            if (l8 == 0) {
-                                if (mDc) atDc = atomicAdd(&T.nDc[cur ^ 1u], static_cast<uint32_t>(__popc(mDc)));
-                                if (mSt) atSt = atomicAdd(&T.nItems[cur ^ 1u], static_cast<uint32_t>(__popc(mSt)));
-                            }
-                            atDc = __shfl_sync(groupMask, atDc, leaderLane);
+                            uint32_t atSt = 0;
+                            if (l8 == 0 && mSt) atSt = atomicAdd(&T.nItems[cur ^ 1u], static_cast<uint32_t>(__popc(mSt)));
                             atSt = __shfl_sync(groupMask, atSt, leaderLane);
                             const unsigned below = (1u << l8) - 1u;
-                            const uint16_t code = static_cast<uint16_t>(slot | (gi << 5));
-                            if (isDc) T.items[cur ^ 1u][kItemCap - 1 - (atDc + __popc(mDc & below))] = code;
-                            else if (valid) T.items[cur ^ 1u][atSt + __popc(mSt & below)] = code;
+                            if (valid && !isDc) T.items[cur ^ 1u][atSt + __popc(mSt & below)] = static_cast<uint16_t>(slot | (gi << 5));
                         }
                     }
                 }
@@ -629,7 +657,6 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
         pairBase += nPairs;
         ++trip;
         ++normalTrips;
-        if (nDc) ++dcUses;
     }
     if (isConsumer) {
 #pragma unroll
@@ -647,7 +674,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                "resident %lld, streamed+bar %lld, cand+bar %lld, stepC %lld; per trip: streamed items %.1f, resident items %.1f, candidates %.1f\n",
                normalTrips, tPhase[0] / normalTrips, tPhase[1] / normalTrips, tPhase[2] / normalTrips, tPhase[3] / normalTrips,
                tPhase[4] / normalTrips, tPhase[5] / normalTrips, tPhase[6] / normalTrips, tPhase[7] / normalTrips,
-               double(nItemsSum) / normalTrips, double(nDcSum) / normalTrips, double(nCandSum) / normalTrips);
+               double(nItemsSum) / normalTrips, 0.0, double(nCandSum) / normalTrips);
 #undef MNENC_TICK
     fenceBefore();
     __syncthreads();
