@@ -17,7 +17,7 @@
 // (block gather + YUVFromRGB: CompressedImage.cpp:595-611, misc.cpp:12-21).
 //
 // TMEM (512 columns): team t owns columns [256 t, 256 t + 256): 4 base tiles x 32 slots, 1 resident-group tile,
-// 3 accumulators for streamed pairs. Shared memory: 64 KB base image + 2 x 16 KB resident tiles + 2 x 61 KB team state.
+// 6 accumulators (16 columns: one half of the slots) for streamed pairs. Shared memory: 64 KB base image + 2 x 16 KB resident tiles + 2 x 61 KB team state.
 #include "mnenc_internal.h"
 #include "mp_tc_common.cuh"
 
@@ -35,7 +35,7 @@ constexpr int kTeamConsumers = 256;                 // 8 warps
 constexpr int kTeamThreads = kTeamConsumers + 64;   // + TMA warp + MMA warp
 constexpr int kThreadsV4 = kTeams * kTeamThreads;   // 640: warps 0-15 consumers, 16/17 TMA, 18/19 MMA
 constexpr int kTStages = 2;                         // ring stages of 16 KB (two group images)
-constexpr int kTAccs = 3;                           // pair accumulators per team
+constexpr int kTAccs = 6;                           // pair accumulators per team (16 columns each: a pair serves one half of the slots)
 constexpr uint32_t kImgBytes = 8192;                // one fp16 group image: 64 rows x 64
 constexpr uint32_t kSbo = 1024, kLbo = 128, kKStep = 256;
 constexpr int kItemCap = kSlots * kMaxK;            // streamed items grow from index 0, resident items from the top
@@ -55,7 +55,7 @@ struct TeamSmem {
     unsigned long long accFull[kTAccs], accEmpty[kTAccs];
     alignas(16) uint32_t approxMax[kSlots];                  // max |p~| per slot (float bits)
     alignas(16) float twoEps[kSlots];
-    uint32_t nItems[2], nActive[2];
+    uint32_t nItems[2], nItemsHi[2], nActive[2];           // streamed items of slots 0-15 (list grows from 0) / 16-31 (from the top)
     uint16_t dcFirst[2][kSlots];                             // dictionary index of row 0 of the slot's FIRST group of atom 0 / atom nBase-1
                                                              // (0xFFFF: none). A repeated group has identical rows, so on the exact
                                                              // ties it produces the lower index - the first occurrence - always wins.
@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             mbarInit(&X.mbarDcLoad, 1);
             for (int i = 0; i < kTStages; ++i) mbarInit(&X.full[i], 1), mbarInit(&X.empty[i], 1);
             for (int i = 0; i < kTAccs; ++i) mbarInit(&X.accFull[i], 1), mbarInit(&X.accEmpty[i], 4);
-            X.nItems[0] = X.nItems[1] = X.nActive[0] = X.nActive[1] = 0;
+            X.nItems[0] = X.nItems[1] = X.nItemsHi[0] = X.nItemsHi[1] = X.nActive[0] = X.nActive[1] = 0;
             X.nCand = 0;
             X.fifoHead = X.fifoTail = 0;
         }
@@ -315,6 +315,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                     T.fifoTail = T.fifoHead;  // whatever is left holds only kNone
                     T.nActive[cur ^ 1u] = 0;
                     T.nItems[cur ^ 1u] = 0;
+                    T.nItemsHi[cur ^ 1u] = 0;
                 }
                 __syncwarp();
                 topUpFifo();
@@ -339,9 +340,15 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             ++trip;
             continue;
         }
-        const uint32_t nItems = T.nItems[cur];
-        const uint32_t nPairs = (nItems + 1u) >> 1;
-        if (timing) nItemsSum += nItems;
+        // Streamed (slot, group) items are paired within one half of the slots, so that a pair's MMA needs only N = 16 columns
+        // and six accumulators fit where three did: TMA and MMA run further ahead of the consumers.
+        const uint32_t nLo = T.nItems[cur], nHi = T.nItemsHi[cur];
+        const uint32_t nPLo = (nLo + 1u) >> 1, nPairs = nPLo + ((nHi + 1u) >> 1);
+        if (timing) nItemsSum += nLo + nHi;
+        auto pairCount = [&](uint32_t q) { return q < nPLo ? min(2u, nLo - 2u * q) : min(2u, nHi - 2u * (q - nPLo)); };
+        auto pairItem = [&](uint32_t q, uint32_t i) -> uint32_t {
+            return q < nPLo ? T.items[cur][2u * q + i] : T.items[cur][kItemCap - 1 - (2u * (q - nPLo) + i)];
+        };
 
         if (isMma) {
             // ================= MMA issuer =================
@@ -374,12 +381,13 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                     mbarWait(&T.accEmpty[acc], (au & 1u) ^ 1u);
                     fenceAfter();
                     const uint32_t aAddr = smemAddr(T.ring[stage]);
+                    const uint32_t halfOff = q < nPLo ? 0u : 2u * kSbo;  // residual rows of slots 16-31
 #pragma unroll
                     for (int h = 0; h < 2; ++h)
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
-                            ummaF16(tmemT + kColAcc + acc * 32, umDesc(aAddr + ks * kKStep, kLbo, kSbo),
-                                    umDesc(rAddr + h * (kSlots * kN * 2) + ks * kKStep, kLbo, kSbo), kIdescF16M128N32, (h | ks) ? 1u : 0u);
+                            ummaF16(tmemT + kColAcc + acc * 16, umDesc(aAddr + ks * kKStep, kLbo, kSbo),
+                                    umDesc(rAddr + halfOff + h * (kSlots * kN * 2) + ks * kKStep, kLbo, kSbo), kIdescF16M128N16, (h | ks) ? 1u : 0u);
                     ummaCommit(&T.empty[stage]);   // ring stage free once these MMAs have read it
                     ummaCommit(&T.accFull[acc]);   // scores of the pair are in TMEM
                 }
@@ -391,10 +399,10 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                     const uint32_t ctr = pairBase + q;
                     const uint32_t stage = ctr % kTStages, su = ctr / kTStages;
                     mbarWait(&T.empty[stage], (su & 1u) ^ 1u);
-                    const uint32_t n = min(2u, nItems - 2u * q);
+                    const uint32_t n = pairCount(q);
                     mbarExpectTx(&T.full[stage], n * kImgBytes);
                     for (uint32_t i = 0; i < n; ++i) {
-                        const uint32_t it = T.items[cur][2u * q + i];
+                        const uint32_t it = pairItem(q, i);
                         const uint32_t atom = T.groupAtom[(it & 31u) * kMaxK + (it >> 5)];
                         bulkCopy(T.ring[stage] + i * kImgBytes,
                                  reinterpret_cast<const unsigned char*>(p.detUm16) + (static_cast<size_t>(ch) * p.nBase + atom) * kImgBytes, kImgBytes,
@@ -408,6 +416,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             // ================= consumers =================
             if (tidT == 0) {
                 T.nItems[cur ^ 1u] = 0;
+                T.nItemsHi[cur ^ 1u] = 0;
                 T.nActive[cur ^ 1u] = 0;
                 T.nCand = 0;
             }
@@ -513,10 +522,11 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             }
             fenceBefore();
             MNENC_TICK(3)
+            MNENC_TICK(4)
             // One (slot, group) item whose 64 scores sit in TMEM column `col`: lanes of this warp hold rows rowBase + lane.
             auto scoreItem = [&](uint32_t it, uint32_t col, int rowBase) {
                 const int sl = static_cast<int>(it & 31u), gi = static_cast<int>(it >> 5);
-                const uint32_t raw = tmemLoad1(tmemT + laneBase + col + static_cast<uint32_t>(sl));
+                const uint32_t raw = tmemLoad1(tmemT + laneBase + col + static_cast<uint32_t>(sl & 15));
                 const int atom = T.groupAtom[sl * kMaxK + gi];
                 const int first = T.groupFirst[sl * kMaxK + gi];
                 const int row = rowBase + lane;
@@ -529,15 +539,16 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                 if (rowOk && ((liveMask >> sl) & 1u) && a + T.twoEps[sl] >= __uint_as_float(seen))
                     pushCandidate(sl, first + row, static_cast<uint32_t>(kRowsPad + (ch * p.nBase + atom) * 64 + row));
             };
-            MNENC_TICK(4)
-            // ---- (c) streamed pairs: warp set w takes pairs w, w+2, ...; quarters 0,1 -> first item, 2,3 -> second ----
+            // ---- (c) streamed pairs: warp set w takes pairs w, w+2, ...; quarters 0,1 -> first item, 2,3 -> second.
+            // (Batching several pairs per warp for ILP was measured slower: the phase is bound by the TMA ring's two stages,
+            // and a batch cannot start before its last pair has arrived.) ----
             for (uint32_t q = static_cast<uint32_t>(wset); q < nPairs; q += 2) {
                 const uint32_t ctr = pairBase + q;
                 const uint32_t acc = ctr % kTAccs, au = ctr / kTAccs;
-                const uint32_t itemIdx = 2u * q + static_cast<uint32_t>(quarter >> 1);
+                const uint32_t itemSel = static_cast<uint32_t>(quarter >> 1);
                 mbarWait(&T.accFull[acc], au & 1u);
                 fenceAfter();
-                if (itemIdx < nItems) scoreItem(T.items[cur][itemIdx], kColAcc + acc * 32, (quarter & 1) * 32);
+                if (itemSel < pairCount(q)) scoreItem(pairItem(q, itemSel), kColAcc + acc * 16, (quarter & 1) * 32);
                 fenceBefore();
                 __syncwarp();
                 if (lane == 0) mbarArrive(&T.accEmpty[acc]);
@@ -627,10 +638,12 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                             const bool isDc = valid && (atom == 0 || atom == p.nBase - 1);
                             const unsigned mSt = (__ballot_sync(groupMask, valid && !isDc) & groupMask) >> leaderLane;
                             uint32_t atSt = 0;
-                            if (l8 == 0 && mSt) atSt = atomicAdd(&T.nItems[cur ^ 1u], static_cast<uint32_t>(__popc(mSt)));
+                            const bool hiHalf = slot >= 16;
+                            if (l8 == 0 && mSt) atSt = atomicAdd(hiHalf ? &T.nItemsHi[cur ^ 1u] : &T.nItems[cur ^ 1u], static_cast<uint32_t>(__popc(mSt)));
                             atSt = __shfl_sync(groupMask, atSt, leaderLane);
                             const unsigned below = (1u << l8) - 1u;
-                            if (valid && !isDc) T.items[cur ^ 1u][atSt + __popc(mSt & below)] = static_cast<uint16_t>(slot | (gi << 5));
+                            const uint32_t at = atSt + __popc(mSt & below);
+                            if (valid && !isDc) T.items[cur ^ 1u][hiHalf ? kItemCap - 1 - at : at] = static_cast<uint16_t>(slot | (gi << 5));
                         }
                     }
                 }

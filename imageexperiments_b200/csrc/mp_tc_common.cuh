@@ -130,6 +130,13 @@ __device__ __forceinline__ uint32_t tmemLoad1(uint32_t taddr) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
     return v;
 }
+// same without the wait: issue several, then one tmemWaitLd()
+__device__ __forceinline__ uint32_t tmemLoad1NoWait(uint32_t taddr) {
+    uint32_t v;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v) : "r"(taddr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void tmemWaitLd() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 template <int kId, int kThreads>
 __device__ __forceinline__ void namedBarrier() {
     asm volatile("bar.sync %0, %1;" ::"n"(kId), "n"(kThreads) : "memory");
@@ -137,6 +144,7 @@ __device__ __forceinline__ void namedBarrier() {
 __device__ __forceinline__ void namedBarrier(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
 
 // M = 128, N = 32, A/B = F16 K-major, D = F32 (cute::UMMA::InstrDescriptor bit layout)
+constexpr uint32_t kIdescF16M128N16 = (1u << 4) | (0u << 7) | (0u << 10) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
 constexpr uint32_t kIdescF16M128N32 = (1u << 4) | (0u << 7) | (0u << 10) | ((32u >> 3) << 17) | ((128u >> 4) << 24);
 
 }  // namespace tc
