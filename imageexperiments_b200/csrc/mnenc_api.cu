@@ -323,7 +323,8 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     p.baseUm16 = c->baseUm16.as<uint16_t>();
     p.detUm16 = c->detUm16.as<uint16_t>();
     p.rows32 = c->rows32.as<float>();
-    p.epsRel16 = c->epsRel16;
+    p.epsRel16 = (c->mpMode == 3 && !c->residualLo) ? c->epsRel16Hi : c->epsRel16;
+    p.residualLo = c->residualLo;
     p.epsAbs16 = c->epsAbs16;
     p.debugTiming = std::getenv("MNENC_MP_TIMING") != nullptr;
     if (c->mpMode == 3) CU(launchMatchingPursuitTeams(p, c->numSMs, c->stream));
@@ -438,7 +439,10 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
         double roundNorm = 0.0, maxNorm = 0.0;
         buildF16Images(base, n_base, detail_rows, det3, b16.data(), d16.data(), rows.data(), &roundNorm, &maxNorm);
         c->epsRel16 = static_cast<float>((roundNorm + maxNorm * (1.0 / 4194304.0 + 4e-5 + 64.0 / 16777216.0)) * 1.15);
+        // residual rounded to fp16 without the lo part: |d.(r - fp16(r))| <= ||d|| 2^-11 ||r|| (subnormal parts: epsAbs16)
+        c->epsRel16Hi = static_cast<float>((roundNorm + maxNorm * (1.0 / 2048.0 + 4e-5 + 64.0 / 16777216.0)) * 1.15);
         c->epsAbs16 = 5e-7f;
+        if (const char* lo = std::getenv("MNENC_MP_LO")) c->residualLo = std::atoi(lo) ? 1 : 0;
         CUB(c->baseUm16.ensure(b16.size() * 2));
         CUB(cudaMemcpy(c->baseUm16.p, b16.data(), b16.size() * 2, cudaMemcpyHostToDevice));
         CUB(c->detUm16.ensure(d16.size() * 2));

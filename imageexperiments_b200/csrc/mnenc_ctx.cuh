@@ -118,7 +118,8 @@ struct mnenc_ctx {
     float hQuant[3 * mnenc::kMaxK] = {};
     // dictionary
     mnenc::DevBuf baseT, baseUm, detT, detRows, quant, baseUm16, detUm16, rows32;
-    float epsRel = 0.0f, epsRel16 = 0.0f, epsAbs16 = 0.0f;
+    float epsRel = 0.0f, epsRel16 = 0.0f, epsAbs16 = 0.0f, epsRel16Hi = 0.0f;
+    int residualLo = 0;  // MNENC_MP_LO=1 restores the hi + lo residual split (tighter pre-filter bound, twice the MMAs; measured slower)
     int mpMode = 3;  // 3 = two-team fp16 tensor-core kernel (default); MNENC_MP=f16 / tf32 / fp32 select the earlier
                      // kernels (single team / base-only TF32 pre-filter / exact full scan) for A/B validation
     // image + symbols

@@ -45,6 +45,7 @@ struct MpParams {
     unsigned int* workCounter;      // [3] zeroed before launch ([0] only, except the team kernel: one per channel)
     unsigned long long* stats;      // [2]: sum of dictionary heights over all iterations, sum of counts
     unsigned int nbc;        // 3 * nbx * nby
+    int residualLo;          // team kernel: 1 = residual split hi + lo (two MMA passes), 0 = hi only (looser bound, half the MMAs)
     int debugTiming;         // fp16 kernel: CTA 0 prints its per-phase cycle counts (MNENC_MP_TIMING=1)
 };
 

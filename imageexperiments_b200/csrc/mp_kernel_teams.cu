@@ -3,7 +3,7 @@
 // covered by the other team's work. Arithmetic, pre-filter bound and exactness argument are those of
 // mp_kernel_f16.cu:
 //   * approximate scores of ALL dictionary rows on the tensor cores (tcgen05.mma kind::f16, fp16 dictionary images,
-//     residual split hi + lo, FP32 accumulators in TMEM),
+//     residual rounded to fp16 (hi part only by default; MNENC_MP_LO=1 adds the lo part as a second pass), FP32 accumulators in TMEM),
 //   * every row within 2*eps of the approximate maximum is re-scored with the oracle's exact FP32 arithmetic
 //     (tc::exactDot) and the exact 64-bit key decides (SelectFast, MatchingPursuit.cpp:27-37),
 //   * quantisation and residual update exact (MatchingPursuit.cpp:86-104).
@@ -170,20 +170,22 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
     auto storeResidual = [&](const float (&r)[8], bool& nonZero) {
         reinterpret_cast<float4*>(myR32)[0] = make_float4(r[0], r[1], r[2], r[3]);
         reinterpret_cast<float4*>(myR32)[1] = make_float4(r[4], r[5], r[6], r[7]);
-        uint32_t hi[4], lo[4];
+        uint32_t hi[4], lo[4] = {0u, 0u, 0u, 0u};
         float ss = 0.0f;
         bool nz = false;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const __half h0 = __float2half_rn(r[2 * i]), h1 = __float2half_rn(r[2 * i + 1]);
-            const __half l0 = __float2half_rn(r[2 * i] - __half2float(h0)), l1 = __float2half_rn(r[2 * i + 1] - __half2float(h1));
             hi[i] = static_cast<uint32_t>(__half_as_ushort(h0)) | (static_cast<uint32_t>(__half_as_ushort(h1)) << 16);
-            lo[i] = static_cast<uint32_t>(__half_as_ushort(l0)) | (static_cast<uint32_t>(__half_as_ushort(l1)) << 16);
+            if (p.residualLo) {
+                const __half l0 = __float2half_rn(r[2 * i] - __half2float(h0)), l1 = __float2half_rn(r[2 * i + 1] - __half2float(h1));
+                lo[i] = static_cast<uint32_t>(__half_as_ushort(l0)) | (static_cast<uint32_t>(__half_as_ushort(l1)) << 16);
+            }
             ss += r[2 * i] * r[2 * i] + r[2 * i + 1] * r[2 * i + 1];
             nz |= (r[2 * i] != 0.0f) | (r[2 * i + 1] != 0.0f);
         }
         *reinterpret_cast<uint4*>(myR16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-        *reinterpret_cast<uint4*>(myR16 + kSlots * kN * sizeof(__half)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        if (p.residualLo) *reinterpret_cast<uint4*>(myR16 + kSlots * kN * sizeof(__half)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         nonZero = (__ballot_sync(groupMask, nz) & groupMask) != 0u;
         return groupSum(ss);
     };
@@ -352,13 +354,14 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
 
         if (isMma) {
             // ================= MMA issuer =================
+            const int nH = p.residualLo ? 2 : 1;  // residual = fp16 hi (+ fp16 lo): one or two accumulating passes
             if (lane == 0) {
                 if (!dictReady) mbarWait(&s.mbarDict, 0), dictReady = true;
                 const uint32_t dAddr = smemAddr(s.D16);
 #pragma unroll
                 for (int t = 0; t < 4; ++t)
 #pragma unroll
-                    for (int h = 0; h < 2; ++h)
+                    for (int h = 0; h < nH; ++h)
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
                             ummaF16(tmemT + t * 32, umDesc(dAddr + t * 16 * kSbo + ks * kKStep, kLbo, kSbo),
@@ -367,7 +370,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                     if (dcLoadPending) mbarWait(&T.mbarDcLoad, (dcLoads - 1u) & 1u), dcLoadPending = false;
                     const uint32_t cAddr = smemAddr(s.dc[team]);
 #pragma unroll
-                    for (int h = 0; h < 2; ++h)
+                    for (int h = 0; h < nH; ++h)
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
                             ummaF16(tmemT + kColDc, umDesc(cAddr + ks * kKStep, kLbo, kSbo),
@@ -383,7 +386,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                     const uint32_t aAddr = smemAddr(T.ring[stage]);
                     const uint32_t halfOff = q < nPLo ? 0u : 2u * kSbo;  // residual rows of slots 16-31
 #pragma unroll
-                    for (int h = 0; h < 2; ++h)
+                    for (int h = 0; h < nH; ++h)
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
                             ummaF16(tmemT + kColAcc + acc * 16, umDesc(aAddr + ks * kKStep, kLbo, kSbo),
