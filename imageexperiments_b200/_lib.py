@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmnenc.so")
+LIB_PATH = os.environ.get("MNENC_LIB") or os.path.join(HERE, "libmnenc.so")  # MNENC_LIB: A/B runs against another build
 
 _vp, _sz = C.c_void_p, C.c_size_t
 

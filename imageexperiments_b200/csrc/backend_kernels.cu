@@ -588,9 +588,20 @@ __global__ void __launch_bounds__(256) seqBitsKernel(CodeLenIn in, uint32_t M, u
     __syncthreads();
     const uint32_t base = blockIdx.x * kHistChunk;
     const uint32_t* start = in.v.table->start;
-    for (uint32_t g = base + threadIdx.x; g < min(base + kHistChunk, M); g += blockDim.x) {
-        const int q = findSeq(start, in.nSeq, g);
-        atomicAdd(&sBits[q], static_cast<unsigned long long>(in(g)));
+    const uint32_t end = min(base + kHistChunk, M);
+    for (uint32_t g0 = base; g0 < end; g0 += blockDim.x) {  // uniform trip count: the warp reductions below need every lane
+        const uint32_t g = g0 + threadIdx.x;
+        const bool ok = g < end;
+        const int q = ok ? findSeq(start, in.nSeq, g) : -1;
+        const uint32_t len = ok ? in(g) : 0u;
+        // a warp's 32 consecutive symbols nearly always lie in one sequence: one shared-memory atomic per warp, not per symbol
+        const int q0 = __shfl_sync(kFull, q, 0);
+        if (__all_sync(kFull, q == q0 || q < 0)) {
+            const uint32_t sum = __reduce_add_sync(kFull, len);
+            if ((threadIdx.x & 31) == 0 && q0 >= 0) atomicAdd(&sBits[q0], static_cast<unsigned long long>(sum));
+        } else if (ok) {
+            atomicAdd(&sBits[q], static_cast<unsigned long long>(len));
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < in.nSeq; i += blockDim.x)

@@ -85,7 +85,7 @@ extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
     for (auto& t : threads) t.join();
     if (const int rc = firstError.load()) {
         for (size_t i = 0; i < n_images; ++i) {
-            std::free(out[i]);
+            resultRelease(out[i]);
             out[i] = nullptr, out_bytes[i] = 0;
         }
         return fail(rc, c->laneError);

@@ -12,6 +12,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <numeric>
 #include <thread>
 #include <string>
@@ -44,6 +45,76 @@ void mergeOverlays(uint8_t* res, const std::vector<Overlay>& overlays) {
             }
         }
     }
+}
+
+namespace {
+struct ResultPool {
+    struct Buf {
+        uint8_t* p;
+        size_t cap;
+        bool inUse;
+    };
+    std::mutex m;
+    std::vector<Buf> bufs;
+    // Idle buffers kept for reuse. cudaHostAlloc / cudaFreeHost synchronise the device, so the limits are generous: a batch of
+    // 16 streams in flight must recycle without ever touching the allocator in steady state.
+    static constexpr size_t kMaxIdle = 64;
+    static constexpr size_t kMaxIdleBytes = size_t(1) << 30;
+};
+ResultPool& resultPool() {
+    static ResultPool* pool = new ResultPool;  // leaked on purpose: no CUDA calls from static destructors
+    return *pool;
+}
+}  // namespace
+
+uint8_t* resultAcquire(size_t bytes) {
+    ResultPool& rp = resultPool();
+    {
+        std::lock_guard<std::mutex> g(rp.m);
+        ResultPool::Buf* best = nullptr;
+        for (auto& b : rp.bufs)
+            if (!b.inUse && b.cap >= bytes && (!best || b.cap < best->cap)) best = &b;
+        if (best && best->cap <= 4 * bytes + (size_t(1) << 20)) {  // do not pin a 56 MB buffer under a 600-byte stream
+            best->inUse = true;
+            return best->p;
+        }
+    }
+    void* p = nullptr;
+    const size_t cap = bytes + bytes / 8 + 4096;
+    if (cudaHostAlloc(&p, cap, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        return static_cast<uint8_t*>(std::malloc(bytes ? bytes : 1));  // plain memory still works as a copy target
+    }
+    std::lock_guard<std::mutex> g(rp.m);
+    rp.bufs.push_back({static_cast<uint8_t*>(p), cap, true});
+    return static_cast<uint8_t*>(p);
+}
+
+void resultRelease(uint8_t* p) {
+    if (!p) return;
+    ResultPool& rp = resultPool();
+    uint8_t* drop = nullptr;
+    {
+        std::lock_guard<std::mutex> g(rp.m);
+        bool mine = false;
+        size_t idle = 0, idleBytes = 0;
+        for (auto& b : rp.bufs) {
+            if (b.p == p) b.inUse = false, mine = true;
+            if (!b.inUse) ++idle, idleBytes += b.cap;
+        }
+        if (!mine) {
+            std::free(p);
+            return;
+        }
+        if (idle > ResultPool::kMaxIdle || idleBytes > ResultPool::kMaxIdleBytes) {
+            size_t k = rp.bufs.size();
+            for (size_t i = 0; i < rp.bufs.size(); ++i)
+                if (!rp.bufs[i].inUse && (k == rp.bufs.size() || rp.bufs[i].cap < rp.bufs[k].cap)) k = i;
+            drop = rp.bufs[k].p;
+            rp.bufs.erase(rp.bufs.begin() + static_cast<long>(k));
+        }
+    }
+    if (drop) cudaFreeHost(drop);
 }
 
 int ensureHistogram(mnenc_ctx* c) {
@@ -254,7 +325,6 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     // ---- phase 3: bit packing ----
     const size_t outAlloc = (totalBytes + 16 + 3) / 4 * 4;
     CU(c->outWords.ensure(outAlloc));
-    CU(c->hOut.ensure(outAlloc));
     CU(cudaMemcpyAsync(c->entryCodes.p, hCodes, static_cast<size_t>(nEntries) * 8, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(c->codeTable.p, &hTable, sizeof(CodeTable), cudaMemcpyHostToDevice, st));
     CU(cudaMemsetAsync(c->outWords.p, 0, outAlloc, st));
@@ -265,14 +335,19 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     c->launches += launchPack(b, M, nSeq, st);
     c->launches += launchResetHistogram(b, nEntries, st);
     CU(cudaEventRecord(c->ev[6], st));
-    CU(cudaMemcpyAsync(c->hOut.p, c->outWords.p, totalBytes, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    uint8_t* res = resultAcquire(totalBytes);
+    if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
+    if (cudaError_t e = cudaMemcpyAsync(res, c->outWords.p, totalBytes, cudaMemcpyDeviceToHost, st); e != cudaSuccess) {
+        resultRelease(res);
+        return fail(MNENC_ERR_CUDA, std::string("D2H of the stream: ") + cudaGetErrorString(e));
+    }
+    if (cudaError_t e = cudaStreamSynchronize(st); e != cudaSuccess) {
+        resultRelease(res);
+        return fail(MNENC_ERR_CUDA, std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e));
+    }
     const double tMerge0 = nowMs();
 
     // ---- merge host-written bits ----
-    uint8_t* res = static_cast<uint8_t*>(std::malloc(totalBytes ? totalBytes : 1));
-    if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
-    parallelCopy(c->pool.get(), res, c->hOut.as<uint8_t>(), totalBytes);
     mergeOverlays(res, overlays);
     *out = res;
     *outBytes = totalBytes;
@@ -368,7 +443,7 @@ extern "C" {
 
 const char* mnenc_last_error(void) { return g_error.c_str(); }
 
-void mnenc_free(uint8_t* p) { std::free(p); }
+void mnenc_free(uint8_t* p) { resultRelease(p); }
 
 int mnenc_quant_tables(int K, int block_size, double bpp_allocation, float* out_3K) {
     if (!out_3K) return fail(MNENC_ERR_ARG, "null argument");

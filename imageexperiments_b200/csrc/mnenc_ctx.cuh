@@ -105,6 +105,12 @@ inline void parallelCopy(HostPool* pool, uint8_t* dst, const uint8_t* src, size_
     });
 }
 
+// Result buffers (the `.mn` stream handed to the caller) come from a process-wide pool of PINNED host buffers, recycled by
+// mnenc_free(): the D2H copy of the packed stream lands directly in the caller's buffer — no staging copy, no page faults
+// of a fresh malloc (for a 56 MB stream those cost more than the whole back end).
+uint8_t* resultAcquire(size_t bytes);  // nullptr when out of memory
+void resultRelease(uint8_t* p);        // pool buffer -> back to the pool; anything else -> free()
+
 // State of one image sharded over ranks (stripe_api.cu), between the phases of the stripe protocol.
 struct StripeState;
 

@@ -461,12 +461,14 @@ int mnenc_stripe_finish(mnenc_t* c, uint8_t** out, size_t* out_bytes) {
     *out = nullptr;
     *out_bytes = 0;
     if (s->rank == 0) {
-        CU(c->hOut.ensure(s->totalBytes + 16));
-        CU(cudaMemcpyAsync(c->hOut.p, c->outWords.p, s->totalBytes, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
-        uint8_t* res = static_cast<uint8_t*>(std::malloc(s->totalBytes ? s->totalBytes : 1));
+        uint8_t* res = resultAcquire(s->totalBytes);
         if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
-        parallelCopy(c->pool.get(), res, c->hOut.as<uint8_t>(), s->totalBytes);
+        cudaError_t e = cudaMemcpyAsync(res, c->outWords.p, s->totalBytes, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) {
+            resultRelease(res);
+            return fail(MNENC_ERR_CUDA, std::string("D2H of the stream: ") + cudaGetErrorString(e));
+        }
         mergeOverlays(res, s->overlays);
         *out = res;
         *out_bytes = s->totalBytes;
