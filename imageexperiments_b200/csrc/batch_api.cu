@@ -27,6 +27,7 @@ int makeLane(mnenc_ctx* parent, int threads, mnenc_ctx** out) {
     *out = l;
     CU(cudaStreamCreateWithFlags(&l->stream, cudaStreamNonBlocking));
     for (auto& e : l->ev) CU(cudaEventCreate(&e));
+    CU(cudaEventCreateWithFlags(&l->evSync, cudaEventDisableTiming));
     return MNENC_OK;
 }
 

@@ -163,7 +163,7 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     CU(cudaEventRecord(c->ev[2], st));
     c->launches += launchTileCounts(b, st);
     CU(cudaMemcpyAsync(c->hTotals.p, b.totals, 3 * K * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(waitStream(c));
     StreamOffsets so{};
     uint64_t N64 = 0;
     for (int ch = 0; ch < 3; ++ch)
@@ -218,7 +218,7 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     CU(cudaMemcpyAsync(c->hSeqTable.p, b.seqTable, sizeof(SeqTable), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(c->hNEntries.p, b.nEntries, 4, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(c->hEntries.p, b.entries, static_cast<size_t>(firstChunk) * sizeof(HistEntry), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(waitStream(c));
     uint32_t nEntries = *c->hNEntries.as<uint32_t>();
     if (nEntries > c->entryCap) {
         // Rare: more distinct (sequence, symbol) pairs than the list holds. Grow and redo the histogram.
@@ -230,14 +230,14 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
         b.entryCap = c->entryCap;
         c->launches += launchHistogram(b, upperM, nSeq, st);
         CU(cudaMemcpyAsync(c->hNEntries.p, b.nEntries, 4, cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
+        CU(waitStream(c));
         nEntries = *c->hNEntries.as<uint32_t>();
         if (nEntries > c->entryCap) return fail(MNENC_ERR_INTERNAL, "histogram entry list overflow");
     }
     if (nEntries > firstChunk || c->hEntries.cap < static_cast<size_t>(nEntries) * sizeof(HistEntry)) {
         CU(c->hEntries.ensure(static_cast<size_t>(nEntries) * sizeof(HistEntry)));
         CU(cudaMemcpyAsync(c->hEntries.p, b.entries, static_cast<size_t>(nEntries) * sizeof(HistEntry), cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
+        CU(waitStream(c));
     }
 
     // ---- host: code tables, Huffman-vs-Golomb choice, bit layout ----
@@ -341,7 +341,7 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
         resultRelease(res);
         return fail(MNENC_ERR_CUDA, std::string("D2H of the stream: ") + cudaGetErrorString(e));
     }
-    if (cudaError_t e = cudaStreamSynchronize(st); e != cudaSuccess) {
+    if (cudaError_t e = waitStream(c); e != cudaSuccess) {
         resultRelease(res);
         return fail(MNENC_ERR_CUDA, std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e));
     }
@@ -483,6 +483,7 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
     } while (0)
     CUB(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     for (auto& e : c->ev) CUB(cudaEventCreate(&e));
+    CUB(cudaEventCreateWithFlags(&c->evSync, cudaEventDisableTiming));
     // base atoms transposed + zero padded: baseT[j*512 + atom]
     std::vector<float> baseT(static_cast<size_t>(kN) * kRowsPad, 0.0f);
     for (int a = 0; a < n_base; ++a)
@@ -567,6 +568,7 @@ void mnenc_destroy(mnenc_t* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (auto& e : c->ev)
         if (e) cudaEventDestroy(e);
+    if (c->evSync) cudaEventDestroy(c->evSync);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }

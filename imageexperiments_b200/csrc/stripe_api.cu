@@ -126,7 +126,7 @@ int mnenc_stripe_begin(mnenc_t* c, const uint8_t* rgb_stripe, int on_device, siz
     if (b.ntiles) c->launches += launchTileCounts(b, st);
     else CU(cudaMemsetAsync(b.totals, 0, 3 * K * 4, st));
     CU(cudaMemcpyAsync(c->hTotals.p, b.totals, 3 * K * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(waitStream(c));
     if (s->nblocks) finishMpAccounting(c);
     s->totals.assign(c->hTotals.as<uint32_t>(), c->hTotals.as<uint32_t>() + 3 * K);
     uint64_t N64 = 0;
@@ -167,7 +167,7 @@ int mnenc_stripe_begin(mnenc_t* c, const uint8_t* rgb_stripe, int on_device, siz
         for (int ch = 0; ch < 3; ++ch)
             if (const uint32_t n = s->totals[ch * K])
                 CU(cudaMemcpyAsync(hLast + ch, b.arena + s->so.off[2 * ch * K + 1] + n - 1, 2, cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
+        CU(waitStream(c));
     }
     for (int i = 0; i < 3 * K; ++i) rec1[i] = s->totals[i];
     for (int ch = 0; ch < 3; ++ch) rec1[3 * K + ch] = hLast[ch];
@@ -197,7 +197,7 @@ int mnenc_stripe_rle(mnenc_t* c, const uint32_t* all_rec1, uint32_t* rec2) {
     c->launches += launchRleRuns(s->b, s->so, s->N, st);
     c->launches += launchStripeRecords(s->b, s->so, s->N, s->recDev.as<StripeBoundary>(), st);
     CU(cudaMemcpyAsync(s->hRec.p, s->recDev.p, static_cast<size_t>(nStreams) * sizeof(StripeBoundary), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(waitStream(c));
     std::memcpy(rec2, s->hRec.p, static_cast<size_t>(nStreams) * sizeof(StripeBoundary));
     c->ms[7] += static_cast<float>(nowMs() - t0);
     s->phase = 2;
@@ -285,7 +285,7 @@ int mnenc_stripe_histogram(mnenc_t* c, const uint32_t* all_rec2, void** hist_dev
     CU(s->scratch.ensure(64));
     c->launches += launchReadIndirect(b.outOff, b.runIdx + s->N, s->scratch.as<uint32_t>(), st);
     CU(cudaMemcpyAsync(s->hScratch.p, s->scratch.p, 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(waitStream(c));
     if (*s->hScratch.as<uint32_t>() != static_cast<uint32_t>(rleOff)) return fail(MNENC_ERR_INTERNAL, "stitched RLE size differs from the plan");
     *hist_dev = c->hist.p;
     *first_pos_dev = c->firstPos.p;
@@ -309,7 +309,7 @@ int mnenc_stripe_plan(mnenc_t* c, uint64_t* seq_bits) {
     c->launches += launchCompact(b, nSeq, st);
     CU(c->hNEntries.ensure(4));
     CU(cudaMemcpyAsync(c->hNEntries.p, b.nEntries, 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(waitStream(c));
     const uint32_t nEntries = s->nEntries = *c->hNEntries.as<uint32_t>();
     if (nEntries > c->entryCap) {
         c->histReady = false;  // bins were consumed; rebuild the clean state on the next encode
@@ -317,7 +317,7 @@ int mnenc_stripe_plan(mnenc_t* c, uint64_t* seq_bits) {
     }
     CU(c->hEntries.ensure(static_cast<size_t>(nEntries) * sizeof(HistEntry) + 16));
     CU(cudaMemcpyAsync(c->hEntries.p, b.entries, static_cast<size_t>(nEntries) * sizeof(HistEntry), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(waitStream(c));
 
     // ---- identical code tables on every rank ----
     const double tHost0 = nowMs();
@@ -361,7 +361,7 @@ int mnenc_stripe_plan(mnenc_t* c, uint64_t* seq_bits) {
     CU(s->hSeqBits.ensure(sizeof(unsigned long long) * kMaxSeq));
     c->launches += launchSeqBits(b, s->M, nSeq, s->seqBitsDev.as<unsigned long long>(), st);
     CU(cudaMemcpyAsync(s->hSeqBits.p, s->seqBitsDev.p, sizeof(unsigned long long) * kMaxSeq, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(waitStream(c));
     for (int q = 0; q < nSeq; ++q) seq_bits[q] = s->hSeqBits.as<unsigned long long>()[q];
     c->ms[7] += static_cast<float>(nowMs() - t0);
     s->phase = 4;
@@ -441,7 +441,7 @@ int mnenc_stripe_pack(mnenc_t* c, const uint64_t* all_seq_bits, void** out_dev, 
     c->launches += launchPack(b, s->M, nSeq, st);
     c->launches += launchResetHistogram(b, s->nEntries, st);
     CU(cudaEventRecord(c->ev[6], st));
-    CU(cudaStreamSynchronize(st));
+    CU(waitStream(c));
     *out_dev = c->outWords.p;
     *out_words = s->outWords;
     *out_bytes = s->totalBytes;
@@ -464,7 +464,7 @@ int mnenc_stripe_finish(mnenc_t* c, uint8_t** out, size_t* out_bytes) {
         uint8_t* res = resultAcquire(s->totalBytes);
         if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
         cudaError_t e = cudaMemcpyAsync(res, c->outWords.p, s->totalBytes, cudaMemcpyDeviceToHost, c->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e == cudaSuccess) e = waitStream(c);
         if (e != cudaSuccess) {
             resultRelease(res);
             return fail(MNENC_ERR_CUDA, std::string("D2H of the stream: ") + cudaGetErrorString(e));
