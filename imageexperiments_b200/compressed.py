@@ -119,9 +119,10 @@ def _take(out: _vp, n: int) -> bytes:
         _lib.load().mnenc_free(out)
 
 
-def encodeImageFast(imgIn, context: CompressionContextFast) -> bytes:
+def encodeImageFast(imgIn, context: CompressionContextFast, zero_copy: bool = False):
     """compressed::encodeImageFast (CompressedImage.cpp:578-633). ``imgIn``: HxWx3 uint8 numpy array on the host
-    (copied to the GPU inside the call) or a CUDA torch uint8 tensor of the same shape (already resident)."""
+    (copied to the GPU inside the call) or a CUDA torch uint8 tensor of the same shape (already resident). Returns the
+    `.mn` stream as bytes (``zero_copy``: as an MnBuffer over the library's pinned host buffer)."""
     L = _lib.load()
     out, n = _vp(), C.c_size_t()
     if isinstance(imgIn, np.ndarray):
@@ -144,13 +145,14 @@ def encodeImageFast(imgIn, context: CompressionContextFast) -> bytes:
                 raise ValueError("tensor is on another device than the context")
             h, w, _ = imgIn.shape
             _lib.check(L.mnenc_encode_rgb8_device(context._h, _vp(imgIn.data_ptr()), w, h, 3 * w, C.byref(out), C.byref(n)))
-    return _take(out, n.value)
+    return MnBuffer(out, n.value) if zero_copy else _take(out, n.value)
 
 
-def encodeImageBatch(images, context: CompressionContextFast) -> list:
+def encodeImageBatch(images, context: CompressionContextFast, zero_copy: bool = False) -> list:
     """Throughput mode: encodeImageFast of every image of ``images`` (all host numpy arrays / CPU tensors, or all CUDA
     tensors on the context's device), pipelined over the context's lanes (mnenc_encode_batch_rgb8). Returns a list of
-    bytes, each identical to encodeImageFast(image, context)."""
+    bytes, each identical to encodeImageFast(image, context) — or, with ``zero_copy``, of MnBuffer objects over the
+    library's own (pinned host) result buffers: copying 16 x 3.4 MB into Python bytes costs ~8 ms with the GPU idle."""
     n = len(images)
     if n == 0:
         return []
@@ -178,6 +180,8 @@ def encodeImageBatch(images, context: CompressionContextFast) -> list:
         ptrs[i], hs[i], ws[i], strides[i] = ptr, im.shape[0], im.shape[1], 3 * im.shape[1]
     outs, sizes = (_vp * n)(), (C.c_size_t * n)()
     _lib.check(_lib.load().mnenc_encode_batch_rgb8(context._h, n, ptrs, int(on_device), ws, hs, strides, outs, sizes))
+    if zero_copy:
+        return [MnBuffer(_vp(outs[i]), sizes[i]) for i in range(n)]
     return [_take(_vp(outs[i]), sizes[i]) for i in range(n)]
 
 

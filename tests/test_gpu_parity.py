@@ -170,6 +170,11 @@ def test_batch_equals_one_at_a_time(ctx, oracle_ctx_factory):
     assert mn.encodeImageBatch(frames, ctx) == want
     assert mn.encodeImageBatch([torch.from_numpy(f).cuda() for f in frames], ctx) == want
     assert mn.encodeImageBatch(frames[:1], ctx) == want[:1]
+    zc = mn.encodeImageBatch(frames, ctx, zero_copy=True)     # streams left in the library's pinned buffers
+    assert [bytes(z) for z in zc] == want and [len(z) for z in zc] == [len(x) for x in want]
+    assert bytes(memoryview(zc[0].array)) == want[0]
+    del zc
+    assert bytes(mn.encodeImageFast(frames[3], ctx, zero_copy=True)) == want[3]
     assert mn.encodeImageBatch([], ctx) == []
     ms, launches = ctx.last_timing()
     assert launches > 0
