@@ -4,7 +4,7 @@
     python bench.py --gpus N --steps K --warmup W            # our arm (torchrun launches N ranks for N > 1)
     python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU encoder on the host cores
 
-A step = one batch of BATCH (16: a ring of 4 distinct images, 4 times) 4928x3264 synthetic RGB images (BASELINE.json configs[1]) per GPU, each completely
+A step = one batch of BATCH (32: a ring of 4 distinct images, 8 times) 4928x3264 synthetic RGB images (BASELINE.json configs[1]) per GPU, each completely
 encoded at quality 3.5 through the public batch call (encodeImageBatch -> mnenc_encode_batch_rgb8: the images are pipelined
 over lanes, every stream byte-identical to the one-at-a-time encodeImageFast). `value` is measured with the pixels already resident in HBM, `e2e` through the
 same public call with pinned HOST pixels (H2D and D2H inside the timed region). N > 1: every rank encodes its own
@@ -29,7 +29,7 @@ sys.path.insert(0, ROOT)
 W, H, QUALITY, K_ATOMS = 4928, 3264, 3.5, 32
 METRIC = "encode megapixels/sec at quality 3.5"
 RING = 4  # distinct input images per rank: 4 x 48.3 MB = 193 MB > 126 MB L2
-BATCH = 16  # images per step: the ring repeated 4 times, so the lanes reach their steady state inside a step
+BATCH = 32  # images per step: the ring repeated 8 times, so the lanes reach their steady state inside a step
 
 
 def make_ring(rank: int):

@@ -40,7 +40,7 @@ extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
     for (size_t i = 0; i < n_images; ++i) out[i] = nullptr, out_bytes[i] = 0;
     if (n_images == 0) return MNENC_OK;
     CU(cudaSetDevice(c->device));
-    int want = 4;
+    int want = 6;
     if (const char* e = std::getenv("MNENC_LANES")) want = std::atoi(e);
     want = static_cast<int>(std::min<size_t>(static_cast<size_t>(std::clamp(want, 1, 8)), n_images));
     while (static_cast<int>(c->lanes.size()) + 1 < want) {

@@ -31,8 +31,9 @@ def main():
         p = torch.empty(a.shape, dtype=torch.uint8, pin_memory=True)
         p.numpy()[...] = a
         pin.append(p)
+    ref = None
     res = {"workload": f"{n} x {w}x{h} RGB synthetic, quality 3.5"}
-    for lanes in (1, 2, 3, 4):
+    for lanes in [int(x) for x in os.environ.get("LANES_SWEEP", "1,2,3,4").split(",")]:
         os.environ["MNENC_LANES"] = str(lanes)
         ctx = mn.createCompressionContextFast(32, 8, 3.5, device=0)
         for name, src in (("resident", dev), ("pinned", pin)):
@@ -41,10 +42,10 @@ def main():
             torch.cuda.synchronize()
             t0 = time.perf_counter()
             for _ in range(3):
-                out = mn.encodeImageBatch(batch, ctx)
+                out = mn.encodeImageBatch(batch, ctx, zero_copy=True)
             dt = (time.perf_counter() - t0) / 3
             res[f"lanes{lanes}_{name}_mp_s"] = round(n * w * h / 1e6 / dt, 1)
-        if lanes == 1:
+        if ref is None:
             ref = [mn.encodeImageFast(imgs[i], ctx) for i in range(distinct)]
         assert all(out[i] == ref[i % distinct] for i in range(n)), "batch stream differs from the single-image stream"
         ctx.close()
