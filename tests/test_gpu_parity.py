@@ -185,3 +185,26 @@ def test_batch_equals_one_at_a_time(ctx, oracle_ctx_factory):
     assert mn.encodeImageFast(frames[0], ctx) == oc8.encode(frames[0])
     oc.close()
     oc8.close()
+
+
+@pytest.mark.parametrize("K", [1, 8, 16])
+def test_other_iteration_budgets(dictionary, oracle_ctx_factory, reflib, K):
+    """K (atoms per block-channel, Compression.cpp:28 uses 32) is an argument of encodeImageFast: smaller budgets must
+    match the oracle and the unmodified reference too (the dictionary does not depend on K)."""
+    img = synthetic_rgb(136, 120, 40 + K)
+    c = mn.createCompressionContextFast(K, 8, 3.5, dictionary=dictionary, device=0)
+    try:
+        oc = oracle_ctx_factory(c.Quant, K)
+        data = mn.encodeImageFast(img, c)
+        counts, pairs = mn.lastSymbols(c, 136, 120)
+        oc_counts, oc_pairs = oc.symbols(img)
+        assert (counts == oc_counts).all() and (pairs == oc_pairs).all()
+        assert counts.max() <= K
+        assert data == oc.encode(img)
+        rctx = reflib.create(K, 8, 3.5)
+        assert data == reflib.encode(rctx, img)
+        reflib.destroy(rctx)
+        assert mn.encodeImageBatch([img, img], c) == [data, data]
+        oc.close()
+    finally:
+        c.close()

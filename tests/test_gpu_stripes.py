@@ -143,3 +143,18 @@ def test_stripes_nccl_two_processes(dictionary):
                        timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "stripe_check OK" in r.stdout
+
+
+def test_stripes_other_iteration_budget(dictionary, oracle_ctx_factory):
+    """K = 8: 48 symbol streams instead of 192; the records, tables and exchanges of the protocol all scale with K."""
+    K = 8
+    cs = [mn.createCompressionContextFast(K, 8, 3.5, dictionary=dictionary, device=0) for _ in range(3)]
+    try:
+        img = synthetic_rgb(264, 96, 77)
+        got, _ = run_stripes(img, 3, cs)
+        oc = oracle_ctx_factory(cs[0].Quant, K)
+        assert got == oc.encode(img)
+        oc.close()
+    finally:
+        for c in cs:
+            c.close()
