@@ -269,6 +269,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
     long long tPhase[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     long long tLast = 0;
     unsigned long long nItemsSum = 0, nCandSum = 0;
+    unsigned long long nFlagSum = 0;  // timing only: cycles of the two tmemLoad32 of phase (a)
     const bool timing = p.debugTiming && tid == 0 && blockIdx.x == 0;
 #define MNENC_TICK(k)                     \
     if (timing) {                         \
@@ -428,6 +429,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             mbarWait(&T.mbarBase, normalTrips & 1u);
             fenceAfter();
             MNENC_TICK(1)
+            float lm0 = 0.0f, lm1 = 0.0f, lmDc = 0.0f;  // this warp's LOCAL maxima (lane L: slot L) of its two tiles / the resident tile
 #pragma unroll 1
             for (int tt = 0; tt < 2; ++tt) {
                 float v[32];
@@ -450,6 +452,8 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                 for (int i = 0; i < 2; ++i) w2[i] = fmaxf(b1 ? w4[i + 2] : w4[i], __shfl_xor_sync(kFullMask, b1 ? w4[i] : w4[i + 2], 2));
                 const float m = fmaxf(b0 ? w2[1] : w2[0], __shfl_xor_sync(kFullMask, b0 ? w2[0] : w2[1], 1));
                 atomicMax(&T.approxMax[lane], __float_as_uint(m));
+                if (tt == 0) lm0 = m;
+                else lm1 = m;
             }
             // resident tile: this warp's 32 rows (quarter) x 16 slots (warp set); rows 0-63 atom 0, 64-127 atom nBase-1
             const int dcK = quarter >> 1, dcRow = (quarter & 1) * 32 + lane;
@@ -474,54 +478,45 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
 #pragma unroll
                 for (int i = 0; i < 2; ++i) w2[i] = fmaxf(b1 ? w4[i + 2] : w4[i], __shfl_xor_sync(kFullMask, b1 ? w4[i] : w4[i + 2], 2));
                 const float m = fmaxf(b0 ? w2[1] : w2[0], __shfl_xor_sync(kFullMask, b0 ? w2[0] : w2[1], 1));
-                if (lane < 16 && ((dcHas >> lane) & 1u)) atomicMax(&T.approxMax[wset * 16 + lane], __float_as_uint(m));
+                if (lane < 16 && ((dcHas >> lane) & 1u)) atomicMax(&T.approxMax[wset * 16 + lane], __float_as_uint(m)), lmDc = m;
             }
             consumerBarrier();
             MNENC_TICK(2)
-            // ---- (b) base atoms that can still be the exact maximum -> candidate list (second TMEM pass) ----
+            // ---- (b) rows that can still be the exact maximum -> candidate list. A slot can only have such a row in this
+            // warp's part of a tile if the warp's LOCAL maximum of that slot is within 2 eps of the slot's global maximum:
+            // that is true for ~3 of the 32 slots, so only those columns are read from TMEM again. ----
+            auto filterColumns = [&](unsigned need, uint32_t colBase, int slBase, auto&& push) {
+                while (need) {
+                    const int i0 = __ffs(need) - 1;
+                    need &= need - 1;
+                    const int i1 = need ? __ffs(need) - 1 : -1;
+                    if (i1 >= 0) need &= need - 1;
+                    const uint32_t r0 = tmemLoad1NoWait(tmemT + laneBase + colBase + static_cast<uint32_t>(i0));
+                    const uint32_t r1 = i1 >= 0 ? tmemLoad1NoWait(tmemT + laneBase + colBase + static_cast<uint32_t>(i1)) : 0u;
+                    tmemWaitLd();
+                    const int s0 = slBase + i0, s1 = slBase + i1;
+                    if (fabsf(__uint_as_float(r0)) + T.twoEps[s0] >= __uint_as_float(T.approxMax[s0])) push(s0);
+                    if (i1 >= 0 && fabsf(__uint_as_float(r1)) + T.twoEps[s1] >= __uint_as_float(T.approxMax[s1])) push(s1);
+                }
+            };
 #pragma unroll 1
             for (int tt = 0; tt < 2; ++tt) {
                 const int tile = wset * 2 + tt;
                 const int atom = tile * 128 + quarter * 32 + lane;
-                uint32_t raw[32];
-                tmemLoad32(tmemT + laneBase + static_cast<uint32_t>(tile * 32), raw);
-                unsigned cand = 0;
-                const float4* mx = reinterpret_cast<const float4*>(T.approxMax);
-                const float4* te = reinterpret_cast<const float4*>(T.twoEps);
-#pragma unroll
-                for (int i4 = 0; i4 < 8; ++i4) {
-                    const float4 m4 = mx[i4];  // bit patterns of non-negative floats
-                    const float4 e4 = te[i4];
-                    cand |= (fabsf(__uint_as_float(raw[4 * i4 + 0])) + e4.x >= m4.x ? 1u : 0u) << (4 * i4 + 0);
-                    cand |= (fabsf(__uint_as_float(raw[4 * i4 + 1])) + e4.y >= m4.y ? 1u : 0u) << (4 * i4 + 1);
-                    cand |= (fabsf(__uint_as_float(raw[4 * i4 + 2])) + e4.z >= m4.z ? 1u : 0u) << (4 * i4 + 2);
-                    cand |= (fabsf(__uint_as_float(raw[4 * i4 + 3])) + e4.w >= m4.w ? 1u : 0u) << (4 * i4 + 3);
-                }
-                cand &= liveMask;
-                if (atom >= p.nBase) cand = 0;
-                while (cand) {
-                    const int sl = __ffs(cand) - 1;
-                    cand &= cand - 1;
-                    pushCandidate(sl, atom, static_cast<uint32_t>(atom));
-                }
+                const float lm = tt ? lm1 : lm0;
+                const unsigned need = __ballot_sync(kFullMask, lm + T.twoEps[lane] >= __uint_as_float(T.approxMax[lane])) & liveMask;
+                if (timing) nFlagSum += __popc(need);
+                filterColumns(need, static_cast<uint32_t>(tile * 32), 0, [&](int sl) {
+                    if (atom < p.nBase) pushCandidate(sl, atom, static_cast<uint32_t>(atom));
+                });
             }
-            if (dcHas) {  // rows of the resident groups that can still be the exact maximum
-                uint32_t raw[16];
-                tmemLoad16(tmemT + laneBase + kColDc + static_cast<uint32_t>(wset * 16), raw);
-                unsigned cand = 0;
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int sl = wset * 16 + i;
-                    cand |= (fabsf(__uint_as_float(raw[i])) + T.twoEps[sl] >= __uint_as_float(T.approxMax[sl]) ? 1u : 0u) << i;
-                }
-                cand &= dcHas;
-                if (!dcRowOk) cand = 0;
-                while (cand) {
-                    const int i = __ffs(cand) - 1;
-                    cand &= cand - 1;
-                    const int sl = wset * 16 + i;
-                    pushCandidate(sl, static_cast<int>(T.dcFirst[dcK][sl]) + dcRow, static_cast<uint32_t>(kRowsPad + (ch * p.nBase + dcAtom) * 64 + dcRow));
-                }
+            if (dcHas) {  // rows of the resident groups
+                const int sl = wset * 16 + (lane & 15);
+                const unsigned need = __ballot_sync(kFullMask, lane < 16 && lmDc + T.twoEps[sl] >= __uint_as_float(T.approxMax[sl])) & dcHas;
+                filterColumns(need, kColDc + static_cast<uint32_t>(wset * 16), wset * 16, [&](int sl2) {
+                    if (dcRowOk)
+                        pushCandidate(sl2, static_cast<int>(T.dcFirst[dcK][sl2]) + dcRow, static_cast<uint32_t>(kRowsPad + (ch * p.nBase + dcAtom) * 64 + dcRow));
+                });
             }
             fenceBefore();
             MNENC_TICK(3)
@@ -687,10 +682,10 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
     }
     if (timing && normalTrips)
         printf("mp teams timing, CTA 0 team 0: %u trips; cycles per trip: barrier %lld, baseMMA wait %lld, max+bar %lld, base filter %lld, "
-               "resident %lld, streamed+bar %lld, cand+bar %lld, stepC %lld; per trip: streamed items %.1f, resident items %.1f, candidates %.1f\n",
+               "resident %lld, streamed+bar %lld, cand+bar %lld, stepC %lld; per trip: streamed items %.1f, flagged columns of warp 0 in (b) %.1f, candidates %.1f\n",
                normalTrips, tPhase[0] / normalTrips, tPhase[1] / normalTrips, tPhase[2] / normalTrips, tPhase[3] / normalTrips,
                tPhase[4] / normalTrips, tPhase[5] / normalTrips, tPhase[6] / normalTrips, tPhase[7] / normalTrips,
-               double(nItemsSum) / normalTrips, 0.0, double(nCandSum) / normalTrips);
+               double(nItemsSum) / normalTrips, double(nFlagSum) / normalTrips, double(nCandSum) / normalTrips);
 #undef MNENC_TICK
     fenceBefore();
     __syncthreads();
