@@ -208,3 +208,26 @@ def test_other_iteration_budgets(dictionary, oracle_ctx_factory, reflib, K):
         oc.close()
     finally:
         c.close()
+
+
+@pytest.mark.parametrize("q", [1.0, 6.0, 8.0])
+def test_full_size_quality_sweep(ctx, oracle_ctx_factory, q):
+    """BASELINE.json configs[2]: 4928x3264 at other qualities (more atoms per block, other Huffman-vs-Golomb choices).
+    Symbols of sampled block columns equal the oracle's; the whole stream equals the oracle's back end on the GPU's symbols;
+    deeper quality means more atoms and a larger file."""
+    w, h = 4928, 3264
+    img = synthetic_rgb(w, h, 12345)
+    set_quality(ctx, q)
+    oc = oracle_ctx_factory(ctx.Quant)
+    data = mn.encodeImageFast(img, ctx)
+    counts, pairs = mn.lastSymbols(ctx, w, h)
+    nby = h // 8
+    for bx in (0, 311, 615):
+        oc_c, oc_p = oc.symbols(img, bx, bx + 1)
+        assert (counts[bx * nby:(bx + 1) * nby] == oc_c).all() and (pairs[bx * nby:(bx + 1) * nby] == oc_p).all(), (q, bx)
+    assert data == oc.lib.write_file(32, 8, w, h, ctx.Quant, counts, pairs)
+    mean_atoms = float(counts.mean())
+    lo, hi = {1.0: (0.5, 3.0), 6.0: (5.0, 14.0), 8.0: (7.0, 20.0)}[q]
+    assert lo < mean_atoms < hi, mean_atoms
+    oc.close()
+    set_quality(ctx, 3.5)
