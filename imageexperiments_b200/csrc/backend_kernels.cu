@@ -433,7 +433,7 @@ __device__ __forceinline__ uint16_t loadSym(const SeqView& v, const SeqDesc& d, 
 // Each CTA owns 4096 consecutive elements of the concatenation; symbols < 4096 of the CTA's first
 // sequence are privatised in shared memory, everything else goes straight to L2 atomics.
 // ------------------------------------------------------------------------------------------------
-constexpr int kHistChunk = 4096;
+constexpr int kHistChunk = 16384;  // elements per CTA: amortises the 32 KB bin initialisation and the flush of the private bins
 __global__ void __launch_bounds__(256) histogramKernel(SeqView v, int nSeq, uint32_t* hist, uint32_t* firstPos, uint32_t* maxSym) {
     __shared__ uint32_t sStart[kMaxSeq + 1];
     __shared__ uint32_t sBase[kMaxSeq];
@@ -450,24 +450,40 @@ __global__ void __launch_bounds__(256) histogramKernel(SeqView v, int nSeq, uint
     uint32_t localMax = 0;
     int qPrev = -1;
     SeqDesc d;
-    for (uint32_t g = base + threadIdx.x; g < min(base + kHistChunk, M); g += blockDim.x) {
-        const int q = (g < sStart[q0 + 1]) ? q0 : findSeq(sStart, nSeq, g);
-        if (q != qPrev) {
-            if (qPrev >= 0) atomicMax(&maxSym[qPrev], localMax);
-            localMax = 0;
-            d = v.table->desc[q];
-            qPrev = q;
+    const uint32_t end = min(base + kHistChunk, M);
+    const int lane = threadIdx.x & 31;
+    for (uint32_t g0 = base; g0 < end; g0 += blockDim.x) {  // uniform trip count: __match_any_sync below needs the whole warp
+        const uint32_t g = g0 + threadIdx.x;
+        const bool ok = g < end;
+        uint32_t key = 0xFFFFFFFFu, pos = 0, sym = 0;
+        int q = -1;
+        if (ok) {
+            q = (g < sStart[q0 + 1]) ? q0 : findSeq(sStart, nSeq, g);
+            if (q != qPrev) {
+                if (qPrev >= 0) atomicMax(&maxSym[qPrev], localMax);
+                localMax = 0;
+                d = v.table->desc[q];
+                qPrev = q;
+            }
+            const uint32_t k = g - sStart[q];
+            sym = loadSym(v, d, k);
+            pos = k + sBase[q];  // position in the WHOLE sequence (posBase = 0 unless the image is stripe-sharded)
+            localMax = max(localMax, sym);
+            key = (static_cast<uint32_t>(q) << 16) | sym;
         }
-        const uint32_t k = g - sStart[q];
-        const uint32_t sym = loadSym(v, d, k);
-        const uint32_t pos = k + sBase[q];  // position in the WHOLE sequence (posBase = 0 unless the image is stripe-sharded)
-        localMax = max(localMax, sym);
-        if (q == q0 && sym < kSmemHistBins) {
-            atomicAdd(&sHist[sym], 1u);
-            atomicMin(&sFirst[sym], pos);
-        } else {
-            atomicAdd(&hist[static_cast<size_t>(q) * kHistBins + sym], 1u);
-            atomicMin(&firstPos[static_cast<size_t>(q) * kHistBins + sym], pos);
+        // Symbol statistics are very skewed (0, 1, 2 dominate): lanes holding the same (sequence, symbol) elect their lowest
+        // lane — it also holds the smallest position — to do ONE add of the group size and ONE min, instead of up to 32
+        // serialised same-address atomics each.
+        const unsigned peers = __match_any_sync(kFull, key);
+        if (ok && lane == __ffs(peers) - 1) {
+            const uint32_t cnt = __popc(peers);
+            if (q == q0 && sym < kSmemHistBins) {
+                atomicAdd(&sHist[sym], cnt);
+                atomicMin(&sFirst[sym], pos);
+            } else {
+                atomicAdd(&hist[static_cast<size_t>(q) * kHistBins + sym], cnt);
+                atomicMin(&firstPos[static_cast<size_t>(q) * kHistBins + sym], pos);
+            }
         }
     }
     if (qPrev >= 0) atomicMax(&maxSym[qPrev], localMax);
