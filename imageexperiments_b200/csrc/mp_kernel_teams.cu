@@ -269,7 +269,8 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
     long long tPhase[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     long long tLast = 0;
     unsigned long long nItemsSum = 0, nCandSum = 0;
-    unsigned long long nFlagSum = 0;  // timing only: cycles of the two tmemLoad32 of phase (a)
+    unsigned long long nFlagSum = 0;
+    long long mmaIssue = 0, mmaDone = 0;  // timing only: cycles of the two tmemLoad32 of phase (a)
     const bool timing = p.debugTiming && tid == 0 && blockIdx.x == 0;
 #define MNENC_TICK(k)                     \
     if (timing) {                         \
@@ -354,46 +355,56 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
         };
 
         if (isMma) {
-            // ================= MMA issuer =================
+            // ================= MMA issuer: the whole warp runs the issue path with warp-uniform operands, one elected lane
+            // issues (see ummaF16Elect) =================
             const int nH = p.residualLo ? 2 : 1;  // residual = fp16 hi (+ fp16 lo): one or two accumulating passes
-            if (lane == 0) {
+            {
                 if (!dictReady) mbarWait(&s.mbarDict, 0), dictReady = true;
-                const uint32_t dAddr = smemAddr(s.D16);
+                const uint32_t dAddr = warpUniform(smemAddr(s.D16));
+                const uint32_t rA = warpUniform(rAddr);
+                const uint32_t tm = warpUniform(tmemT);
+                // descriptors differ only in the 16-byte-granular start address (low 14 bits, no carry: shared memory < 256 KB)
+                const unsigned long long descD = umDesc(dAddr, kLbo, kSbo), descR = umDesc(rA, kLbo, kSbo);
+                const bool mmaTiming = p.debugTiming && blockIdx.x == 0 && team == 0;
+                const long long tm0 = mmaTiming ? clock64() : 0;
 #pragma unroll
                 for (int t = 0; t < 4; ++t)
-#pragma unroll
                     for (int h = 0; h < nH; ++h)
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
-                            ummaF16(tmemT + t * 32, umDesc(dAddr + t * 16 * kSbo + ks * kKStep, kLbo, kSbo),
-                                    umDesc(rAddr + h * (kSlots * kN * 2) + ks * kKStep, kLbo, kSbo), kIdescF16M128N32, (h | ks) ? 1u : 0u);
+                            ummaF16Elect(tm + t * 32, descD + ((t * 16 * kSbo + ks * kKStep) >> 4),
+                                         descR + ((h * (kSlots * kN * 2) + ks * kKStep) >> 4), kIdescF16M128N32, (h | ks) ? 1u : 0u);
                 {   // resident tile: KLT groups of atoms 0 and nBase-1 of the team's channel against every slot
                     if (dcLoadPending) mbarWait(&T.mbarDcLoad, (dcLoads - 1u) & 1u), dcLoadPending = false;
-                    const uint32_t cAddr = smemAddr(s.dc[team]);
-#pragma unroll
+                    const unsigned long long descC = umDesc(warpUniform(smemAddr(s.dc[team])), kLbo, kSbo);
                     for (int h = 0; h < nH; ++h)
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
-                            ummaF16(tmemT + kColDc, umDesc(cAddr + ks * kKStep, kLbo, kSbo),
-                                    umDesc(rAddr + h * (kSlots * kN * 2) + ks * kKStep, kLbo, kSbo), kIdescF16M128N32, (h | ks) ? 1u : 0u);
+                            ummaF16Elect(tm + kColDc, descC + ((ks * kKStep) >> 4),
+                                         descR + ((h * (kSlots * kN * 2) + ks * kKStep) >> 4), kIdescF16M128N32, (h | ks) ? 1u : 0u);
                 }
-                ummaCommit(&T.mbarBase);
+                const long long tm1 = mmaTiming ? clock64() : 0;
+                ummaCommitElect(&T.mbarBase);
+                if (mmaTiming) {  // timing only: how long the issue takes, and when the scores are complete
+                    mbarWait(&T.mbarBase, normalTrips & 1u);
+                    mmaIssue += tm1 - tm0;
+                    mmaDone += clock64() - tm0;
+                }
                 for (uint32_t q = 0; q < nPairs; ++q) {
                     const uint32_t ctr = pairBase + q;
                     const uint32_t stage = ctr % kTStages, su = ctr / kTStages, acc = ctr % kTAccs, au = ctr / kTAccs;
                     mbarWait(&T.full[stage], su & 1u);
                     mbarWait(&T.accEmpty[acc], (au & 1u) ^ 1u);
                     fenceAfter();
-                    const uint32_t aAddr = smemAddr(T.ring[stage]);
-                    const uint32_t halfOff = q < nPLo ? 0u : 2u * kSbo;  // residual rows of slots 16-31
-#pragma unroll
+                    const unsigned long long descA = umDesc(warpUniform(smemAddr(T.ring[stage])), kLbo, kSbo);
+                    const unsigned long long descRh = descR + (q < nPLo ? 0u : (2u * kSbo) >> 4);  // residual rows of slots 16-31
                     for (int h = 0; h < nH; ++h)
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
-                            ummaF16(tmemT + kColAcc + acc * 16, umDesc(aAddr + ks * kKStep, kLbo, kSbo),
-                                    umDesc(rAddr + halfOff + h * (kSlots * kN * 2) + ks * kKStep, kLbo, kSbo), kIdescF16M128N16, (h | ks) ? 1u : 0u);
-                    ummaCommit(&T.empty[stage]);   // ring stage free once these MMAs have read it
-                    ummaCommit(&T.accFull[acc]);   // scores of the pair are in TMEM
+                            ummaF16Elect(tm + kColAcc + acc * 16, descA + ((ks * kKStep) >> 4),
+                                         descRh + ((h * (kSlots * kN * 2) + ks * kKStep) >> 4), kIdescF16M128N16, (h | ks) ? 1u : 0u);
+                    ummaCommitElect(&T.empty[stage]);   // ring stage free once these MMAs have read it
+                    ummaCommitElect(&T.accFull[acc]);   // scores of the pair are in TMEM
                 }
             }
         } else if (isTma) {
@@ -680,6 +691,9 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             atomicAdd(&p.stats[1], statPicks);
         }
     }
+    if (p.debugTiming && blockIdx.x == 0 && team == 0 && isMma && lane == 0 && normalTrips)
+        printf("mp teams timing, MMA thread: base + resident MMAs per trip: %lld cycles to issue, %lld cycles until complete\n",
+               mmaIssue / normalTrips, mmaDone / normalTrips);
     if (timing && normalTrips)
         printf("mp teams timing, CTA 0 team 0: %u trips; cycles per trip: barrier %lld, baseMMA wait %lld, max+bar %lld, base filter %lld, "
                "resident %lld, streamed+bar %lld, cand+bar %lld, stepC %lld; per trip: streamed items %.1f, flagged columns of warp 0 in (b) %.1f, candidates %.1f\n",

@@ -94,6 +94,26 @@ __device__ __forceinline__ void ummaF16(uint32_t tmemD, unsigned long long descA
         "l"(descA), "l"(descB), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// A warp-uniform value the compiler KNOWS is uniform: REDUX delivers its result in a uniform register, so descriptors built
+// from it stay in the uniform datapath (no R2UR.BROADCAST per MMA).
+__device__ __forceinline__ uint32_t warpUniform(uint32_t v) { return __reduce_max_sync(kFullMask, v); }
+// Warp-convergent variants: EVERY lane of the issuing warp executes the call with warp-uniform operands, one elected lane
+// issues. With the whole issue path inside `if (lane == 0)` the compiler cannot keep descriptors in uniform registers and
+// wraps each UTCHMMA in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop: ~140 cycles per MMA, measured - the issuing thread, not
+// the tensor pipe, was the limit.
+__device__ __forceinline__ void ummaF16Elect(uint32_t tmemD, unsigned long long descA, unsigned long long descB, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\telect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmemD),
+        "l"(descA), "l"(descB), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void ummaCommitElect(unsigned long long* bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smemAddr(bar))
+        : "memory");
+}
 __device__ __forceinline__ void ummaCommit(unsigned long long* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smemAddr(bar)) : "memory");
 }
