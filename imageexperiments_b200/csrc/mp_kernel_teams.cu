@@ -408,21 +408,21 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                 }
             }
         } else if (isTma) {
-            // ================= TMA producer: streamed group images, then the block-index FIFO =================
-            if (lane == 0) {
-                for (uint32_t q = 0; q < nPairs; ++q) {
-                    const uint32_t ctr = pairBase + q;
-                    const uint32_t stage = ctr % kTStages, su = ctr / kTStages;
-                    mbarWait(&T.empty[stage], (su & 1u) ^ 1u);
-                    const uint32_t n = pairCount(q);
-                    mbarExpectTx(&T.full[stage], n * kImgBytes);
-                    for (uint32_t i = 0; i < n; ++i) {
-                        const uint32_t it = pairItem(q, i);
-                        const uint32_t atom = T.groupAtom[(it & 31u) * kMaxK + (it >> 5)];
-                        bulkCopy(T.ring[stage] + i * kImgBytes,
-                                 reinterpret_cast<const unsigned char*>(p.detUm16) + (static_cast<size_t>(ch) * p.nBase + atom) * kImgBytes, kImgBytes,
-                                 &T.full[stage]);
-                    }
+            // ================= TMA producer: streamed group images, then the block-index FIFO. The whole warp runs the
+            // issue path (warp-uniform operands, one elected lane issues): with two ring stages the issue latency of a pair
+            // adds directly to the time per pair =================
+            for (uint32_t q = 0; q < nPairs; ++q) {
+                const uint32_t ctr = pairBase + q;
+                const uint32_t stage = ctr % kTStages, su = ctr / kTStages;
+                mbarWait(&T.empty[stage], (su & 1u) ^ 1u);
+                const uint32_t n = pairCount(q);
+                mbarExpectTxElect(&T.full[stage], n * kImgBytes);
+                for (uint32_t i = 0; i < n; ++i) {
+                    const uint32_t it = pairItem(q, i);
+                    const uint32_t atom = T.groupAtom[(it & 31u) * kMaxK + (it >> 5)];
+                    bulkCopyElect(T.ring[stage] + i * kImgBytes,
+                                  reinterpret_cast<const unsigned char*>(p.detUm16) + (static_cast<size_t>(ch) * p.nBase + atom) * kImgBytes, kImgBytes,
+                                  &T.full[stage]);
                 }
             }
             __syncwarp();

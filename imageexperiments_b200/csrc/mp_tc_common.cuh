@@ -79,6 +79,19 @@ __device__ __forceinline__ void bulkCopy(void* dstSmem, const void* srcGlobal, u
                  "l"(srcGlobal), "r"(bytes), "r"(smemAddr(bar))
                  : "memory");
 }
+// warp-convergent variants (every lane executes the call with warp-uniform operands, one elected lane issues; see ummaF16Elect)
+__device__ __forceinline__ void mbarExpectTxElect(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t}" ::"r"(smemAddr(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulkCopyElect(void* dstSmem, const void* srcGlobal, uint32_t bytes, unsigned long long* bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+        "@q cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n\t}" ::"r"(smemAddr(dstSmem)),
+        "l"(srcGlobal), "r"(bytes), "r"(smemAddr(bar))
+        : "memory");
+}
 __device__ __forceinline__ void fenceProxyAsync() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // ---- tcgen05 ----
