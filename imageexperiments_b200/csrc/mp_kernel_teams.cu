@@ -50,7 +50,7 @@ struct TeamSmem {
     alignas(1024) unsigned char ring[kTStages][2 * kImgBytes];
     alignas(16) float R32[kSlots * kRStr];                   // exact residuals
     unsigned long long best[kSlots];                         // exact arg-max key per slot
-    unsigned long long mbarBase, mbarDc, mbarDcLoad;
+    unsigned long long mbarBase, mbarBase2, mbarDc, mbarDcLoad;  // scores complete: base tiles 0-1 / base tiles 2-3 / resident tile
     unsigned long long full[kTStages], empty[kTStages];
     unsigned long long accFull[kTAccs], accEmpty[kTAccs];
     alignas(16) uint32_t approxMax[kSlots];                  // max |p~| per slot (float bits)
@@ -110,6 +110,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
         for (int t = 0; t < kTeams; ++t) {
             TeamSmem& X = s.team[t];
             mbarInit(&X.mbarBase, 1);
+            mbarInit(&X.mbarBase2, 1);
             mbarInit(&X.mbarDc, 1);
             mbarInit(&X.mbarDcLoad, 1);
             for (int i = 0; i < kTStages; ++i) mbarInit(&X.full[i], 1), mbarInit(&X.empty[i], 1);
@@ -367,13 +368,17 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                 const unsigned long long descD = umDesc(dAddr, kLbo, kSbo), descR = umDesc(rA, kLbo, kSbo);
                 const bool mmaTiming = p.debugTiming && blockIdx.x == 0 && team == 0;
                 const long long tm0 = mmaTiming ? clock64() : 0;
+                // one commit per pair of tiles: warp set 0 (tiles 0, 1) starts its epilogue while tiles 2, 3 are still being issued
 #pragma unroll
-                for (int t = 0; t < 4; ++t)
+                for (int t = 0; t < 4; ++t) {
                     for (int h = 0; h < nH; ++h)
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
                             ummaF16Elect(tm + t * 32, descD + ((t * 16 * kSbo + ks * kKStep) >> 4),
                                          descR + ((h * (kSlots * kN * 2) + ks * kKStep) >> 4), kIdescF16M128N32, (h | ks) ? 1u : 0u);
+                    if (t == 1) ummaCommitElect(&T.mbarBase);
+                    if (t == 3) ummaCommitElect(&T.mbarBase2);
+                }
                 {   // resident tile: KLT groups of atoms 0 and nBase-1 of the team's channel against every slot
                     if (dcLoadPending) mbarWait(&T.mbarDcLoad, (dcLoads - 1u) & 1u), dcLoadPending = false;
                     const unsigned long long descC = umDesc(warpUniform(smemAddr(s.dc[team])), kLbo, kSbo);
@@ -384,9 +389,9 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                                          descR + ((h * (kSlots * kN * 2) + ks * kKStep) >> 4), kIdescF16M128N32, (h | ks) ? 1u : 0u);
                 }
                 const long long tm1 = mmaTiming ? clock64() : 0;
-                ummaCommitElect(&T.mbarBase);
+                ummaCommitElect(&T.mbarDc);
                 if (mmaTiming) {  // timing only: how long the issue takes, and when the scores are complete
-                    mbarWait(&T.mbarBase, normalTrips & 1u);
+                    mbarWait(&T.mbarDc, normalTrips & 1u);
                     mmaIssue += tm1 - tm0;
                     mmaDone += clock64() - tm0;
                 }
@@ -437,7 +442,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             }
             const unsigned liveMask = __ballot_sync(kFullMask, T.bc[lane] >= 0 && !T.zeroRes[lane]);
             // ---- (a) base scores: per-slot maximum over this warp's two tiles ----
-            mbarWait(&T.mbarBase, normalTrips & 1u);
+            mbarWait(wset ? &T.mbarBase2 : &T.mbarBase, normalTrips & 1u);
             fenceAfter();
             MNENC_TICK(1)
             float lm0 = 0.0f, lm1 = 0.0f, lmDc = 0.0f;  // this warp's LOCAL maxima (lane L: slot L) of its two tiles / the resident tile
@@ -472,6 +477,8 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
             const bool dcRowOk = dcRow < s.detRows[dcAtom];
             const unsigned dcHas = __ballot_sync(kFullMask, lane < 16 && T.dcFirst[dcK][wset * 16 + (lane & 15)] != 0xFFFFu) & 0xFFFFu &
                                    (liveMask >> (wset * 16));
+            mbarWait(&T.mbarDc, normalTrips & 1u);  // every warp: the next trip's MMAs may only start once all have seen this one's
+            fenceAfter();
             if (dcHas) {
                 uint32_t raw[16];
                 tmemLoad16(tmemT + laneBase + kColDc + static_cast<uint32_t>(wset * 16), raw);
