@@ -271,10 +271,9 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
     long long tLast = 0;
     unsigned long long nItemsSum = 0, nCandSum = 0;
     unsigned long long nFlagSum = 0;
-    long long mmaIssue = 0, mmaDone = 0;
-    long long tBar[3] = {0, 0, 0};  // timing only: cycles thread 0 waits inside the three consumer barriers  // timing only: cycles of the two tmemLoad32 of phase (a)
+    long long mmaIssue = 0, mmaDone = 0;  // timing only: cycles of the two tmemLoad32 of phase (a)
+    const bool timing = p.debugTiming && tid == 0 && blockIdx.x == 0;
     const bool timing = p.debugTiming && tid == p.debugTiming - 1 && blockIdx.x == 0;  // MNENC_MP_TIMING=n: consumer thread n-1 reports
-#define MNENC_TICK(k)                     \
     if (timing) {                         \
         const long long now_ = clock64(); \
         tPhase[k] += now_ - tLast;        \
@@ -499,11 +498,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                 const float m = fmaxf(b0 ? w2[1] : w2[0], __shfl_xor_sync(kFullMask, b0 ? w2[0] : w2[1], 1));
                 if (lane < 16 && ((dcHas >> lane) & 1u)) atomicMax(&T.approxMax[wset * 16 + lane], __float_as_uint(m)), lmDc = m;
             }
-            {
-                const long long tb_ = timing ? clock64() : 0;
-                consumerBarrier();
-                if (timing) tBar[0] += clock64() - tb_;
-            }
+            consumerBarrier();
             MNENC_TICK(2)
             // ---- (b) rows that can still be the exact maximum -> candidate list. A slot can only have such a row in this
             // warp's part of a tile if the warp's LOCAL maximum of that slot is within 2 eps of the slot's global maximum:
@@ -574,11 +569,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                 __syncwarp();
                 if (lane == 0) mbarArrive(&T.accEmpty[acc]);
             }
-            {
-                const long long tb_ = timing ? clock64() : 0;
-                consumerBarrier();
-                if (timing) tBar[1] += clock64() - tb_;
-            }
+            consumerBarrier();
             MNENC_TICK(5)
             // ---- (d) exact re-score of the listed candidates, one per thread ----
             {
@@ -591,11 +582,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
                     atomicMax(&T.best[sl], makeKey(a, static_cast<int>(c.x >> 8)));
                 }
             }
-            {
-                const long long tb_ = timing ? clock64() : 0;
-                consumerBarrier();
-                if (timing) tBar[2] += clock64() - tb_;
-            }
+            consumerBarrier();
             MNENC_TICK(6)
             // ================= step C: select, quantise, update (MatchingPursuit.cpp:86-104), 8 threads per slot =================
             const int bc = T.bc[slot];
@@ -714,9 +701,6 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
     if (p.debugTiming && blockIdx.x == 0 && team == 0 && isMma && lane == 0 && normalTrips)
         printf("mp teams timing, MMA thread: base + resident MMAs per trip: %lld cycles to issue, %lld cycles until complete\n",
                mmaIssue / normalTrips, mmaDone / normalTrips);
-    if (timing && normalTrips)
-        printf("mp teams timing, CTA 0 team 0: cycles per trip inside the consumer barriers after (a) / (c) / (d): %lld / %lld / %lld\n",
-               tBar[0] / normalTrips, tBar[1] / normalTrips, tBar[2] / normalTrips);
     if (timing && normalTrips)
         printf("mp teams timing, CTA 0 thread %d: %u trips; cycles per trip: barrier %lld, baseMMA wait %lld, max+bar %lld, base filter %lld, "
                "resident %lld, streamed+bar %lld, cand+bar %lld, stepC %lld; per trip: streamed items %.1f, flagged columns of warp 0 in (b) %.1f, candidates %.1f\n",
