@@ -272,8 +272,8 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
     unsigned long long nItemsSum = 0, nCandSum = 0;
     unsigned long long nFlagSum = 0;
     long long mmaIssue = 0, mmaDone = 0;  // timing only: cycles of the two tmemLoad32 of phase (a)
-    const bool timing = p.debugTiming && tid == 0 && blockIdx.x == 0;
     const bool timing = p.debugTiming && tid == p.debugTiming - 1 && blockIdx.x == 0;  // MNENC_MP_TIMING=n: consumer thread n-1 reports
+#define MNENC_TICK(k)                     \
     if (timing) {                         \
         const long long now_ = clock64(); \
         tPhase[k] += now_ - tLast;        \
