@@ -272,7 +272,7 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
     unsigned long long nItemsSum = 0, nCandSum = 0;
     unsigned long long nFlagSum = 0;
     long long mmaIssue = 0, mmaDone = 0;  // timing only: cycles of the two tmemLoad32 of phase (a)
-    const bool timing = p.debugTiming && tid == p.debugTiming - 1 && blockIdx.x == 0;  // MNENC_MP_TIMING=n: consumer thread n-1 reports
+    const bool timing = p.debugTiming && tid == 0 && blockIdx.x == 0;
 #define MNENC_TICK(k)                     \
     if (timing) {                         \
         const long long now_ = clock64(); \
@@ -702,9 +702,9 @@ __global__ void __launch_bounds__(kThreadsV4, 1) matchingPursuitTeamsKernel(cons
         printf("mp teams timing, MMA thread: base + resident MMAs per trip: %lld cycles to issue, %lld cycles until complete\n",
                mmaIssue / normalTrips, mmaDone / normalTrips);
     if (timing && normalTrips)
-        printf("mp teams timing, CTA 0 thread %d: %u trips; cycles per trip: barrier %lld, baseMMA wait %lld, max+bar %lld, base filter %lld, "
+        printf("mp teams timing, CTA 0 team 0: %u trips; cycles per trip: barrier %lld, baseMMA wait %lld, max+bar %lld, base filter %lld, "
                "resident %lld, streamed+bar %lld, cand+bar %lld, stepC %lld; per trip: streamed items %.1f, flagged columns of warp 0 in (b) %.1f, candidates %.1f\n",
-               tid, normalTrips, tPhase[0] / normalTrips, tPhase[1] / normalTrips, tPhase[2] / normalTrips, tPhase[3] / normalTrips,
+               normalTrips, tPhase[0] / normalTrips, tPhase[1] / normalTrips, tPhase[2] / normalTrips, tPhase[3] / normalTrips,
                tPhase[4] / normalTrips, tPhase[5] / normalTrips, tPhase[6] / normalTrips, tPhase[7] / normalTrips,
                double(nItemsSum) / normalTrips, double(nFlagSum) / normalTrips, double(nCandSum) / normalTrips);
 #undef MNENC_TICK
