@@ -401,7 +401,7 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     p.epsRel16 = (c->mpMode == 3 && !c->residualLo) ? c->epsRel16Hi : c->epsRel16;
     p.residualLo = c->residualLo;
     p.epsAbs16 = c->epsAbs16;
-    p.debugTiming = std::getenv("MNENC_MP_TIMING") ? std::max(1, std::atoi(std::getenv("MNENC_MP_TIMING"))) : 0;  // n: thread n-1 of CTA 0 reports
+    p.debugTiming = std::getenv("MNENC_MP_TIMING") != nullptr;
     if (c->mpMode == 3) CU(launchMatchingPursuitTeams(p, c->numSMs, c->stream));
     else if (c->mpMode == 2) CU(launchMatchingPursuitF16(p, c->numSMs, c->stream));
     else if (c->mpMode == 1) CU(launchMatchingPursuitTc(p, c->numSMs, c->stream));
