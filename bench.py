@@ -277,11 +277,11 @@ def run_ours(args):
                     "ms_per_step": round(dt_e2e / args.steps * 1e3, 3)},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "matchingPursuitTeamsKernel", "bound": "tensor", "achieved": round(achieved, 3), "peak": round(tensor_peak, 1),
-                         "unit": "TFLOP/s", "frac": round(achieved / tensor_peak, 4), "traffic": 236.1e6,
+                         "unit": "TFLOP/s", "frac": round(achieved / tensor_peak, 4), "traffic": 236.9e6,
                          "note": "algorithmic flops (SURVEY.md 8d: 2*64*dictionary height per greedy iteration, counted by the kernel) / "
                                  f"CUDA-event time of the kernel on its own stream (one-image-at-a-time pass, no other lane on the GPU); peak = {peak_src}. The kernel is latency bound "
                                  "(N = 32 slots per MMA, exact re-score and residual update between MMAs), see "
-                                 "profiles/r01_mp_teams_v5_ncu.md; traffic = dram read+write bytes of one launch from that ncu capture "
+                                 "profiles/r01_mp_teams_v6_ncu.md; traffic = dram read+write bytes of one launch from that ncu capture "
                                  "(algorithmic: 48.3 MB pixels + 37.5 MB dictionary images + 98 MB symbols)",
                          "frac_of_fp32_issue_peak": round(achieved / fp32_peak, 4),
                          "ms_per_launch": round(mp_ms, 3), "gflop_per_launch": round(flops / 1e9, 2)},
