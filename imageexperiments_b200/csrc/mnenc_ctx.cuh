@@ -91,21 +91,6 @@ struct Overlay {  // host-written bits (headers, EOF codes) OR-ed into the packe
 // ORs the overlays into the byte stream `res` (MSB-first bit positions).
 void mergeOverlays(uint8_t* res, const std::vector<Overlay>& overlays);
 
-// Copies `n` bytes into freshly malloc'ed (not yet faulted-in) memory on the pool's threads: for a stream of tens of MB the
-// page faults of a single-threaded memcpy cost more than the D2H copy itself.
-inline void parallelCopy(HostPool* pool, uint8_t* dst, const uint8_t* src, size_t n) {
-    const size_t kChunk = size_t(1) << 20;
-    if (!pool || pool->size() == 1 || n <= 2 * kChunk) {
-        std::memcpy(dst, src, n);
-        return;
-    }
-    const int chunks = static_cast<int>((n + kChunk - 1) / kChunk);
-    pool->parallelFor(chunks, [&](int i) {
-        const size_t o = static_cast<size_t>(i) * kChunk;
-        std::memcpy(dst + o, src + o, std::min(kChunk, n - o));
-    });
-}
-
 // Result buffers (the `.mn` stream handed to the caller) come from a process-wide pool of PINNED host buffers, recycled by
 // mnenc_free(): the D2H copy of the packed stream lands directly in the caller's buffer — no staging copy, no page faults
 // of a fresh malloc (for a 56 MB stream those cost more than the whole back end).
@@ -139,7 +124,7 @@ struct mnenc_ctx {
         maxSym, entries, nEntries, entryCodes, codeTable, outWords;
     uint32_t entryCap = 0;
     bool histReady = false;
-    mnenc::PinBuf hTotals, hSeqTable, hEntries, hNEntries, hEntryCodes, hCodeTable, hOut, hStats, hRgb;
+    mnenc::PinBuf hTotals, hSeqTable, hEntries, hNEntries, hEntryCodes, hCodeTable, hStats;
     std::unique_ptr<mnenc::HostPool> pool;  // code-table builds of one image run on these threads
     // accounting
     float ms[8] = {};

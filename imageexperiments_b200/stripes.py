@@ -59,7 +59,7 @@ class TorchComm:
         t = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1))
         if self.backend == "nccl":
             t = t.cuda(device)
-        out = torch.empty((self.world, t.numel()), dtype=torch.uint8, device=t.device)
+        out = torch.empty(self.world * t.numel(), dtype=torch.uint8, device=t.device)  # flat: gloo accepts only the concatenated form
         self.dist.all_gather_into_tensor(out, t, group=self.group)
         return out.cpu().numpy().view(a.dtype).reshape((self.world,) + a.shape)
 

@@ -64,3 +64,28 @@ def test_gpu_entry_points_fail_loudly_without_device():
     rc = L.mnenc_create(C.byref(h), 0, 32, 8, p(base), 510, p(rows), p(det), p(det), p(det))
     assert rc == -2, "must report MNENC_ERR_CUDA, never fall back to a CPU path"
     assert L.mnenc_last_error()
+
+
+def test_batch_and_stripe_entry_points_reject_bad_arguments():
+    """No context can exist without a GPU, so the batch / stripe entry points must refuse a null context (MNENC_ERR_ARG)
+    instead of touching the device; the product has no CPU path behind them."""
+    L = _lib.load()
+    out, n = C.c_void_p(), C.c_size_t()
+    one = (C.c_void_p * 1)()
+    sz = (C.c_size_t * 1)(8)
+    assert L.mnenc_encode_batch_rgb8(None, 1, one, 0, sz, sz, sz, one, sz) == -1
+    rec = np.zeros(99, np.uint32)
+    assert L.mnenc_stripe_begin(None, None, 0, 8, 8, 24, 0, 1, 0, 1, rec.ctypes.data_as(C.c_void_p)) == -1
+    for f in (L.mnenc_stripe_rle, ):
+        assert f(None, rec.ctypes.data_as(C.c_void_p), rec.ctypes.data_as(C.c_void_p)) == -1
+    assert L.mnenc_stripe_plan(None, rec.ctypes.data_as(C.c_void_p)) == -1
+    assert L.mnenc_stripe_finish(None, C.byref(out), C.byref(n)) == -1
+    L.mnenc_free(None)  # releasing nothing is allowed
+
+
+def test_python_host_fails_loudly_without_library(monkeypatch, tmp_path):
+    """The Python mirror has no fallback either: a missing libmnenc.so is an error that names the build command."""
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "libmnenc.so"))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        _lib.load()
