@@ -262,6 +262,26 @@ class OracleLib:
         L.mno_write_file.argtypes = [C.c_int, C.c_int, _sz, _sz, _vp, _vp, _vp, _vp]
         L.mno_encode.restype = _vp
         L.mno_encode.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp]
+        L.mno_parse.restype = C.c_int
+        L.mno_parse.argtypes = [_vp, _sz] + [_vp] * 8
+        L.mno_decode.restype = C.c_int
+        L.mno_decode.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp]
+
+    def parse(self, data: bytes):
+        """Same result layout as RefLib.parse; raises ValueError on an invalid stream."""
+        buf = np.frombuffer(data, np.uint8)
+        K, bs, w, h, nl = _sz(), _sz(), _sz(), _sz(), _sz()
+        lengths, streams = _vp(), _vp()
+        sizes = np.zeros(6 * 64, np.uint64)
+        if self.L.mno_parse(_ptr(buf), len(data), C.byref(K), C.byref(bs), C.byref(w), C.byref(h), C.byref(lengths), C.byref(nl),
+                            _ptr(sizes), C.byref(streams)):
+            raise ValueError("invalid .mn stream")
+        sizes = sizes[: 6 * K.value].astype(np.int64)
+        ln = _take(self.L.mno_free, lengths, nl.value, np.uint16)
+        flat = _take(self.L.mno_free, streams, int(sizes.sum()), np.uint16)
+        offs = np.concatenate([[0], np.cumsum(sizes)])
+        return dict(K=K.value, bs=bs.value, w=w.value, h=h.value, lengths=ln,
+                    streams=[flat[offs[i]:offs[i + 1]] for i in range(len(sizes))])
 
     # -- dictionary handle ---------------------------------------------------------------------------
     def create(self, d: Dictionary):
@@ -358,3 +378,11 @@ class _OracleCtx:
         n = _u64()
         p = self.lib.L.mno_encode(self.h, _ptr(rgb), w, h, 3 * w, C.byref(n))
         return _take(self.lib.L.mno_free, p, n.value, np.uint8).tobytes()
+
+    def decode(self, data: bytes) -> np.ndarray:
+        buf = np.frombuffer(data, np.uint8)
+        out, w, h = _vp(), _sz(), _sz()
+        rc = self.lib.L.mno_decode(self.h, _ptr(buf), len(data), C.byref(out), C.byref(w), C.byref(h))
+        if rc:
+            raise ValueError("invalid .mn stream" if rc == -1 else "block size differs from the dictionary's")
+        return _take(self.lib.L.mno_free, out, w.value * h.value * 3, np.uint8).reshape(h.value, w.value, 3)

@@ -507,3 +507,296 @@ uint8_t* mno_encode(void* h, const uint8_t* rgb, size_t w, size_t hgt, size_t st
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// Decoder: restates readCompressedFast (CompressedImage.cpp:709-782), decodeImageFast (:837-889),
+// FromCoeffsDynamicFast (MatchingPursuit.cpp:152-169), huffmanDecode (Huffman.cpp:173-244), runLengthDecode (:281-307),
+// readGolombCode / readEliasFanoSequenceCode (BitBuffer.cpp:243-258, 319-343), RGBFromYUV (ImageHelper/src/misc.cpp:28-36).
+// Pinned against the reference's own reader/decoder in tests/test_oracle.py (symbols and pixels, bit-exact).
+// ---------------------------------------------------------------------------------------------------
+namespace {
+
+struct DecodeError {};
+
+// BitBuffer.h:112-114
+inline int32_t unzz(uint32_t x) { return static_cast<int32_t>((x >> 1) ^ -(static_cast<int64_t>(x) & 1)); }
+
+// BitBuffer::Load + ReadBits (BitBuffer.cpp:112-156): MSB-first; a read past the end is clamped to the bits that remain.
+struct BitsIn {
+    const uint8_t* p;
+    uint64_t n, pos = 0;
+    uint64_t remaining() const { return n - pos; }
+    uint64_t read(int width) {
+        if (static_cast<uint64_t>(width) > remaining()) width = static_cast<int>(remaining());
+        uint64_t v = 0;
+        for (int i = 0; i < width; ++i, ++pos) v = (v << 1) | ((p[pos >> 3] >> (7 - (pos & 7))) & 1u);
+        return v;
+    }
+};
+
+// BitBuffer.cpp:243-258
+uint32_t golombGet(BitsIn& in, uint32_t M) {
+    uint32_t q = 0;
+    while (in.read(1) != 0) {
+        ++q;
+        if (in.remaining() == 0) throw DecodeError{};  // (the reference would spin on a truncated stream)
+    }
+    const uint32_t b = std::bit_width(M), limit = (1u << (b + 1)) - M;
+    const uint32_t rem1 = static_cast<uint32_t>(in.read(b));
+    const uint32_t rem = rem1 < limit ? rem1 : (rem1 << 1) + static_cast<uint32_t>(in.read(1)) - limit;
+    return q * M + rem;
+}
+
+// BitBuffer.cpp:319-343
+std::vector<uint16_t> eliasFanoGet(BitsIn& in, size_t n, uint16_t maxSymbol) {
+    std::vector<uint16_t> r(n);
+    if (n == 0) return r;
+    const uint32_t m = std::bit_width(maxSymbol), nb = std::bit_width(static_cast<uint32_t>(n)), lb = m >= nb ? m - nb : 0;
+    uint16_t bucket = 0;
+    for (uint16_t& s : r) {
+        if (in.remaining() == 0) throw DecodeError{};
+        while (in.read(1) == 0) {
+            ++bucket;
+            if (in.remaining() == 0) throw DecodeError{};
+        }
+        s = static_cast<uint16_t>(bucket << lb);
+    }
+    for (uint16_t& s : r) s |= static_cast<uint16_t>(in.read(lb));
+    return r;
+}
+
+// Huffman.cpp:173-244
+void huffmanGet(BitsIn& in, std::vector<uint16_t>& out) {
+    const uint8_t maxLength = static_cast<uint8_t>(in.read(8));
+    std::vector<uint16_t> lengthCounts;
+    uint16_t total = 0;
+    for (int len = 1; len <= maxLength; ++len) {
+        const uint16_t c = static_cast<uint16_t>(in.read(16));
+        total = static_cast<uint16_t>(total + c);
+        lengthCounts.push_back(c);
+    }
+    const uint8_t width = static_cast<uint8_t>(in.read(8));
+    const uint16_t mask = static_cast<uint16_t>((1u << width) - 1u);
+    std::vector<uint16_t> symbols;
+    for (uint16_t rangeLength : lengthCounts) {
+        if (eliasFanoBound(rangeLength, mask) < static_cast<uint32_t>(rangeLength) * width) {
+            std::vector<uint16_t> part = eliasFanoGet(in, rangeLength, mask);
+            symbols.insert(symbols.end(), part.begin(), part.end());
+        } else {
+            for (int i = 0; i < rangeLength; ++i) symbols.push_back(static_cast<uint16_t>(in.read(width)));
+        }
+    }
+    struct Entry {
+        uint32_t symbol;
+        uint8_t len;
+    };
+    std::unordered_map<uint32_t, Entry> codeMap;
+    uint8_t length = 1, prevLength = 0;
+    uint32_t code = 0;
+    for (uint16_t k = 0; k < total; ++k) {
+        while (lengthCounts.at(static_cast<size_t>(length) - 1) == 0) ++length;
+        --lengthCounts[static_cast<size_t>(length) - 1];
+        uint32_t symbol = symbols.at(k);
+        if (length != prevLength) code <<= (length - prevLength);
+        if (k == total - 1) {
+            if (symbol != mask) throw DecodeError{};
+            symbol = 0xFFFFFFFFu;
+        }
+        codeMap[code] = Entry{symbol, length};
+        ++code;
+        prevLength = length;
+    }
+    uint32_t decode = 0;
+    uint8_t bitcount = 0;
+    while (in.remaining() > 0) {
+        decode = (decode << 1) | static_cast<uint32_t>(in.read(1));
+        ++bitcount;
+        auto it = codeMap.find(decode);
+        if (it != codeMap.end() && it->second.len == bitcount) {
+            if (it->second.symbol == 0xFFFFFFFFu) return;
+            out.push_back(static_cast<uint16_t>(it->second.symbol));
+            decode = 0;
+            bitcount = 0;
+        }
+    }
+    throw DecodeError{};
+}
+
+// CompressedImage.cpp:392-401
+void huffmanOrGolombGet(BitsIn& in, size_t length, std::vector<uint16_t>& out) {
+    if (in.read(1) == 0) {
+        huffmanGet(in, out);
+    } else {
+        const uint32_t m = static_cast<uint32_t>(in.read(16));
+        if (m == 0) throw DecodeError{};  // (the reference divides by zero in the encoder only; m = 0 is never written)
+        for (size_t i = 0; i < length; ++i) out.push_back(static_cast<uint16_t>(golombGet(in, m)));
+    }
+}
+
+// Huffman.cpp:281-307
+std::vector<uint16_t> unrle(const std::vector<uint16_t>& d) {
+    std::vector<uint16_t> r;
+    uint16_t prev = 0;
+    bool pending = false, newRun = true;
+    for (uint16_t v : d) {
+        if (pending) {
+            r.insert(r.end(), v, prev);
+            pending = false;
+            newRun = true;
+        } else {
+            r.push_back(v);
+            if (v == prev && !newRun) pending = true;
+            newRun = false;
+            prev = v;
+        }
+    }
+    return r;
+}
+
+struct Parsed {
+    size_t K = 0, bs = 0, w = 0, h = 0;
+    float quant[3][64] = {};
+    std::vector<uint16_t> lengths;
+    std::vector<std::vector<uint16_t>> codes;
+};
+
+// CompressedImage.cpp:709-782
+void parseFile(const uint8_t* bytes, size_t n, Parsed& P) {
+    BitsIn in{bytes, 8ull * n};
+    if (in.read(32) != 0x4D4E3234u) throw DecodeError{};
+    P.w = in.read(32);
+    P.h = in.read(32);
+    P.K = in.read(8);
+    P.bs = in.read(8);
+    if (P.K == 0 || P.K > 64 || P.bs == 0) throw DecodeError{};
+    for (int c = 0; c < 3; ++c)
+        for (size_t i = 0; i < P.K; ++i) P.quant[c][i] = static_cast<float>(in.read(16));
+    const size_t K = P.K, patch = 3 * ((P.w + P.bs - 1) / P.bs) * ((P.h + P.bs - 1) / P.bs);
+    huffmanOrGolombGet(in, patch, P.lengths);
+    P.codes.assign(6 * K, {});
+    for (size_t i = 0; i < 6 * K; ++i) {
+        if (in.read(1) == 1) {
+            const size_t codeLength = in.read(32);
+            std::vector<uint16_t> comp;
+            huffmanOrGolombGet(in, codeLength, comp);
+            P.codes[i] = unrle(comp);
+        } else {
+            const size_t layer = (i / 2) / K, depth = (i / 2) % K;
+            size_t layerLength = 0;
+            for (size_t o = 0; o < P.lengths.size() / 3; ++o) layerLength += P.lengths[3 * o + layer] > depth;
+            huffmanOrGolombGet(in, layerLength, P.codes[i]);
+        }
+    }
+    for (int ch = 0; ch < 3; ++ch) {  // undo the DC delta chains, :766-781
+        int32_t acc = 0;
+        for (uint16_t& c : P.codes[2 * K * ch + 1]) {
+            acc = unzz(c) + acc;
+            c = static_cast<uint16_t>(acc);
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+// Same output layout as mnref_parse (oracle/ref_driver.cpp). Returns 0, or -1 on an invalid stream.
+int mno_parse(const uint8_t* bytes, size_t n, size_t* K, size_t* bs, size_t* w, size_t* h, uint16_t** lengths, size_t* nLengths,
+              size_t* streamSizes, uint16_t** streams) {
+    Parsed P;
+    try {
+        parseFile(bytes, n, P);
+    } catch (...) {
+        return -1;
+    }
+    *K = P.K, *bs = P.bs, *w = P.w, *h = P.h;
+    *nLengths = P.lengths.size();
+    *lengths = static_cast<uint16_t*>(std::malloc(P.lengths.size() * 2 + 2));
+    std::memcpy(*lengths, P.lengths.data(), P.lengths.size() * 2);
+    size_t total = 0;
+    for (size_t i = 0; i < P.codes.size(); ++i) total += (streamSizes[i] = P.codes[i].size());
+    *streams = static_cast<uint16_t*>(std::malloc(total * 2 + 2));
+    size_t o = 0;
+    for (const auto& s : P.codes) {
+        std::memcpy(*streams + o, s.data(), s.size() * 2);
+        o += s.size();
+    }
+    return 0;
+}
+
+// decodeImageFast (CompressedImage.cpp:837-889) with the dictionary of `h` (block size and atoms; the quantisation tables
+// come from the file, as in readCompressedFast :727-736). rgbOut: malloc'ed packed RGB8, row-major.
+int mno_decode(void* h, const uint8_t* bytes, size_t n, uint8_t** rgbOut, size_t* wOut, size_t* hOut) {
+    const Dict& D = static_cast<mno_dict*>(h)->d;
+    Parsed P;
+    try {
+        parseFile(bytes, n, P);
+    } catch (...) {
+        return -1;
+    }
+    if (static_cast<int>(P.bs) != D.bs) return -2;
+    const size_t K = P.K, bs = P.bs, N = bs * bs, w = P.w, hgt = P.h;
+    uint8_t* out = static_cast<uint8_t*>(std::calloc(w * hgt * 3 + 1, 1));
+    std::vector<size_t> offsets(3 * K, 0);
+    size_t lengthOffset = 0;
+    std::vector<float> dec(3 * N);
+    try {
+        for (size_t x = 0; x < w; x += bs)
+            for (size_t y = 0; y < hgt; y += bs) {
+                for (int ch = 0; ch < 3; ++ch) {
+                    const int count = P.lengths.at(lengthOffset++);
+                    float* r = dec.data() + ch * N;
+                    std::fill(r, r + N, 0.0f);
+                    // FromCoeffsDynamicFast (MatchingPursuit.cpp:152-169) on the dictionary dynamicBasisFast builds from ALL `count`
+                    // picks (CompressedImage.cpp:252-289): base atoms, then the detail group of every pick < nBase, in pick order.
+                    int choice = 0;
+                    std::vector<int> groups;
+                    std::vector<int> abs(count);
+                    for (int i = 0; i < count; ++i) {
+                        const uint16_t deltaId = P.codes[2 * K * ch + 2 * i].at(offsets[K * ch + i]);
+                        choice = i ? choice + unzz(deltaId) : static_cast<int>(deltaId);
+                        abs[i] = choice;
+                        if (choice < D.nBase) groups.push_back(choice);  // a negative index makes the reference read out of range
+                    }
+                    for (int i = 0; i < count; ++i) {
+                        const uint16_t intCoeff = P.codes[2 * K * ch + 2 * i + 1].at(offsets[K * ch + i]++);
+                        const float coeff = P.quant[ch][i] * static_cast<float>(unzz(intCoeff));
+                        const float* row = nullptr;
+                        int idx = abs[i];
+                        if (idx < 0) throw DecodeError{};
+                        if (idx < D.nBase) {
+                            row = D.base + static_cast<size_t>(idx) * N;
+                        } else {
+                            idx -= D.nBase;
+                            for (int g : groups) {
+                                if (idx < D.rows[g]) {
+                                    row = D.detail[ch] + (D.rowOffset[g] + idx) * N;
+                                    break;
+                                }
+                                idx -= D.rows[g];
+                            }
+                            if (!row) throw DecodeError{};
+                        }
+                        for (size_t j = 0; j < N; ++j) r[j] = r[j] + coeff * row[j];  // results += coeff * dictionary.row(choice)
+                    }
+                }
+                for (size_t dx = 0; dx < bs; ++dx)
+                    for (size_t dy = 0; dy < bs; ++dy) {
+                        const size_t u = x + dx, v = y + dy;
+                        if (u >= w || v >= hgt) continue;
+                        const double yy = dec[dx + bs * dy], uu = dec[N + dx + bs * dy], vv = dec[2 * N + dx + bs * dy];
+                        uint8_t* px = out + (v * w + u) * 3;  // misc.cpp:28-36
+                        px[0] = static_cast<uint8_t>(std::clamp(std::round(yy + 1.13983 * vv), 0.0, 255.0));
+                        px[1] = static_cast<uint8_t>(std::clamp(std::round(yy - 0.39466 * uu - 0.58060 * vv), 0.0, 255.0));
+                        px[2] = static_cast<uint8_t>(std::clamp(std::round(yy + 2.03211 * uu), 0.0, 255.0));
+                    }
+            }
+    } catch (...) {
+        std::free(out);
+        return -1;
+    }
+    *rgbOut = out, *wOut = w, *hOut = hgt;
+    return 0;
+}
+
+}  // extern "C"
