@@ -185,6 +185,65 @@ def encodeImageBatch(images, context: CompressionContextFast, zero_copy: bool = 
     return [_take(_vp(outs[i]), sizes[i]) for i in range(n)]
 
 
+def _stream(data):
+    """bytes / bytearray / MnBuffer / uint8 array -> (pointer, size, keep-alive)."""
+    if isinstance(data, MnBuffer):
+        return C.cast(data.array, _vp), len(data), data
+    a = np.frombuffer(data, np.uint8) if not isinstance(data, np.ndarray) else np.ascontiguousarray(data, np.uint8)
+    return _p(a), a.size, a
+
+
+def decodeImageFast(data, context: CompressionContextFast, out=None, zero_copy: bool = False):
+    """compressed::decodeImageFast (CompressedImage.cpp:837-889): `.mn` stream -> HxWx3 uint8 pixels, bit for bit those of the
+    reference's decoder. ``data``: bytes, MnBuffer or uint8 array. The dictionary is the context's, the quantisation tables the
+    stream's. ``out``: optional CUDA torch uint8 tensor [H, W, 3] (contiguous) that receives the pixels on the GPU (returned);
+    otherwise a numpy array (``zero_copy``: a view of the library's pinned buffer, kept alive by the array)."""
+    L = _lib.load()
+    ptr, n, keep = _stream(data)
+    w, h = C.c_size_t(), C.c_size_t()
+    if out is not None:
+        if not out.is_cuda or str(out.dtype) != "torch.uint8" or out.dim() != 3 or out.shape[2] != 3 or not out.is_contiguous():
+            raise ValueError("expected a contiguous CUDA HxWx3 uint8 tensor")
+        if out.device.index != context.device:
+            raise ValueError("tensor is on another device than the context")
+        _lib.check(L.mnenc_decode_rgb8_device(context._h, ptr, n, _vp(out.data_ptr()), out.numel(), 3 * out.shape[1], C.byref(w), C.byref(h)))
+        if (h.value, w.value) != tuple(out.shape[:2]):
+            raise ValueError(f"stream holds a {w.value}x{h.value} image, the tensor is {out.shape[1]}x{out.shape[0]}")
+        return out
+    rgb = _vp()
+    _lib.check(L.mnenc_decode_rgb8(context._h, ptr, n, C.byref(rgb), C.byref(w), C.byref(h)))
+    buf = MnBuffer(rgb, 3 * w.value * h.value)
+    if not zero_copy:
+        return np.frombuffer(buf.array, np.uint8).reshape(h.value, w.value, 3).copy()
+    buf.array._owner = buf  # numpy keeps the ctypes array alive, the array keeps the pinned block from being recycled
+    return np.frombuffer(buf.array, np.uint8).reshape(h.value, w.value, 3)
+
+
+def streamInfo(data) -> dict:
+    """Header of a `.mn` stream (CompressedImage.cpp:721-736): width, height, K, blockSize, Quant [3K]. Host only."""
+    ptr, n, keep = _stream(data)
+    w, h, K, bs = C.c_size_t(), C.c_size_t(), C.c_int(), C.c_int()
+    q = np.zeros(96, np.float32)
+    _lib.check(_lib.load().mnenc_stream_info(ptr, n, C.byref(w), C.byref(h), C.byref(K), C.byref(bs), _p(q)))
+    return dict(width=w.value, height=h.value, K=K.value, blockSize=bs.value, Quant=q[: 3 * K.value].copy())
+
+
+def parseStream(data) -> dict:
+    """Debug tap, host only: compressed::readCompressedFast (CompressedImage.cpp:709-782) -> lengths [3*nblocks] and the 6K
+    symbol streams (run lengths expanded, DC chains undone)."""
+    L = _lib.load()
+    info = streamInfo(data)
+    ptr, n, keep = _stream(data)
+    nb = ((info["width"] + 7) // 8) * ((info["height"] + 7) // 8)
+    lengths = np.zeros(3 * nb, np.uint16)
+    offs = np.zeros(6 * info["K"] + 1, np.uint64)
+    _lib.check(L.mnenc_debug_parse(ptr, n, _p(lengths), lengths.size, _p(offs), None, 0))
+    symbols = np.zeros(int(offs[-1]) + 1, np.uint16)
+    _lib.check(L.mnenc_debug_parse(ptr, n, _p(lengths), lengths.size, _p(offs), _p(symbols), symbols.size))
+    o = offs.astype(np.int64)
+    return dict(info, lengths=lengths, streams=[symbols[o[i]:o[i + 1]] for i in range(len(o) - 1)])
+
+
 def lastSymbols(context: CompressionContextFast, width: int, height: int) -> Tuple[np.ndarray, np.ndarray]:
     """Debug tap: (counts [nblocks,3], pairs [nblocks,3,K,2]) of the last encode, column-major block order."""
     nb = ((width + 7) // 8) * ((height + 7) // 8)

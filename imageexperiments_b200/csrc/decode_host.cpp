@@ -1,0 +1,364 @@
+// Host side of the decoder: the `.mn` bit stream back into `lengths` and the 6K symbol streams.
+// Replaces, on the decode path,
+//   compressed::readCompressedFast      CompressionLib/src/CompressedImage.cpp:709-782
+//   compressed::readHuffmanOrGolomb     CompressionLib/src/CompressedImage.cpp:392-401
+//   huffman::huffmanDecode              CompressionLib/src/Huffman.cpp:173-244
+//   huffman::runLengthDecode            CompressionLib/src/Huffman.cpp:281-307
+//   bitbuffer::readGolombCode           CompressionLib/src/BitBuffer.cpp:243-258
+//   bitbuffer::readEliasFanoSequenceCode CompressionLib/src/BitBuffer.cpp:319-343
+//
+// Why this stage stays on the host: the format has no stream offsets — a Huffman payload ends at its pseudo-EOF code, so
+// sequence i + 1 starts wherever decoding sequence i stopped. The bit stream of one image is one serial chain; a GPU
+// thread would walk it an order of magnitude slower than a CPU core. The reference walks it bit by bit through an
+// unordered_map (Huffman.cpp:228-241); here canonical codes are resolved by a 12-bit table plus first-code compares,
+// symbols go straight into their final place in pinned memory, and the pixels are rebuilt on the GPU (decode_kernels.cu).
+//
+// Every length and count that the reference trusts is checked: a damaged stream gives an error, never an out-of-range access.
+#include <bit>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "mnenc_internal.h"
+
+namespace mnenc {
+namespace {
+
+struct Bad {
+    const char* why;
+};
+
+// MSB-first reader over the caller's bytes. `buf` holds `cnt` valid bits, left aligned; reading past the end yields zeros
+// (BitBuffer::PeekBits clamps the same way) and is reported by overrun().
+class BitReader {
+public:
+    BitReader(const uint8_t* p, size_t n) : base_(p), ptr_(p), end_(p + n) {}
+    uint64_t peek(int n) {  // n in 1..56
+        if (cnt_ < n) refill();
+        return buf_ >> (64 - n);
+    }
+    void skip(int n) {
+        buf_ <<= n;
+        cnt_ -= n;
+    }
+    uint64_t read(int n) {  // n in 0..56
+        if (n == 0) return 0;
+        const uint64_t v = peek(n);
+        skip(n);
+        return v;
+    }
+    uint32_t read32() {
+        const uint32_t hi = static_cast<uint32_t>(read(16));
+        return hi << 16 | static_cast<uint32_t>(read(16));
+    }
+    bool overrun() const { return cnt_ < 0; }
+    uint64_t position() const { return static_cast<uint64_t>(ptr_ - base_) * 8 - static_cast<uint64_t>(cnt_); }
+    // number of leading one bits (unary quotient of a Golomb code), consumed together with the terminating zero
+    uint32_t readUnaryOnes() {
+        uint32_t q = 0;
+        for (;;) {
+            if (cnt_ < 32) refill();
+            if (cnt_ <= 0) throw Bad{"unary code runs past the end of the stream"};
+            const int valid = cnt_ < 56 ? cnt_ : 56;
+            const uint64_t inv = ~buf_ | ((1ull << (64 - valid)) - 1ull);  // a zero bit, or the end of the valid window
+            const int ones = std::countl_zero(inv);
+            if (ones < valid) {
+                skip(ones + 1);
+                return q + static_cast<uint32_t>(ones);
+            }
+            skip(valid);
+            q += static_cast<uint32_t>(valid);
+            if (q > (1u << 20)) throw Bad{"unary code too long"};
+        }
+    }
+    // number of leading zero bits before the next one bit (Elias-Fano bucket advance), consumed together with the one
+    uint32_t readUnaryZeros() {
+        uint32_t q = 0;
+        for (;;) {
+            if (cnt_ < 32) refill();
+            if (cnt_ <= 0) throw Bad{"bucket code runs past the end of the stream"};
+            const int valid = cnt_ < 56 ? cnt_ : 56;
+            const uint64_t w = buf_ & ~((1ull << (64 - valid)) - 1ull);
+            const int zeros = w ? std::countl_zero(w) : 64;
+            if (zeros < valid) {
+                skip(zeros + 1);
+                return q + static_cast<uint32_t>(zeros);
+            }
+            skip(valid);
+            q += static_cast<uint32_t>(valid);
+            if (q > 65536u) throw Bad{"bucket code too long"};
+        }
+    }
+
+private:
+    void refill() {
+        if (cnt_ < 0) return;  // already past the end: keep delivering zeros
+        if (end_ - ptr_ >= 8) {
+            uint64_t w;
+            std::memcpy(&w, ptr_, 8);
+            w = __builtin_bswap64(w);
+            buf_ |= cnt_ ? w >> cnt_ : w;
+            const int take = (63 - cnt_) >> 3;  // whole bytes that fit
+            ptr_ += take;
+            cnt_ += take * 8;
+            if (cnt_ < 64) buf_ &= ~((1ull << (64 - cnt_)) - 1ull);  // drop the partial byte; it is read again next time
+        } else {
+            while (cnt_ <= 56 && ptr_ < end_) {
+                buf_ |= static_cast<uint64_t>(*ptr_++) << (56 - cnt_);
+                cnt_ += 8;
+            }
+        }
+    }
+    const uint8_t* base_;
+    const uint8_t* ptr_;
+    const uint8_t* end_;
+    uint64_t buf_ = 0;
+    int cnt_ = 0;
+};
+
+// BitBuffer.cpp:345-354 (decision bound, as in the encoder)
+inline uint32_t eliasFanoBound(uint32_t n, uint32_t maxSymbol) {
+    if (n == 0) return 0;
+    const uint32_t m = std::bit_width(maxSymbol), nb = std::bit_width(n), lb = m >= nb ? m - nb : 0;
+    return n * (1 + lb) + (1u << (m - lb)) - 1;
+}
+
+inline int32_t unzigzag(uint32_t x) { return static_cast<int32_t>((x >> 1) ^ -(static_cast<int64_t>(x) & 1)); }  // BitBuffer.h:112-114
+
+constexpr int kLutBits = 12;
+constexpr int kMaxCodeLen = 48;
+
+// Canonical Huffman table of one sequence (Huffman.cpp:176-226): counts per length, symbols in (length, symbol) order, the
+// last one being the pseudo-EOF written as the all-ones `mask`.
+struct HuffTable {
+    int maxLen = 0;
+    uint32_t total = 0;
+    std::vector<uint16_t> symbols;           // [total]; index total-1 = EOF
+    uint64_t firstCode[kMaxCodeLen + 2] = {};  // first code of each length
+    uint32_t firstIndex[kMaxCodeLen + 2] = {};
+    uint32_t count[kMaxCodeLen + 2] = {};
+    std::vector<uint32_t> lut;               // [1 << kLutBits]: index << 8 | length, 0 = not resolved by the table
+
+    void read(BitReader& in) {
+        maxLen = static_cast<int>(in.read(8));
+        if (maxLen > kMaxCodeLen) throw Bad{"Huffman code longer than 48 bits"};
+        total = 0;
+        for (int len = 1; len <= maxLen; ++len) total += (count[len] = static_cast<uint32_t>(in.read(16)));
+        if (total == 0 || total > 65536u) throw Bad{"Huffman table without pseudo-EOF or with too many symbols"};
+        const int width = static_cast<int>(in.read(8));
+        if (width > 16) throw Bad{"symbol width above 16 bits"};
+        const uint32_t mask = (1u << width) - 1u;
+        symbols.resize(total);
+        uint32_t at = 0;
+        for (int len = 1; len <= maxLen; ++len) {
+            const uint32_t n = count[len];
+            if (eliasFanoBound(n, mask) < n * static_cast<uint32_t>(width)) {  // Huffman.cpp:187-190
+                const uint32_t m = std::bit_width(mask), nb = std::bit_width(n), lb = m >= nb ? m - nb : 0;
+                uint32_t bucket = 0;
+                for (uint32_t i = 0; i < n; ++i) {
+                    bucket += in.readUnaryZeros();
+                    if (bucket > 65535u) throw Bad{"Elias-Fano bucket out of range"};
+                    symbols[at + i] = static_cast<uint16_t>(bucket << lb);
+                }
+                for (uint32_t i = 0; i < n; ++i) symbols[at + i] |= static_cast<uint16_t>(in.read(static_cast<int>(lb)));
+            } else {
+                for (uint32_t i = 0; i < n; ++i) symbols[at + i] = static_cast<uint16_t>(in.read(width));
+            }
+            at += n;
+        }
+        if (symbols[total - 1] != mask) throw Bad{"last table symbol is not the pseudo-EOF"};  // Huffman.cpp:212-215
+        if (in.overrun()) throw Bad{"Huffman table runs past the end of the stream"};
+        // canonical codes: code <<= (length - prevLength) before each entry, ++code after (Huffman.cpp:200-226)
+        uint64_t code = 0;
+        int prevLen = 0;
+        uint32_t index = 0;
+        lut.assign(size_t{1} << kLutBits, 0u);
+        for (int len = 1; len <= maxLen; ++len) {
+            if (count[len] == 0) continue;
+            code <<= (len - prevLen);
+            prevLen = len;
+            firstCode[len] = code;
+            firstIndex[len] = index;
+            if (code + count[len] > (1ull << len)) throw Bad{"Huffman code lengths oversubscribed"};
+            if (len <= kLutBits) {
+                for (uint32_t i = 0; i < count[len]; ++i) {
+                    const uint32_t entry = (index + i) << 8 | static_cast<uint32_t>(len);
+                    const size_t lo = static_cast<size_t>(code + i) << (kLutBits - len);
+                    std::fill(lut.begin() + lo, lut.begin() + lo + (size_t{1} << (kLutBits - len)), entry);
+                }
+            }
+            code += count[len];
+            index += count[len];
+        }
+    }
+
+    // Payload codes up to the pseudo-EOF into out[0, cap); returns the number of symbols (Huffman.cpp:227-243).
+    size_t decode(BitReader& in, uint16_t* out, size_t cap) const {
+        size_t n = 0;
+        const uint32_t eof = total - 1;
+        for (;;) {
+            const uint64_t window = in.peek(kMaxCodeLen);
+            uint32_t entry = lut[window >> (kMaxCodeLen - kLutBits)];
+            uint32_t index = 0, len;
+            if (entry) {
+                index = entry >> 8, len = entry & 0xFF;
+            } else {
+                len = 0;
+                for (int l = kLutBits + 1; l <= maxLen; ++l) {
+                    const uint64_t v = window >> (kMaxCodeLen - l);
+                    if (count[l] && v >= firstCode[l] && v - firstCode[l] < count[l]) {
+                        index = firstIndex[l] + static_cast<uint32_t>(v - firstCode[l]), len = static_cast<uint32_t>(l);
+                        break;
+                    }
+                }
+                if (!len) throw Bad{"bit pattern is not a Huffman code"};
+            }
+            in.skip(static_cast<int>(len));
+            if (in.overrun()) throw Bad{"Huffman payload without pseudo-EOF"};
+            if (index == eof) return n;
+            if (n >= cap) throw Bad{"sequence longer than the block counts allow"};
+            out[n++] = symbols[index];
+        }
+    }
+};
+
+// readHuffmanOrGolomb (CompressedImage.cpp:392-401): `expect` symbols when Golomb coded; a Huffman payload carries its own end.
+size_t readSequence(BitReader& in, HuffTable& table, size_t expect, uint16_t* out, size_t cap) {
+    if (in.read(1) == 0) {
+        table.read(in);
+        return table.decode(in, out, cap);
+    }
+    const uint32_t M = static_cast<uint32_t>(in.read(16));
+    if (M == 0) throw Bad{"Golomb parameter 0"};
+    if (expect > cap) throw Bad{"sequence longer than the block counts allow"};
+    const uint32_t b = std::bit_width(M), limit = (1u << (b + 1)) - M;  // BitBuffer.cpp:248-256
+    for (size_t i = 0; i < expect; ++i) {
+        const uint32_t q = in.readUnaryOnes();
+        const uint32_t rem1 = static_cast<uint32_t>(in.read(static_cast<int>(b)));
+        const uint32_t rem = rem1 < limit ? rem1 : (rem1 << 1) + static_cast<uint32_t>(in.read(1)) - limit;
+        out[i] = static_cast<uint16_t>(q * M + rem);
+        if (in.overrun()) throw Bad{"Golomb payload runs past the end of the stream"};
+    }
+    return expect;
+}
+
+// runLengthDecode (Huffman.cpp:281-307) from `in` into out[0, cap).
+size_t expandRuns(const uint16_t* in, size_t n, uint16_t* out, size_t cap) {
+    size_t o = 0;
+    uint16_t prev = 0;
+    bool pending = false, newRun = true;
+    for (size_t i = 0; i < n; ++i) {
+        const uint16_t v = in[i];
+        if (pending) {
+            if (o + v > cap) throw Bad{"run-length coded stream longer than the block counts allow"};
+            std::fill(out + o, out + o + v, prev);
+            o += v;
+            pending = false;
+            newRun = true;
+        } else {
+            if (o >= cap) throw Bad{"run-length coded stream longer than the block counts allow"};
+            out[o++] = v;
+            if (v == prev && !newRun) pending = true;
+            newRun = false;
+            prev = v;
+        }
+    }
+    return o;
+}
+
+}  // namespace
+
+struct MnParser::Impl {
+    BitReader in;
+    HuffTable table;
+    std::vector<uint16_t> runs;
+    Impl(const uint8_t* p, size_t n) : in(p, n) {}
+};
+
+MnParser::MnParser(const uint8_t* bytes, size_t n) : impl_(new Impl(bytes, n)), nbytes_(n) {}
+MnParser::~MnParser() { delete impl_; }
+
+int MnParser::readHeader(std::string& err, bool headerOnly) {
+    BitReader& in = impl_->in;
+    if (nbytes_ < 14) return err = "stream shorter than its header", -1;
+    if (in.read32() != 0x4D4E3234u) return err = "not a .mn stream (magic)", -1;  // CompressedImage.cpp:721-723
+    width = in.read32();
+    height = in.read32();
+    K = static_cast<int>(in.read(8));
+    blockSize = static_cast<int>(in.read(8));
+    if (K < 1 || K > kMaxK) return err = "K outside 1..32", -1;
+    if (blockSize != 8) return err = "block size is not 8", -1;
+    if (width == 0 || height == 0 || width > (1u << 20) || height > (1u << 20)) return err = "image dimensions out of range", -1;
+    if (nbytes_ < 14 + 6 * static_cast<size_t>(K)) return err = "stream shorter than its header", -1;
+    for (int i = 0; i < 3 * K; ++i) quant[i] = static_cast<float>(in.read(16));  // :727-736
+    nblocks = static_cast<size_t>((width + 7) / 8) * ((height + 7) / 8);
+    // every `lengths` symbol costs at least one bit: bounds what a caller allocates for a stream that claims absurd dimensions
+    if (!headerOnly && 3 * nblocks > 8 * nbytes_) return err = "fewer bits than blocks", -1;
+    return 0;
+}
+
+int MnParser::readLengths(uint16_t* counts, std::string& err) {
+    try {
+        const size_t n = readSequence(impl_->in, impl_->table, 3 * nblocks, counts, 3 * nblocks);
+        if (n != 3 * nblocks) throw Bad{"`lengths` does not hold one count per block and channel"};
+    } catch (const Bad& b) {
+        return err = b.why, -1;
+    }
+    // stream (layer, depth) holds one entry per block with count > depth (CompressedImage.cpp:751-758)
+    size_t hist[3][kMaxK + 1] = {};
+    for (size_t b = 0; b < nblocks; ++b)
+        for (int ch = 0; ch < 3; ++ch) {
+            const uint16_t c = counts[3 * b + ch];
+            if (c > K) return err = "block count above K", -1;
+            ++hist[ch][c];
+        }
+    size_t at = 0;
+    for (int ch = 0; ch < 3; ++ch) {
+        size_t deeper[kMaxK + 1] = {};
+        for (int d = K - 1; d >= 0; --d) deeper[d] = (d + 1 < K ? deeper[d + 1] : 0) + hist[ch][d + 1];
+        for (int d = 0; d < K; ++d)
+            for (int part = 0; part < 2; ++part) {
+                streamOffset[2 * (ch * K + d) + part] = at;
+                at += deeper[d];
+            }
+    }
+    streamOffset[6 * K] = at;
+    if (at > 0xFFFFFFF0ull) return err = "more than 2^32 symbols", -1;
+    return 0;
+}
+
+int MnParser::readStreams(uint16_t* arena, std::string& err) {
+    BitReader& in = impl_->in;
+    try {
+        for (int s = 0; s < 6 * K; ++s) {
+            uint16_t* dst = arena + streamOffset[s];
+            const size_t want = streamOffset[s + 1] - streamOffset[s];
+            size_t got;
+            if (in.read(1) == 1) {  // run-length coded, CompressedImage.cpp:744-750
+                const size_t codeLength = in.read32();
+                if (codeLength > want + 4) throw Bad{"run-length coded stream longer than the plain one"};
+                impl_->runs.resize(codeLength + 1);
+                const size_t n = readSequence(in, impl_->table, codeLength, impl_->runs.data(), codeLength);
+                got = expandRuns(impl_->runs.data(), n, dst, want);
+            } else {
+                got = readSequence(in, impl_->table, want, dst, want);
+            }
+            if (got != want) throw Bad{"stream size differs from the block counts"};
+        }
+    } catch (const Bad& b) {
+        return err = b.why, -1;
+    }
+    for (int ch = 0; ch < 3; ++ch) {  // undo the DC delta chains, :766-781
+        uint16_t* dc = arena + streamOffset[2 * ch * K + 1];
+        const size_t n = streamOffset[2 * ch * K + 2] - streamOffset[2 * ch * K + 1];
+        int32_t acc = 0;
+        for (size_t i = 0; i < n; ++i) {
+            acc = unzigzag(dc[i]) + acc;
+            dc[i] = static_cast<uint16_t>(acc);
+        }
+    }
+    bitsRead = in.position();
+    return 0;
+}
+
+}  // namespace mnenc

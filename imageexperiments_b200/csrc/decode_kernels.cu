@@ -1,0 +1,153 @@
+// Device side of the decoder: symbol streams -> pixels. Replaces the block loop of
+//   compressed::decodeImageFast        CompressionLib/src/CompressedImage.cpp:837-889
+//   matching::FromCoeffsDynamicFast    CompressionLib/src/MatchingPursuit.cpp:152-169
+//   dynamicBasisFast (row lookup only) CompressionLib/src/CompressedImage.cpp:252-289
+//   img::RGBFromYUV                    ImageHelper/src/misc.cpp:28-36
+//
+// Both kernels are HBM/L2 streaming work: the symbols are read once, every picked atom row (256 B) comes out of the
+// L2-resident dictionary (24.5 MB), 3 B per pixel are written. No dictionary is materialised per block (the reference
+// copies up to 2 463 x 64 floats per block-channel): an absolute atom index is resolved to a row by walking the block's
+// earlier picks, exactly as the encoder's kernel does.
+#include <algorithm>
+
+#include "backend_kernels.cuh"
+#include "decode_kernels.cuh"
+
+namespace mnenc {
+namespace {
+
+constexpr unsigned kFull = 0xFFFFFFFFu;
+
+// Inverse of scatterKernel (backend_kernels.cu): stream (layer, depth) holds one entry per block whose count in that layer
+// exceeds depth, in ascending block order; tileOffsets = exclusive scan of the per-tile counts (launchTileCounts).
+__global__ void __launch_bounds__(kTileBlocks) gatherKernel(const uint16_t* __restrict__ counts, uint32_t nblocks, int K,
+                                                            const uint32_t* __restrict__ tileOffsets,
+                                                            const __grid_constant__ StreamOffsets so,
+                                                            const uint16_t* __restrict__ arena, uint32_t* __restrict__ pairs) {
+    __shared__ uint32_t warpCnt[kTileBlocks / 32][kMaxK];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t blk = blockIdx.x * kTileBlocks + threadIdx.x;
+    for (int ch = 0; ch < 3; ++ch) {
+        const int count = blk < nblocks ? counts[3 * blk + ch] : 0;
+        int maxCount = count;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) maxCount = max(maxCount, __shfl_xor_sync(kFull, maxCount, off));
+        for (int d = lane; d < K; d += 32) warpCnt[warp][d] = 0;
+        __syncwarp();
+        uint32_t myRank[kMaxK];
+        for (int d = 0; d < maxCount; ++d) {
+            const unsigned m = __ballot_sync(kFull, count > d);
+            if (count > d) myRank[d] = __popc(m & ((1u << lane) - 1u));
+            if (lane == 0) warpCnt[warp][d] = __popc(m);
+        }
+        __syncthreads();
+        if (count > 0) {
+            const uint32_t* tileOff = tileOffsets + static_cast<size_t>(blockIdx.x) * 3 * K + ch * K;
+            uint32_t* pp = pairs + (static_cast<size_t>(3) * blk + ch) * K;
+            for (int d = 0; d < count; ++d) {
+                uint32_t before = 0;
+                for (int w = 0; w < warp; ++w) before += warpCnt[w][d];
+                const uint32_t pos = tileOff[d] + before + myRank[d];
+                const int sid = 2 * (ch * K + d);
+                pp[d] = static_cast<uint32_t>(arena[so.off[sid] + pos]) | static_cast<uint32_t>(arena[so.off[sid + 1] + pos]) << 16;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+__device__ __forceinline__ int unzigzag(uint32_t x) { return static_cast<int>(x >> 1) ^ -static_cast<int>(x & 1u); }  // BitBuffer.h:112-114
+
+__device__ __forceinline__ uint8_t toByte(double v) {  // static_cast<uchar>(std::clamp(std::round(v), 0.0, 255.0)), misc.cpp:30-32
+    return static_cast<uint8_t>(fmin(fmax(round(v), 0.0), 255.0));
+}
+
+constexpr int kBlocksPerCta = 4;  // 64 threads (one per pixel) per image block
+
+// One image block per 64 threads: thread j = dx + 8 * dy rebuilds pixel j of the three channels and converts it.
+__global__ void __launch_bounds__(64 * kBlocksPerCta) reconstructKernel(const DecodeParams p) {
+    __shared__ int absIdx[2 * kBlocksPerCta][kMaxK];  // per warp: absolute atom index of each pick of the current block-channel
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int j = threadIdx.x & 63;
+    const int dx = j & 7, dy = j >> 3;
+    const uint32_t ngroups = (p.nblocks + kBlocksPerCta - 1) / kBlocksPerCta;
+    for (uint32_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
+        const uint32_t blk = g * kBlocksPerCta + (threadIdx.x >> 6);
+        if (blk >= p.nblocks) continue;  // whole warps leave together (64 threads per block)
+        float yuv[3];
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            const int count = p.counts[3 * blk + ch];
+            const uint32_t* pp = p.pairs + (static_cast<size_t>(3) * blk + ch) * p.K;
+            const float* quant = p.quant + ch * p.K;
+            float r = 0.0f;
+            // absolute atom indices: running sum of the zig-zag decoded deltaIds (MatchingPursuit.cpp:160-164), one pick per lane
+            __syncwarp();
+            int v = 0;
+            if (lane < count) {
+                const uint32_t id = __ldg(pp + lane) & 0xFFFFu;
+                v = lane ? unzigzag(id) : static_cast<int>(id);
+            }
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const int up = __shfl_up_sync(kFull, v, off);
+                if (lane >= off) v += up;
+            }
+            absIdx[warp][lane] = v;
+            __syncwarp();
+            for (int i = 0; i < count; ++i) {
+                const int choice = absIdx[warp][i];
+                const float coeff = __fmul_rn(__ldg(quant + i), static_cast<float>(unzigzag(__ldg(pp + i) >> 16)));  // :165
+                // row of the dictionary dynamicBasisFast builds from all `count` picks: base atoms, then the detail group of
+                // every pick below nBase, in pick order (CompressedImage.cpp:258-288)
+                const float* row = nullptr;
+                if (choice >= 0 && choice < p.nBase) {
+                    row = p.rows32 + static_cast<size_t>(choice) * kN;
+                } else if (choice >= p.nBase) {
+                    int off = choice - p.nBase;
+                    for (int e = 0; e < count; ++e) {
+                        const int c = absIdx[warp][e];
+                        if (c < 0 || c >= p.nBase) continue;
+                        const int rows = p.detRows[c];
+                        if (off < rows) {
+                            row = p.rows32 + (static_cast<size_t>(kRowsPad) + (static_cast<size_t>(ch) * p.nBase + c) * 64 + off) * kN;
+                            break;
+                        }
+                        off -= rows;
+                    }
+                }
+                if (row == nullptr) {  // index outside the block's dictionary: damaged stream (the reference reads out of range)
+                    if (j == 0) atomicExch(p.error, 1u);
+                    continue;
+                }
+                r = __fadd_rn(r, __fmul_rn(coeff, __ldg(row + j)));  // results += coeff * dictionary.row(choice), unfused, :166
+            }
+            yuv[ch] = r;
+        }
+        const uint32_t bx = blk / p.nby, by = blk - bx * p.nby;  // column-major block walk, CompressedImage.cpp:851-853
+        const uint32_t x = bx * 8 + dx, y = by * 8 + dy;
+        if (x < p.width && y < p.height) {
+            const double Y = yuv[0], U = yuv[1], V = yuv[2];
+            uint8_t* px = p.rgb + static_cast<size_t>(y) * p.stride + 3 * static_cast<size_t>(x);
+            px[0] = toByte(__dadd_rn(Y, __dmul_rn(1.13983, V)));
+            px[1] = toByte(__dsub_rn(__dsub_rn(Y, __dmul_rn(0.39466, U)), __dmul_rn(0.58060, V)));
+            px[2] = toByte(__dadd_rn(Y, __dmul_rn(2.03211, U)));
+        }
+    }
+}
+
+}  // namespace
+
+int launchGather(const BackendBuffers& b, const StreamOffsets& so, uint32_t* pairsOut, cudaStream_t st) {
+    gatherKernel<<<b.ntiles, kTileBlocks, 0, st>>>(b.counts, b.nblocks, b.K, b.tileCounts, so, b.arena, pairsOut);
+    return 1;
+}
+
+int launchReconstruct(const DecodeParams& p, int numSMs, cudaStream_t st) {
+    const uint32_t ngroups = (p.nblocks + kBlocksPerCta - 1) / kBlocksPerCta;
+    const uint32_t grid = std::min<uint32_t>(ngroups, static_cast<uint32_t>(numSMs) * 8u);  // 8 x 256 threads fill an SM
+    reconstructKernel<<<grid, 64 * kBlocksPerCta, 0, st>>>(p);
+    return 1;
+}
+
+}  // namespace mnenc

@@ -8,6 +8,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstddef>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
@@ -126,6 +127,9 @@ struct mnenc_ctx {
     bool histReady = false;
     mnenc::PinBuf hTotals, hSeqTable, hEntries, hNEntries, hEntryCodes, hCodeTable, hStats;
     std::unique_ptr<mnenc::HostPool> pool;  // code-table builds of one image run on these threads
+    // decoder (decode_api.cu): parsed `lengths` / streams in pinned memory, the stream's quantisers + error flag on the device
+    mnenc::PinBuf hDecCounts, hDecArena, hDecMisc;
+    mnenc::DevBuf decQuant;
     // accounting
     float ms[8] = {};
     int launches = 0;

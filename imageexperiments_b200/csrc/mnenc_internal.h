@@ -126,4 +126,32 @@ void planStripes(const StripeBoundary* rec, int nranks, int nStreams, StripePlan
 // compressed::createQuantizationTables, float overload (CompressedImage.cpp:168-210).
 int quantTables(int K, int blockSize, double bpp, float* out3K);
 
+// ------------------------------------------------------------------------------------------------
+// Decoder, host side (decode_host.cpp): readCompressedFast (CompressedImage.cpp:709-782) in three steps, so that the
+// caller can size its (pinned) buffers between them and start uploading `lengths` while the streams are still being read.
+// Each step returns 0, or -1 with a message in `err`.
+// ------------------------------------------------------------------------------------------------
+class MnParser {
+public:
+    MnParser(const uint8_t* bytes, size_t n);
+    ~MnParser();
+    MnParser(const MnParser&) = delete;
+    MnParser& operator=(const MnParser&) = delete;
+    int readHeader(std::string& err, bool headerOnly = false);  // magic, dimensions, K, block size, 3K quantisers -> fields below
+    int readLengths(uint16_t* counts, std::string& err);  // counts[3 * nblocks]; fills streamOffset
+    int readStreams(uint16_t* arena, std::string& err);   // arena[streamOffset[6K]]: run lengths expanded, DC chains undone
+
+    uint32_t width = 0, height = 0;
+    int K = 0, blockSize = 0;
+    float quant[3 * kMaxK] = {};
+    size_t nblocks = 0;
+    size_t streamOffset[6 * kMaxK + 1] = {};  // stream s = arena[streamOffset[s], streamOffset[s + 1])
+    uint64_t bitsRead = 0;
+
+private:
+    struct Impl;
+    Impl* impl_;
+    size_t nbytes_;
+};
+
 }  // namespace mnenc

@@ -24,6 +24,7 @@ extern "C" {
 #define MNENC_ERR_CUDA (-2)     /* CUDA runtime error or no usable device */
 #define MNENC_ERR_STATE (-3)    /* call order (e.g. encode before set_quant) */
 #define MNENC_ERR_INTERNAL (-4) /* consistency check failed inside the encoder */
+#define MNENC_ERR_STREAM (-5)   /* decoder: not a `.mn` stream, or a damaged one (the reference throws range_error("Invalid ...")) */
 
 typedef struct mnenc_ctx mnenc_t;
 
@@ -78,6 +79,37 @@ void mnenc_free(uint8_t* p);
  */
 int mnenc_encode_batch_rgb8(mnenc_t* ctx, size_t n_images, const uint8_t* const* rgb, int on_device, const size_t* width,
                             const size_t* height, const size_t* row_stride_bytes, uint8_t** out, size_t* out_bytes);
+
+/*
+ * Decoder. Replaces
+ *   std::unique_ptr<image<rgb>> compressed::decodeImageFast(const uint8_t bytes[], size_t byteSize)
+ *       CompressionLib/inc/CompressedImage.h:75, CompressionLib/src/CompressedImage.cpp:837-889
+ * (readCompressedFast :709-782, huffmanDecode Huffman.cpp:173-244, runLengthDecode :281-307, readGolombCode
+ * BitBuffer.cpp:243-258, FromCoeffsDynamicFast MatchingPursuit.cpp:152-169, RGBFromYUV misc.cpp:28-36).
+ *   mn, mn_bytes: the stream, host memory. The quantisation tables are the stream's; the dictionary is the context's
+ *                 (the reference rebuilds it in readCompressedFast :726 — same floats by construction);
+ *                 K of the stream may differ from the context's.
+ *   *rgb:         packed RGB8, row-major, 3 * width bytes per row (image<rgb>::data), from the library: mnenc_free().
+ * The pixels are those of the reference's decoder, bit for bit. A stream the reference would reject (bad magic, no
+ * pseudo-EOF) and any stream whose lengths are inconsistent — where the reference reads out of range — give
+ * MNENC_ERR_STREAM; block sizes other than 8 and K > 32 give MNENC_ERR_STREAM as well (unsupported).
+ * The entropy decode runs on the calling thread (one serial bit chain per image, see decode_host.cpp), the block loop
+ * on the GPU. mnenc_last_timing afterwards: ms[0] = header + `lengths`, ms[1] = symbol streams, ms[2] = uploads + kernels +
+ * download (host clock), ms[3] = gather + reconstruct kernels (CUDA events), ms[7] = whole call.
+ */
+int mnenc_decode_rgb8(mnenc_t* ctx, const uint8_t* mn, size_t mn_bytes, uint8_t** rgb, size_t* width, size_t* height);
+/* Same, writing into device memory of the context's GPU (capacity_bytes >= row_stride_bytes * (height - 1) + 3 * width). */
+int mnenc_decode_rgb8_device(mnenc_t* ctx, const uint8_t* mn, size_t mn_bytes, uint8_t* rgb_dev, size_t capacity_bytes,
+                             size_t row_stride_bytes, size_t* width, size_t* height);
+/* Header only (host, no GPU): CompressedImage.cpp:721-736. Any out pointer may be NULL; quant receives 3 * K floats (<= 96). */
+int mnenc_stream_info(const uint8_t* mn, size_t mn_bytes, size_t* width, size_t* height, int* K, int* block_size, float* quant);
+/*
+ * Debug tap (host, no GPU): readCompressedFast's result. lengths[3 * nblocks]; stream_offsets[6K + 1] (stream s =
+ * symbols[stream_offsets[s], stream_offsets[s + 1])); symbols may be NULL to obtain the sizes first. Run lengths are
+ * expanded and the DC chains undone, as in the reference (:744-781).
+ */
+int mnenc_debug_parse(const uint8_t* mn, size_t mn_bytes, uint16_t* lengths, size_t lengths_capacity, uint64_t* stream_offsets,
+                      uint16_t* symbols, size_t symbols_capacity);
 
 /*
  * Debug taps for parity tests (the reference has no equivalent call; they expose the intermediates of

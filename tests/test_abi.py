@@ -80,6 +80,10 @@ def test_batch_and_stripe_entry_points_reject_bad_arguments():
         assert f(None, rec.ctypes.data_as(C.c_void_p), rec.ctypes.data_as(C.c_void_p)) == -1
     assert L.mnenc_stripe_plan(None, rec.ctypes.data_as(C.c_void_p)) == -1
     assert L.mnenc_stripe_finish(None, C.byref(out), C.byref(n)) == -1
+    w, h = C.c_size_t(), C.c_size_t()
+    assert L.mnenc_decode_rgb8(None, rec.ctypes.data_as(C.c_void_p), 99, C.byref(out), C.byref(w), C.byref(h)) == -1
+    assert L.mnenc_decode_rgb8_device(None, rec.ctypes.data_as(C.c_void_p), 99, rec.ctypes.data_as(C.c_void_p), 99, 3, C.byref(w), C.byref(h)) == -1
+    assert L.mnenc_stream_info(rec.ctypes.data_as(C.c_void_p), 99 * 4, None, None, None, None, None) == -5  # not a .mn stream
     L.mnenc_free(None)  # releasing nothing is allowed
 
 

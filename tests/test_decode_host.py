@@ -1,0 +1,92 @@
+"""CPU tests of the product's host-side `.mn` reader (imageexperiments_b200/csrc/decode_host.cpp through the host-only
+entry points mnenc_stream_info / mnenc_debug_parse): same `lengths` and streams as the reference's readCompressedFast
+(golden vectors), as the oracle on larger images, and errors — not crashes — on damaged streams."""
+import os
+import time
+
+import numpy as np
+import pytest
+
+import imageexperiments_b200 as mn
+
+FIXTURE = "/root/reference/Data/r0c1de5e1t_3_5.mn"
+
+
+@pytest.fixture(scope="module")
+def gd():
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_decode.npz"))
+
+
+def same_parse(p, lengths, streams):
+    assert (p["lengths"] == lengths).all()
+    assert len(p["streams"]) == len(streams)
+    for i, (a, b) in enumerate(zip(p["streams"], streams)):
+        assert a.shape == b.shape and (a == b).all(), i
+
+
+def test_parse_golden(gd):
+    for name in gd["names"]:
+        data = gd[f"mn_{name}"].tobytes()
+        p = mn.parseStream(data)
+        sizes = gd[f"sizes_{name}"]
+        offs = np.concatenate([[0], np.cumsum(sizes)])
+        same_parse(p, gd[f"len_{name}"], [gd[f"sym_{name}"][offs[i]:offs[i + 1]] for i in range(len(sizes))])
+        h, w = gd[f"rgb_{name}"].shape[:2]
+        assert (p["width"], p["height"], p["blockSize"]) == (w, h, 8) and p["K"] == len(sizes) // 6
+
+
+def test_stream_info_is_the_header(gd, golden):
+    info = mn.streamInfo(gd["mn_coarse"].tobytes())
+    assert (info["Quant"] == mn.createQuantizationTables(32, 8, 1.0)).all()
+    hdr = golden["fixture_header"].tobytes()  # the reference's own fixture: 4928 x 3264, K 32, tables of quality 3.5
+    info = mn.streamInfo(hdr + b"\0" * 64)
+    assert (info["width"], info["height"], info["K"], info["blockSize"]) == (4928, 3264, 32, 8)
+    assert (info["Quant"] == mn.createQuantizationTables(32, 8, 3.5)).all()
+
+
+def test_parse_vs_oracle_larger_images(oraclelib, oracle_ctx_factory):
+    from imageexperiments_b200.synth import synthetic_rgb
+    rng = np.random.default_rng(5)
+    cases = [(synthetic_rgb(512, 384, 41), 3.5), (synthetic_rgb(333, 257, 42), 8.0), (synthetic_rgb(640, 120, 43), 1.0),
+             (np.full((1600, 1608, 3), 200, np.uint8), 3.5),                       # runs over the 32 769 chunk limit
+             (rng.integers(0, 256, (96, 160, 3)).astype(np.uint8), 8.0)]         # wide alphabets, long codes
+    for img, q in cases:
+        oc = oracle_ctx_factory(mn.createQuantizationTables(32, 8, q))
+        data = oc.encode(img)
+        oc.close()
+        want = oraclelib.parse(data)
+        same_parse(mn.parseStream(data), want["lengths"], want["streams"])
+
+
+def test_damaged_streams_give_errors(gd):
+    data = gd["mn_synth"].tobytes()
+    bad = [b"", data[:10], b"\0\0\0\0" + data[4:], data[: len(data) // 2], data[:300],
+           data[:12] + bytes([33]) + data[13:],      # K = 33
+           data[:13] + bytes([4]) + data[14:],       # block size 4
+           data[:4] + b"\x7f\xff\xff\xff" + data[8:]]  # absurd width
+    for b in bad:
+        with pytest.raises(mn.MnencError) as e:
+            mn.parseStream(b)
+        assert e.value.code == -5, len(b)
+    rng = np.random.default_rng(9)
+    arr = np.frombuffer(data, np.uint8)
+    for _ in range(300):  # random damage after the header: either rejected or parsed, never a crash
+        a = arr.copy()
+        pos = rng.integers(206, a.size, 4)
+        a[pos] ^= rng.integers(1, 256, 4).astype(np.uint8)
+        try:
+            mn.parseStream(a.tobytes())
+        except mn.MnencError as e:
+            assert e.code == -5
+
+
+@pytest.mark.skipif(not os.path.exists(FIXTURE), reason="reference tree absent (GPU box)")
+def test_parse_reference_fixture(oraclelib):
+    with open(FIXTURE, "rb") as f:
+        data = f.read()
+    t = time.perf_counter()
+    p = mn.parseStream(data)
+    ms = (time.perf_counter() - t) * 1e3
+    want = oraclelib.parse(data)
+    same_parse(p, want["lengths"], want["streams"])
+    print(f"fixture: {len(data)} B, {sum(len(s) for s in p['streams'])} symbols parsed (twice) in {ms:.1f} ms")
