@@ -5,11 +5,11 @@ host-side mirror of the reference's encoder interface (compressed.py; stripes.py
 process group).
 """
 from .compressed import (CompressionContextFast, MnBuffer, createCompressionContextFast, createQuantizationTables, encodeImageBatch, encodeImageFast,
-                         decodeImageFast, parseStream, streamInfo, lastSymbols, packSymbols, planSequenceHost)
+                         decodeImageBatch, decodeImageFast, parseStream, streamInfo, lastSymbols, packSymbols, planSequenceHost)
 from .dictionary import Dictionary
 from .stripes import TorchComm, ThreadComm, encodeImageStripes, stripeColumns
 from ._lib import MnencError
 
-__all__ = ["CompressionContextFast", "MnBuffer", "createCompressionContextFast", "createQuantizationTables", "encodeImageFast", "encodeImageBatch", "decodeImageFast", "parseStream", "streamInfo", "lastSymbols",
+__all__ = ["CompressionContextFast", "MnBuffer", "createCompressionContextFast", "createQuantizationTables", "encodeImageFast", "encodeImageBatch", "decodeImageBatch", "decodeImageFast", "parseStream", "streamInfo", "lastSymbols",
            "packSymbols", "planSequenceHost", "Dictionary", "MnencError", "TorchComm", "ThreadComm", "encodeImageStripes",
            "stripeColumns"]

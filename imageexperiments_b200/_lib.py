@@ -18,7 +18,7 @@ EXPORTS = (
     "mnenc_last_error", "mnenc_create", "mnenc_destroy", "mnenc_quant_tables", "mnenc_set_quant", "mnenc_encode_rgb8",
     "mnenc_encode_rgb8_device", "mnenc_encode_batch_rgb8", "mnenc_free", "mnenc_get_symbols", "mnenc_pack_symbols", "mnenc_last_timing", "mnenc_last_work",
     "mnenc_debug_plan_sequence", "mnenc_debug_stitch_runs", "mnenc_debug_rle_chunk_size", "mnenc_debug_plan_stripes",
-    "mnenc_decode_rgb8", "mnenc_decode_rgb8_device", "mnenc_stream_info", "mnenc_debug_parse",
+    "mnenc_decode_rgb8", "mnenc_decode_rgb8_device", "mnenc_decode_batch_rgb8", "mnenc_stream_info", "mnenc_debug_parse",
     "mnenc_stripe_begin", "mnenc_stripe_rle", "mnenc_stripe_histogram", "mnenc_stripe_plan", "mnenc_stripe_pack", "mnenc_stripe_finish",
 )
 
@@ -68,6 +68,7 @@ def load() -> C.CDLL:
     L.mnenc_stripe_finish.argtypes = [_vp, _vp, _vp]
     L.mnenc_decode_rgb8.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp]
     L.mnenc_decode_rgb8_device.argtypes = [_vp, _vp, _sz, _vp, _sz, _sz, _vp, _vp]
+    L.mnenc_decode_batch_rgb8.argtypes = [_vp, _sz, _vp, _vp, _vp, _vp, _vp]
     L.mnenc_stream_info.argtypes = [_vp, _sz, _vp, _vp, _vp, _vp, _vp]
     L.mnenc_debug_parse.argtypes = [_vp, _sz, _vp, _sz, _vp, _vp, _sz]
     _lib = L

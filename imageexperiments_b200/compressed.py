@@ -185,6 +185,29 @@ def encodeImageBatch(images, context: CompressionContextFast, zero_copy: bool = 
     return [_take(_vp(outs[i]), sizes[i]) for i in range(n)]
 
 
+class _PinnedBlock:
+    """Owner of one library result buffer; released (recycled by the library) when the last view of it goes away."""
+
+    def __init__(self, ptr: _vp):
+        self._ptr = ptr
+
+    def __del__(self):
+        try:
+            if self._ptr:
+                _lib.load().mnenc_free(self._ptr)
+                self._ptr = None
+        except Exception:
+            pass
+
+
+def _pixels(rgb: _vp, w: int, h: int, zero_copy: bool) -> np.ndarray:
+    n = 3 * w * h
+    arr = (C.c_uint8 * n).from_address(rgb.value)
+    arr._owner = _PinnedBlock(rgb)  # numpy keeps the ctypes array alive, the array keeps the pinned block from being recycled
+    img = np.frombuffer(arr, np.uint8).reshape(h, w, 3)
+    return img if zero_copy else img.copy()
+
+
 def _stream(data):
     """bytes / bytearray / MnBuffer / uint8 array -> (pointer, size, keep-alive)."""
     if isinstance(data, MnBuffer):
@@ -212,11 +235,25 @@ def decodeImageFast(data, context: CompressionContextFast, out=None, zero_copy: 
         return out
     rgb = _vp()
     _lib.check(L.mnenc_decode_rgb8(context._h, ptr, n, C.byref(rgb), C.byref(w), C.byref(h)))
-    buf = MnBuffer(rgb, 3 * w.value * h.value)
-    if not zero_copy:
-        return np.frombuffer(buf.array, np.uint8).reshape(h.value, w.value, 3).copy()
-    buf.array._owner = buf  # numpy keeps the ctypes array alive, the array keeps the pinned block from being recycled
-    return np.frombuffer(buf.array, np.uint8).reshape(h.value, w.value, 3)
+    return _pixels(rgb, w.value, h.value, zero_copy)
+
+
+def decodeImageBatch(streams, context: CompressionContextFast, zero_copy: bool = False) -> list:
+    """Throughput mode: decodeImageFast of every stream of ``streams`` (bytes / MnBuffer / uint8 arrays), pipelined over the
+    context's lanes (mnenc_decode_batch_rgb8). Returns a list of HxWx3 uint8 arrays, each identical to
+    decodeImageFast(stream, context)."""
+    n = len(streams)
+    if n == 0:
+        return []
+    ptrs, sizes = (_vp * n)(), (C.c_size_t * n)()
+    keep = []
+    for i, d in enumerate(streams):
+        ptr, size, k = _stream(d)
+        keep.append(k)
+        ptrs[i], sizes[i] = C.cast(ptr, _vp).value, size
+    outs, ws, hs = (_vp * n)(), (C.c_size_t * n)(), (C.c_size_t * n)()
+    _lib.check(_lib.load().mnenc_decode_batch_rgb8(context._h, n, ptrs, sizes, outs, ws, hs))
+    return [_pixels(_vp(outs[i]), ws[i], hs[i], zero_copy) for i in range(n)]
 
 
 def streamInfo(data) -> dict:

@@ -31,6 +31,22 @@ int makeLane(mnenc_ctx* parent, int threads, mnenc_ctx** out) {
     return MNENC_OK;
 }
 
+// The context itself + up to MNENC_LANES - 1 (default 6, at most 8 in all) extra lanes, created on first use.
+int acquireLanes(mnenc_ctx* c, size_t nImages, std::vector<mnenc_ctx*>& lanes) {
+    int want = 6;
+    if (const char* e = std::getenv("MNENC_LANES")) want = std::atoi(e);
+    want = static_cast<int>(std::min<size_t>(static_cast<size_t>(std::clamp(want, 1, 8)), nImages));
+    while (static_cast<int>(c->lanes.size()) + 1 < want) {
+        mnenc_ctx* lane = nullptr;
+        const int rc = makeLane(c, std::max(1, c->hostThreads / 2), &lane);
+        if (lane) c->lanes.push_back(lane);
+        if (rc) return rc;
+    }
+    lanes.assign(1, c);
+    for (int i = 0; i + 1 < want; ++i) lanes.push_back(c->lanes[i]);
+    return MNENC_OK;
+}
+
 }  // namespace
 
 extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_t* const* rgb, int on_device, const size_t* width,
@@ -40,21 +56,12 @@ extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
     for (size_t i = 0; i < n_images; ++i) out[i] = nullptr, out_bytes[i] = 0;
     if (n_images == 0) return MNENC_OK;
     CU(cudaSetDevice(c->device));
-    int want = 6;
-    if (const char* e = std::getenv("MNENC_LANES")) want = std::atoi(e);
-    want = static_cast<int>(std::min<size_t>(static_cast<size_t>(std::clamp(want, 1, 8)), n_images));
-    while (static_cast<int>(c->lanes.size()) + 1 < want) {
-        mnenc_ctx* lane = nullptr;
-        const int rc = makeLane(c, std::max(1, c->hostThreads / 2), &lane);
-        if (lane) c->lanes.push_back(lane);
-        if (rc) return rc;
-    }
-    std::vector<mnenc_ctx*> lanes{c};
-    for (int i = 0; i + 1 < want; ++i) {
-        mnenc_ctx* l = c->lanes[i];
-        std::memcpy(l->hQuant, c->hQuant, sizeof(c->hQuant));  // the device table is shared; the header needs the host copy
-        l->quantSet = true;
-        lanes.push_back(l);
+    std::vector<mnenc_ctx*> lanes;
+    if (const int rc = acquireLanes(c, n_images, lanes)) return rc;
+    const int want = static_cast<int>(lanes.size());
+    for (int i = 1; i < want; ++i) {
+        std::memcpy(lanes[i]->hQuant, c->hQuant, sizeof(c->hQuant));  // the device table is shared; the header needs the host copy
+        lanes[i]->quantSet = true;
     }
     std::atomic<size_t> next{0};
     std::atomic<int> firstError{MNENC_OK};
@@ -94,6 +101,54 @@ extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
     // accounting of the whole batch on the parent context (mnenc_last_timing / mnenc_last_work)
     c->launches = 0, c->mpFlops = 0, c->ms[1] = 0;
     for (int li = 0; li < want; ++li) c->launches += launches[li], c->mpFlops += flops[li], c->ms[1] += mpMs[li];
+    c->ms[7] = static_cast<float>(nowMs() - t0);
+    return MNENC_OK;
+}
+
+// Decoder twin: n independent `.mn` streams -> n images (decodeImageFast in a loop). The entropy decode of one stream is one
+// serial chain on one host thread (decode_host.cpp), so the lanes here buy host parallelism first, copy/kernel overlap second.
+extern "C" int mnenc_decode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_t* const* mn, const size_t* mn_bytes, uint8_t** rgb,
+                                       size_t* width, size_t* height) {
+    if (!c || (n_images && (!mn || !mn_bytes || !rgb || !width || !height))) return fail(MNENC_ERR_ARG, "null argument");
+    for (size_t i = 0; i < n_images; ++i) rgb[i] = nullptr, width[i] = height[i] = 0;
+    if (n_images == 0) return MNENC_OK;
+    CU(cudaSetDevice(c->device));
+    std::vector<mnenc_ctx*> lanes;
+    if (const int rc = acquireLanes(c, n_images, lanes)) return rc;
+    const int want = static_cast<int>(lanes.size());
+    std::atomic<size_t> next{0};
+    std::atomic<int> firstError{MNENC_OK};
+    int launches[8] = {};
+    auto work = [&](int li) {
+        mnenc_ctx* l = lanes[li];
+        cudaSetDevice(l->device);
+        while (firstError.load(std::memory_order_relaxed) == MNENC_OK) {
+            const size_t i = next.fetch_add(1);
+            if (i >= n_images) break;
+            const int rc = mnenc_decode_rgb8(l, mn[i], mn_bytes[i], &rgb[i], &width[i], &height[i]);
+            if (rc != MNENC_OK) {
+                int expected = MNENC_OK;
+                if (firstError.compare_exchange_strong(expected, rc)) c->laneError = "stream " + std::to_string(i) + ": " + mnenc_last_error();
+                break;
+            }
+            launches[li] += l->launches;
+        }
+    };
+    const double t0 = nowMs();
+    std::vector<std::thread> threads;
+    for (int li = 1; li < want; ++li) threads.emplace_back(work, li);
+    work(0);
+    for (auto& t : threads) t.join();
+    if (const int rc = firstError.load()) {
+        for (size_t i = 0; i < n_images; ++i) {
+            resultRelease(rgb[i]);
+            rgb[i] = nullptr, width[i] = height[i] = 0;
+        }
+        return fail(rc, c->laneError);
+    }
+    c->launches = 0;
+    for (int li = 0; li < want; ++li) c->launches += launches[li];
+    for (auto& m : c->ms) m = 0;
     c->ms[7] = static_cast<float>(nowMs() - t0);
     return MNENC_OK;
 }

@@ -90,7 +90,6 @@ public:
         }
     }
 
-private:
     void refill() {
         if (cnt_ < 0) return;  // already past the end: keep delivering zeros
         if (end_ - ptr_ >= 8) {
@@ -109,6 +108,7 @@ private:
             }
         }
     }
+    // state (public: HuffTable::decode keeps it in registers across its fast loop)
     const uint8_t* base_;
     const uint8_t* ptr_;
     const uint8_t* end_;
@@ -138,6 +138,7 @@ struct HuffTable {
     uint32_t firstIndex[kMaxCodeLen + 2] = {};
     uint32_t count[kMaxCodeLen + 2] = {};
     std::vector<uint32_t> lut;               // [1 << kLutBits]: index << 8 | length, 0 = not resolved by the table
+    std::vector<uint32_t> fast;              // same slots: symbol << 8 | length, or kSpecial (pseudo-EOF, long code, no code)
 
     void read(BitReader& in) {
         maxLen = static_cast<int>(in.read(8));
@@ -173,6 +174,7 @@ struct HuffTable {
         int prevLen = 0;
         uint32_t index = 0;
         lut.assign(size_t{1} << kLutBits, 0u);
+        fast.assign(size_t{1} << kLutBits, kSpecial);
         for (int len = 1; len <= maxLen; ++len) {
             if (count[len] == 0) continue;
             code <<= (len - prevLen);
@@ -185,6 +187,9 @@ struct HuffTable {
                     const uint32_t entry = (index + i) << 8 | static_cast<uint32_t>(len);
                     const size_t lo = static_cast<size_t>(code + i) << (kLutBits - len);
                     std::fill(lut.begin() + lo, lut.begin() + lo + (size_t{1} << (kLutBits - len)), entry);
+                    if (index + i != total - 1)
+                        std::fill(fast.begin() + lo, fast.begin() + lo + (size_t{1} << (kLutBits - len)),
+                                  static_cast<uint32_t>(symbols[index + i]) << 8 | static_cast<uint32_t>(len));
                 }
             }
             code += count[len];
@@ -193,32 +198,64 @@ struct HuffTable {
     }
 
     // Payload codes up to the pseudo-EOF into out[0, cap); returns the number of symbols (Huffman.cpp:227-243).
+    // Fast loop: one unconditional 8-byte refill, then up to four table hits (4 x 12 <= 56 valid bits) without any end-of-stream
+    // or capacity test; everything else (long codes, the pseudo-EOF, the last bytes, the last symbols) goes through step().
     size_t decode(BitReader& in, uint16_t* out, size_t cap) const {
         size_t n = 0;
-        const uint32_t eof = total - 1;
         for (;;) {
-            const uint64_t window = in.peek(kMaxCodeLen);
-            uint32_t entry = lut[window >> (kMaxCodeLen - kLutBits)];
-            uint32_t index = 0, len;
-            if (entry) {
-                index = entry >> 8, len = entry & 0xFF;
-            } else {
-                len = 0;
-                for (int l = kLutBits + 1; l <= maxLen; ++l) {
-                    const uint64_t v = window >> (kMaxCodeLen - l);
-                    if (count[l] && v >= firstCode[l] && v - firstCode[l] < count[l]) {
-                        index = firstIndex[l] + static_cast<uint32_t>(v - firstCode[l]), len = static_cast<uint32_t>(l);
+            while (in.end_ - in.ptr_ >= 8 && n + 4 <= cap && in.cnt_ >= 0) {
+                uint64_t w;
+                std::memcpy(&w, in.ptr_, 8);
+                uint64_t buf = in.buf_ | (__builtin_bswap64(w) >> in.cnt_);
+                in.ptr_ += (63 - in.cnt_) >> 3;
+                int cnt = in.cnt_ | 56;
+                bool special = false;
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t e = fast[buf >> (64 - kLutBits)];
+                    if (e >= kSpecial) {
+                        special = true;
                         break;
                     }
+                    buf <<= (e & 0xFF);
+                    cnt -= static_cast<int>(e & 0xFF);
+                    out[n++] = static_cast<uint16_t>(e >> 8);
                 }
-                if (!len) throw Bad{"bit pattern is not a Huffman code"};
+                in.buf_ = cnt < 64 ? buf & ~((1ull << (64 - cnt)) - 1ull) : buf;  // drop the partial byte (BitReader's invariant)
+                in.cnt_ = cnt;
+                if (special) break;
             }
-            in.skip(static_cast<int>(len));
-            if (in.overrun()) throw Bad{"Huffman payload without pseudo-EOF"};
-            if (index == eof) return n;
-            if (n >= cap) throw Bad{"sequence longer than the block counts allow"};
-            out[n++] = symbols[index];
+            if (step(in, out, n, cap)) return n;
         }
+    }
+
+    static constexpr uint32_t kSpecial = 1u << 24;  // `fast` entry: pseudo-EOF or a code longer than the table
+
+private:
+    // One symbol, all checks. Returns true at the pseudo-EOF.
+    bool step(BitReader& in, uint16_t* out, size_t& n, size_t cap) const {
+        const uint32_t eof = total - 1;
+        const uint64_t window = in.peek(kMaxCodeLen);
+        const uint32_t entry = lut[window >> (kMaxCodeLen - kLutBits)];
+        uint32_t index = 0, len;
+        if (entry) {
+            index = entry >> 8, len = entry & 0xFF;
+        } else {
+            len = 0;
+            for (int l = kLutBits + 1; l <= maxLen; ++l) {
+                const uint64_t v = window >> (kMaxCodeLen - l);
+                if (count[l] && v >= firstCode[l] && v - firstCode[l] < count[l]) {
+                    index = firstIndex[l] + static_cast<uint32_t>(v - firstCode[l]), len = static_cast<uint32_t>(l);
+                    break;
+                }
+            }
+            if (!len) throw Bad{"bit pattern is not a Huffman code"};
+        }
+        in.skip(static_cast<int>(len));
+        if (in.overrun()) throw Bad{"Huffman payload without pseudo-EOF"};
+        if (index == eof) return true;
+        if (n >= cap) throw Bad{"sequence longer than the block counts allow"};
+        out[n++] = symbols[index];
+        return false;
     }
 };
 

@@ -101,6 +101,13 @@ int mnenc_decode_rgb8(mnenc_t* ctx, const uint8_t* mn, size_t mn_bytes, uint8_t*
 /* Same, writing into device memory of the context's GPU (capacity_bytes >= row_stride_bytes * (height - 1) + 3 * width). */
 int mnenc_decode_rgb8_device(mnenc_t* ctx, const uint8_t* mn, size_t mn_bytes, uint8_t* rgb_dev, size_t capacity_bytes,
                              size_t row_stride_bytes, size_t* width, size_t* height);
+/*
+ * Batch / throughput mode of the decoder: n_images independent streams -> n_images images, what decodeImageFast gives in a
+ * loop; pipelined over the same lanes as mnenc_encode_batch_rgb8 (one host thread per lane runs the entropy decode of its
+ * stream while the other lanes' kernels and copies proceed). rgb[i] from mnenc_free(); on error every rgb[i] is NULL.
+ */
+int mnenc_decode_batch_rgb8(mnenc_t* ctx, size_t n_images, const uint8_t* const* mn, const size_t* mn_bytes, uint8_t** rgb,
+                            size_t* width, size_t* height);
 /* Header only (host, no GPU): CompressedImage.cpp:721-736. Any out pointer may be NULL; quant receives 3 * K floats (<= 96). */
 int mnenc_stream_info(const uint8_t* mn, size_t mn_bytes, size_t* width, size_t* height, int* K, int* block_size, float* quant);
 /*
