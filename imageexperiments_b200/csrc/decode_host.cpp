@@ -139,6 +139,8 @@ struct HuffTable {
     uint32_t count[kMaxCodeLen + 2] = {};
     std::vector<uint32_t> lut;               // [1 << kLutBits]: index << 8 | length, 0 = not resolved by the table
     std::vector<uint32_t> fast;              // same slots: symbol << 8 | length, or kSpecial (pseudo-EOF, long code, no code)
+    std::vector<uint64_t> pair;              // same slots, up to TWO codes: bits 0-7 total length, 8-15 symbols (0 = special),
+                                             // 16-31 first symbol, 32-47 second symbol
 
     void read(BitReader& in) {
         maxLen = static_cast<int>(in.read(8));
@@ -195,15 +197,27 @@ struct HuffTable {
             code += count[len];
             index += count[len];
         }
+        // second code of a slot: whatever single code starts in the bits the first one leaves over
+        pair.assign(size_t{1} << kLutBits, 0ull);
+        for (uint32_t slot = 0; slot < (1u << kLutBits); ++slot) {
+            const uint32_t e0 = fast[slot];
+            if (e0 >= kSpecial) continue;
+            const uint32_t l0 = e0 & 0xFF;
+            uint64_t v = static_cast<uint64_t>(e0 >> 8) << 16 | 1u << 8 | l0;
+            const uint32_t e1 = fast[(slot << l0) & ((1u << kLutBits) - 1u)];
+            if (e1 < kSpecial && l0 + (e1 & 0xFF) <= static_cast<uint32_t>(kLutBits))
+                v = static_cast<uint64_t>(e1 >> 8) << 32 | static_cast<uint64_t>(e0 >> 8) << 16 | 2u << 8 | (l0 + (e1 & 0xFF));
+            pair[slot] = v;
+        }
     }
 
     // Payload codes up to the pseudo-EOF into out[0, cap); returns the number of symbols (Huffman.cpp:227-243).
-    // Fast loop: one unconditional 8-byte refill, then up to four table hits (4 x 12 <= 56 valid bits) without any end-of-stream
-    // or capacity test; everything else (long codes, the pseudo-EOF, the last bytes, the last symbols) goes through step().
+    // Fast loop: one unconditional 8-byte refill, then up to four table hits (4 x 12 <= 56 valid bits), each giving one or two
+    // symbols, without any end-of-stream or capacity test; everything else (long codes, the pseudo-EOF, the last bytes, the last symbols) goes through step().
     size_t decode(BitReader& in, uint16_t* out, size_t cap) const {
         size_t n = 0;
         for (;;) {
-            while (in.end_ - in.ptr_ >= 8 && n + 4 <= cap && in.cnt_ >= 0) {
+            while (in.end_ - in.ptr_ >= 8 && n + 8 <= cap && in.cnt_ >= 0) {
                 uint64_t w;
                 std::memcpy(&w, in.ptr_, 8);
                 uint64_t buf = in.buf_ | (__builtin_bswap64(w) >> in.cnt_);
@@ -211,14 +225,17 @@ struct HuffTable {
                 int cnt = in.cnt_ | 56;
                 bool special = false;
                 for (int k = 0; k < 4; ++k) {
-                    const uint32_t e = fast[buf >> (64 - kLutBits)];
-                    if (e >= kSpecial) {
+                    const uint64_t e = pair[buf >> (64 - kLutBits)];
+                    const uint32_t got = static_cast<uint32_t>(e >> 8) & 0xFF;
+                    if (got == 0) {
                         special = true;
                         break;
                     }
+                    out[n] = static_cast<uint16_t>(e >> 16);
+                    out[n + 1] = static_cast<uint16_t>(e >> 32);  // junk when got == 1: overwritten by the next symbol
+                    n += got;
                     buf <<= (e & 0xFF);
                     cnt -= static_cast<int>(e & 0xFF);
-                    out[n++] = static_cast<uint16_t>(e >> 8);
                 }
                 in.buf_ = cnt < 64 ? buf & ~((1ull << (64 - cnt)) - 1ull) : buf;  // drop the partial byte (BitReader's invariant)
                 in.cnt_ = cnt;
