@@ -58,8 +58,12 @@ struct ResultPool {
     std::vector<Buf> bufs;
     // Idle buffers kept for reuse. cudaHostAlloc / cudaFreeHost synchronise the device, so the limits are generous: a batch of
     // 16 streams in flight must recycle without ever touching the allocator in steady state.
+    // Decoded images are 48 MB each at 16 MP: a batch of 32 holds 1.7 GB at once, hence 4 GiB (MNENC_POOL_MB overrides).
     static constexpr size_t kMaxIdle = 64;
-    static constexpr size_t kMaxIdleBytes = size_t(1) << 30;
+    size_t maxIdleBytes = size_t(4) << 30;
+    ResultPool() {
+        if (const char* e = std::getenv("MNENC_POOL_MB")) maxIdleBytes = static_cast<size_t>(std::max(0L, std::atol(e))) << 20;
+    }
 };
 ResultPool& resultPool() {
     static ResultPool* pool = new ResultPool;  // leaked on purpose: no CUDA calls from static destructors
@@ -106,7 +110,7 @@ void resultRelease(uint8_t* p) {
             std::free(p);
             return;
         }
-        if (idle > ResultPool::kMaxIdle || idleBytes > ResultPool::kMaxIdleBytes) {
+        if (idle > ResultPool::kMaxIdle || idleBytes > rp.maxIdleBytes) {
             size_t k = rp.bufs.size();
             for (size_t i = 0; i < rp.bufs.size(); ++i)
                 if (!rp.bufs[i].inUse && (k == rp.bufs.size() || rp.bufs[i].cap < rp.bufs[k].cap)) k = i;

@@ -45,14 +45,17 @@ def main():
     ms_dev, ph_dev = run(lambda d: mn.decodeImageFast(d, ctx, out=out))
     # throughput mode: 32 streams per call over the lanes (host threads run the entropy decode of different streams in parallel)
     batch = [ring[i % 4] for i in range(32)]
+    imgs = None
     for _ in range(2):
-        mn.decodeImageBatch(batch, ctx, zero_copy=True)
-    t = time.perf_counter()
+        imgs = None  # hand the 32 pinned blocks back before the next batch asks for 32
+        imgs = mn.decodeImageBatch(batch, ctx, zero_copy=True)
     reps = max(1, a.steps // 3)
+    t = time.perf_counter()
     for _ in range(reps):
+        imgs = None
         imgs = mn.decodeImageBatch(batch, ctx, zero_copy=True)
     ms_batch = (time.perf_counter() - t) / reps * 1e3
-    del imgs
+    imgs = None
     line = {"metric": "decode_throughput", "unit": "MP/s", "workload": f"{W}x{H} q3.5 K32, stream from the GPU encoder ({len(ring[0])} B)",
             "e2e": {"value": round(mp / ms_host * 1e3, 1), "ms": round(ms_host, 3), "h2d_bytes_per_step": len(ring[0]), "d2h_bytes_per_step": 3 * W * H},
             "pixels_on_device": {"value": round(mp / ms_dev * 1e3, 1), "ms": round(ms_dev, 3)},
