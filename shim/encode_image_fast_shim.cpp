@@ -4,6 +4,7 @@
 // where the reference tree is present (oracle/Makefile target `shim`, output in oracle/_ref/).
 //
 //   compressed::encodeImageFast   CompressionLib/inc/CompressedImage.h:67-73, src/CompressedImage.cpp:578-633
+//   compressed::decodeImageFast   CompressionLib/inc/CompressedImage.h:75,    src/CompressedImage.cpp:837-889
 //
 // The dictionary never crosses the reference API as data: encodeImageFast receives three opaque
 // DynamicDictionaryFunctionFast callbacks (MatchingPursuit.h:20). They are pure functions of their arguments
@@ -49,11 +50,11 @@ void failWith(const char* what) { throw new std::range_error(std::string(what) +
 
 }  // namespace
 
-std::unique_ptr<uint8_t[]> encodeImageFast(const img::image<img::rgb>* imgIn, const size_t K, const size_t blockSize,
-                                           const Eigen::VectorXf& quantY, const Eigen::VectorXf& quantU, const Eigen::VectorXf& quantV,
-                                           const matching::DynamicDictionaryFunctionFast& dynamicY,
-                                           const matching::DynamicDictionaryFunctionFast& dynamicU,
-                                           const matching::DynamicDictionaryFunctionFast& dynamicV, size_t& outputByteSize) {
+namespace {
+
+// GPU context for the dictionary behind the three callbacks (created once per dictionary build and K, then cached).
+mnenc_t* contextFor(const size_t K, const size_t blockSize, const matching::DynamicDictionaryFunctionFast& dynamicY,
+                    const matching::DynamicDictionaryFunctionFast& dynamicU, const matching::DynamicDictionaryFunctionFast& dynamicV) {
     const int k = static_cast<int>(K);
     // --- dictionary identity probe (one callback call) ---
     const Eigen::MatrixXf probeM = callDynamic(dynamicY, k, 0);
@@ -81,23 +82,53 @@ std::unique_ptr<uint8_t[]> encodeImageFast(const img::image<img::rgb>* imgIn, co
         g_cache.K = k;
         g_cache.probe = probe;
     }
+    return g_cache.ctx;
+}
+
+}  // namespace
+
+std::unique_ptr<uint8_t[]> encodeImageFast(const img::image<img::rgb>* imgIn, const size_t K, const size_t blockSize,
+                                           const Eigen::VectorXf& quantY, const Eigen::VectorXf& quantU, const Eigen::VectorXf& quantV,
+                                           const matching::DynamicDictionaryFunctionFast& dynamicY,
+                                           const matching::DynamicDictionaryFunctionFast& dynamicU,
+                                           const matching::DynamicDictionaryFunctionFast& dynamicV, size_t& outputByteSize) {
+    mnenc_t* ctx = contextFor(K, blockSize, dynamicY, dynamicU, dynamicV);
     std::vector<float> quant(3 * K);
     for (size_t i = 0; i < K; ++i) {
         quant[i] = quantY[i];
         quant[K + i] = quantU[i];
         quant[2 * K + i] = quantV[i];
     }
-    if (mnenc_set_quant(g_cache.ctx, quant.data()) != MNENC_OK) failWith("mnenc_set_quant");
+    if (mnenc_set_quant(ctx, quant.data()) != MNENC_OK) failWith("mnenc_set_quant");
     // img::image<rgb> stores rows contiguously (image.h:67-75): data + y*w
     uint8_t* bytes = nullptr;
     size_t n = 0;
-    if (mnenc_encode_rgb8(g_cache.ctx, reinterpret_cast<const uint8_t*>(imgIn->data), imgIn->width(), imgIn->height(),
+    if (mnenc_encode_rgb8(ctx, reinterpret_cast<const uint8_t*>(imgIn->data), imgIn->width(), imgIn->height(),
                           imgIn->width() * sizeof(img::rgb), &bytes, &n) != MNENC_OK)
         failWith("mnenc_encode_rgb8");
     std::unique_ptr<uint8_t[]> out = std::make_unique<uint8_t[]>(n);
     std::memcpy(out.get(), bytes, n);
     mnenc_free(bytes);
     outputByteSize = n;
+    return out;
+}
+
+// decodeImageFast (CompressedImage.cpp:837-889). The reference builds its context inside readCompressedFast (:726,
+// createCompressionContextFast(K, blockSize, 0.0)); the shim does the same once per (K, blockSize) — the dictionary does not
+// depend on the quality argument — and hands its callbacks to contextFor(), so the GPU decodes with the floats of THIS build.
+std::unique_ptr<img::image<img::rgb>> decodeImageFast(const uint8_t bytes[], size_t byteSize) {
+    size_t w = 0, h = 0;
+    int K = 0, blockSize = 0;
+    if (mnenc_stream_info(bytes, byteSize, &w, &h, &K, &blockSize, nullptr) != MNENC_OK) failWith("Invalid input data");
+    static std::unique_ptr<compressed::CompressionContextFast> refCtx;
+    if (!refCtx || refCtx->K != static_cast<size_t>(K) || refCtx->BlockSize != static_cast<size_t>(blockSize))
+        refCtx = compressed::createCompressionContextFast(K, blockSize, 0.0);
+    mnenc_t* ctx = contextFor(refCtx->K, refCtx->BlockSize, refCtx->Y.Dynamic, refCtx->U.Dynamic, refCtx->V.Dynamic);
+    uint8_t* rgb = nullptr;
+    if (mnenc_decode_rgb8(ctx, bytes, byteSize, &rgb, &w, &h) != MNENC_OK) failWith("Invalid bitstream");
+    auto out = std::make_unique<img::image<img::rgb>>(static_cast<int>(w), static_cast<int>(h), false);
+    std::memcpy(out->data, rgb, w * h * sizeof(img::rgb));
+    mnenc_free(rgb);
     return out;
 }
 
@@ -115,6 +146,21 @@ extern "C" int mnenc_shim_selftest(const uint8_t* rgb, size_t w, size_t h, doubl
         *out = static_cast<uint8_t*>(std::malloc(n ? n : 1));
         std::memcpy(*out, bytes.get(), n);
         *outBytes = n;
+        return 0;
+    } catch (std::exception* e) {
+        return -1;
+    } catch (...) {
+        return -2;
+    }
+}
+
+// C entry used by tests/test_shim.py: decodes through the shim's decodeImageFast.
+extern "C" int mnenc_shim_selftest_decode(const uint8_t* mn, size_t n, uint8_t** out, size_t* w, size_t* h) {
+    try {
+        auto im = mnenc_shim::decodeImageFast(mn, n);
+        *w = im->width(), *h = im->height();
+        *out = static_cast<uint8_t*>(std::malloc(*w * *h * 3 + 1));
+        std::memcpy(*out, im->data, *w * *h * 3);
         return 0;
     } catch (std::exception* e) {
         return -1;
