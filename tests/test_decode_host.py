@@ -90,3 +90,62 @@ def test_parse_reference_fixture(oraclelib):
     want = oraclelib.parse(data)
     same_parse(p, want["lengths"], want["streams"])
     print(f"fixture: {len(data)} B, {sum(len(s) for s in p['streams'])} symbols parsed (twice) in {ms:.1f} ms")
+
+
+def crafted(oraclelib, K, w, h, counts, pairs):
+    """counts [nb,3], pairs [nb,3,K,2] (raw symbols, any u16 values) -> stream written by the oracle's writeCompressed."""
+    return oraclelib.write_file(K, 8, w, h, np.arange(1, 3 * K + 1, dtype=np.float32), counts, pairs)
+
+
+def expected_streams(K, counts, pairs):
+    """Stream (layer, depth, part) = entries of the blocks with count > depth, block order (CompressedImage.cpp:612-629)."""
+    out = []
+    for ch in range(3):
+        for d in range(K):
+            sel = counts[:, ch] > d
+            for part in range(2):
+                out.append(pairs[sel, ch, d, part])
+    return out
+
+
+@pytest.mark.parametrize("kind", ["uniform16", "geometric", "constant", "sparse", "bimodal", "ramp"])
+@pytest.mark.parametrize("K", [1, 8, 32])
+def test_parse_crafted_symbol_distributions(oraclelib, kind, K):
+    """Symbol statistics the matching pursuit never produces, to reach every branch of the reader: 16-bit alphabets with
+    codes far beyond the 12-bit table, raw vs Elias-Fano symbol lists, Golomb-coded sequences of every parameter, runs across
+    the 32 769 chunk limit, single-symbol and empty streams."""
+    rng = np.random.default_rng(sum(map(ord, kind)) * 100 + K)
+    w, h = 8 * 70, 8 * 64
+    nb = 70 * 64
+    if kind == "constant":
+        w, h, nb = 8 * 300, 8 * 120, 36000  # one run of 36 000 > 32 769
+    if kind == "sparse":
+        counts = (rng.random((nb, 3)) < 0.002).astype(np.uint16) * K  # nearly empty streams
+    elif kind == "constant":
+        counts = np.full((nb, 3), K, np.uint16)
+    else:
+        counts = rng.integers(0, K + 1, (nb, 3)).astype(np.uint16)
+    shape = (nb, 3, K, 2)
+    if kind == "uniform16":
+        pairs = rng.integers(0, 65536, shape)
+    elif kind == "geometric":
+        pairs = np.minimum(rng.geometric(0.02, shape) - 1, 65535)
+    elif kind == "constant":
+        pairs = np.full(shape, 4321)
+        pairs[:, 1] = 0          # leading zeros: not a repeat of the initial prevVal (Huffman.cpp:253-255)
+        pairs[::7000, 2, 0, 0] = 9  # a few breaks
+    elif kind == "sparse":
+        pairs = rng.integers(0, 3, shape)
+    elif kind == "bimodal":
+        pairs = np.where(rng.random(shape) < 0.97, rng.integers(0, 4, shape), rng.integers(0, 65536, shape))  # short + very long codes
+    else:
+        pairs = (np.arange(np.prod(shape)).reshape(shape) // 3) % 50000
+    pairs = pairs.astype(np.uint16)
+    pairs[:, :, 0, 1] %= 16384  # DC chain: zig-zag of a difference must fit 16 bits to survive (CompressedImage.cpp:487-505 truncates)
+    pairs[np.broadcast_to(np.arange(K)[None, None, :, None] >= counts[:, :, None, None], shape)] = 0  # entries beyond count are not coded
+    data = crafted(oraclelib, K, w, h, counts, pairs)
+    p = mn.parseStream(data)
+    assert p["K"] == K and (p["width"], p["height"]) == (w, h)
+    same_parse(p, counts.reshape(-1), expected_streams(K, counts, pairs))
+    op = oraclelib.parse(data)  # and the oracle's own reader agrees
+    same_parse(p, op["lengths"], op["streams"])
