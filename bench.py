@@ -104,6 +104,34 @@ def cpu_baseline_sample():
 _REF = {}
 
 
+def decode_sample(ctx, inputs):
+    """Secondary figure (not the headline metric): decodeImageFast / decodeImageBatch of streams the encoder
+    just wrote, host stream in -> host pixels out. Never allowed to break the bench line."""
+    try:
+        import imageexperiments_b200 as mn
+        streams = [mn.encodeImageFast(inputs[i % len(inputs)], ctx) for i in range(RING)]
+        for s in streams[:2]:
+            mn.decodeImageFast(s, ctx, zero_copy=True)
+        t0 = time.perf_counter()
+        for i in range(8):
+            img = mn.decodeImageFast(streams[i % RING], ctx, zero_copy=True)
+        single = (time.perf_counter() - t0) / 8
+        h, w = img.shape[:2]
+        img = None
+        batch = [streams[i % RING] for i in range(16)]
+        out = mn.decodeImageBatch(batch, ctx, zero_copy=True)
+        out = None
+        t0 = time.perf_counter()
+        out = mn.decodeImageBatch(batch, ctx, zero_copy=True)
+        dt = time.perf_counter() - t0
+        out = None
+        return {"single_image_e2e": round(w * h / 1e6 / single, 1), "batch16_e2e": round(16 * w * h / 1e6 / dt, 1), "unit": "MP/s",
+                "single_image_ms": round(single * 1e3, 3), "note": "host .mn stream -> host RGB8; entropy decode on the host (serial bit "
+                "chain per image), reconstruction on the GPU; pixels bit-identical to the reference decoder (tests/test_gpu_decode.py)"}
+    except Exception as e:  # noqa: BLE001
+        return {"error": repr(e)}
+
+
 def _ref_tile(i):
     R, ctx, tiles = _REF["R"], _REF["ctx"], _REF["tiles"]
     return len(R.encode(ctx, tiles[i]))
@@ -290,6 +318,7 @@ def run_ours(args):
         }
         if world == 1:
             line["cpu_baseline"] = cpu_baseline_sample()
+            line["decode"] = decode_sample(ctx, pinned)
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
