@@ -70,7 +70,7 @@ def load() -> C.CDLL:
     L.mnenc_decode_rgb8_device.argtypes = [_vp, _vp, _sz, _vp, _sz, _sz, _vp, _vp]
     L.mnenc_decode_batch_rgb8.argtypes = [_vp, _sz, _vp, _vp, _vp, _vp, _vp]
     L.mnenc_stream_info.argtypes = [_vp, _sz, _vp, _vp, _vp, _vp, _vp]
-    L.mnenc_debug_parse.argtypes = [_vp, _sz, _vp, _sz, _vp, _vp, _sz]
+    L.mnenc_debug_parse.argtypes = [_vp, _sz, _vp, _sz, _vp, _vp, _sz, C.c_int]
     _lib = L
     return L
 

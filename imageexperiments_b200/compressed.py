@@ -265,18 +265,18 @@ def streamInfo(data) -> dict:
     return dict(width=w.value, height=h.value, K=K.value, blockSize=bs.value, Quant=q[: 3 * K.value].copy())
 
 
-def parseStream(data) -> dict:
+def parseStream(data, threads: int = 1) -> dict:
     """Debug tap, host only: compressed::readCompressedFast (CompressedImage.cpp:709-782) -> lengths [3*nblocks] and the 6K
-    symbol streams (run lengths expanded, DC chains undone)."""
+    symbol streams (run lengths expanded, DC chains undone). ``threads`` > 1 uses the decoder's parallel reader (same result)."""
     L = _lib.load()
     info = streamInfo(data)
     ptr, n, keep = _stream(data)
     nb = ((info["width"] + 7) // 8) * ((info["height"] + 7) // 8)
     lengths = np.zeros(3 * nb, np.uint16)
     offs = np.zeros(6 * info["K"] + 1, np.uint64)
-    _lib.check(L.mnenc_debug_parse(ptr, n, _p(lengths), lengths.size, _p(offs), None, 0))
+    _lib.check(L.mnenc_debug_parse(ptr, n, _p(lengths), lengths.size, _p(offs), None, 0, threads))
     symbols = np.zeros(int(offs[-1]) + 1, np.uint16)
-    _lib.check(L.mnenc_debug_parse(ptr, n, _p(lengths), lengths.size, _p(offs), _p(symbols), symbols.size))
+    _lib.check(L.mnenc_debug_parse(ptr, n, _p(lengths), lengths.size, _p(offs), _p(symbols), symbols.size, threads))
     o = offs.astype(np.int64)
     return dict(info, lengths=lengths, streams=[symbols[o[i]:o[i + 1]] for i in range(len(o) - 1)])
 

@@ -122,6 +122,11 @@ extern "C" int mnenc_decode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
     auto work = [&](int li) {
         mnenc_ctx* l = lanes[li];
         cudaSetDevice(l->device);
+        l->inBatch = true;
+        struct Reset {
+            mnenc_ctx* l;
+            ~Reset() { l->inBatch = false; }
+        } reset{l};
         while (firstError.load(std::memory_order_relaxed) == MNENC_OK) {
             const size_t i = next.fetch_add(1);
             if (i >= n_images) break;

@@ -23,11 +23,16 @@ struct DecodeMisc {  // pinned: uploaded tables, downloaded error flag
 int decodeImage(mnenc_ctx* c, const uint8_t* mn, size_t mnBytes, uint8_t* rgbDev, size_t capacity, size_t stride, uint8_t** hostOut,
                 size_t* widthOut, size_t* heightOut) {
     if (!c || !mn || !widthOut || !heightOut) return fail(MNENC_ERR_ARG, "null argument");
+    static const bool envParallel = [] {
+        const char* e = std::getenv("MNENC_DECODE_THREADS");
+        return e && std::atoi(e) > 1;
+    }();
+    const bool parallelReader = envParallel && !c->inBatch;
     if (hostOut) *hostOut = nullptr;
     *widthOut = *heightOut = 0;
     const double t0 = nowMs();
     CU(cudaSetDevice(c->device));
-    MnParser P(mn, mnBytes);
+    MnParser P(mn, mnBytes, parallelReader ? c->pool.get() : nullptr);
     std::string err;
     if (P.readHeader(err)) return fail(MNENC_ERR_STREAM, err);
     const size_t w = P.width, h = P.height, nblocks = P.nblocks, nbc = 3 * nblocks;
@@ -43,30 +48,36 @@ int decodeImage(mnenc_ctx* c, const uint8_t* mn, size_t mnBytes, uint8_t* rgbDev
     c->launches = 0;
     c->haveSymbols = false;  // counts / pairs now hold the DECODED image's symbols
 
-    // `lengths` -> GPU, tile offsets of every (layer, depth) stream
-    CU(c->hDecCounts.ensure(nbc * 2));
-    CU(c->hDecMisc.ensure(sizeof(DecodeMisc)));
-    if (P.readLengths(c->hDecCounts.as<uint16_t>(), err)) return fail(MNENC_ERR_STREAM, err);
-    const double t1 = nowMs();
+    // `lengths` -> GPU, tile offsets of every (layer, depth) stream; then the streams, while the GPU works on the counts.
+    // MNENC_DECODE_THREADS > 1 (single-image calls only): the context's host threads stand by as helpers of the parallel
+    // reader (decode_host.cpp); off by default until it has been measured on the target host.
+    double t1 = t0, t2 = t0;
+    size_t N = 0;
     BackendBuffers b{};
-    b.K = K, b.nblocks = static_cast<uint32_t>(nblocks), b.ntiles = static_cast<uint32_t>((nblocks + kTileBlocks - 1) / kTileBlocks);
-    CU(c->counts.ensure(nbc * 2));
-    CU(c->pairs.ensure(nbc * static_cast<size_t>(K) * 4));
-    CU(c->tileCounts.ensure(static_cast<size_t>(b.ntiles) * 3 * K * 4));
-    CU(c->totals.ensure(3 * kMaxK * 4));
-    CU(c->decQuant.ensure(sizeof(DecodeMisc)));
-    b.counts = c->counts.as<uint16_t>(), b.tileCounts = c->tileCounts.as<uint32_t>(), b.totals = c->totals.as<uint32_t>();
-    CU(cudaMemcpyAsync(c->counts.p, c->hDecCounts.p, nbc * 2, cudaMemcpyHostToDevice, c->stream));
-    c->launches += launchTileCounts(b, c->stream);
-
-    // the streams, while the GPU works on the counts
-    const size_t N = P.streamOffset[6 * K];
-    CU(c->hDecArena.ensure(N * 2 + 16));
-    if (P.readStreams(c->hDecArena.as<uint16_t>(), err)) {
-        cudaStreamSynchronize(c->stream);
-        return fail(MNENC_ERR_STREAM, err);
-    }
-    const double t2 = nowMs();
+    const int rcParse = P.withTeam([&]() -> int {
+        CU(c->hDecCounts.ensure(nbc * 2));
+        CU(c->hDecMisc.ensure(sizeof(DecodeMisc)));
+        if (P.readLengths(c->hDecCounts.as<uint16_t>(), err)) return fail(MNENC_ERR_STREAM, err);
+        t1 = nowMs();
+        b.K = K, b.nblocks = static_cast<uint32_t>(nblocks), b.ntiles = static_cast<uint32_t>((nblocks + kTileBlocks - 1) / kTileBlocks);
+        CU(c->counts.ensure(nbc * 2));
+        CU(c->pairs.ensure(nbc * static_cast<size_t>(K) * 4));
+        CU(c->tileCounts.ensure(static_cast<size_t>(b.ntiles) * 3 * K * 4));
+        CU(c->totals.ensure(3 * kMaxK * 4));
+        CU(c->decQuant.ensure(sizeof(DecodeMisc)));
+        b.counts = c->counts.as<uint16_t>(), b.tileCounts = c->tileCounts.as<uint32_t>(), b.totals = c->totals.as<uint32_t>();
+        CU(cudaMemcpyAsync(c->counts.p, c->hDecCounts.p, nbc * 2, cudaMemcpyHostToDevice, c->stream));
+        c->launches += launchTileCounts(b, c->stream);
+        N = P.streamOffset[6 * K];
+        CU(c->hDecArena.ensure(N * 2 + 16));
+        if (P.readStreams(c->hDecArena.as<uint16_t>(), err)) {
+            cudaStreamSynchronize(c->stream);
+            return fail(MNENC_ERR_STREAM, err);
+        }
+        t2 = nowMs();
+        return MNENC_OK;
+    });
+    if (rcParse) return rcParse;
     CU(c->arena.ensure(N * 2 + 16));
     b.arena = c->arena.as<uint16_t>();
     if (N) CU(cudaMemcpyAsync(c->arena.p, c->hDecArena.p, N * 2, cudaMemcpyHostToDevice, c->stream));
@@ -151,16 +162,22 @@ extern "C" int mnenc_stream_info(const uint8_t* mn, size_t mn_bytes, size_t* wid
 }
 
 extern "C" int mnenc_debug_parse(const uint8_t* mn, size_t mn_bytes, uint16_t* lengths, size_t lengths_capacity, uint64_t* stream_offsets,
-                                 uint16_t* symbols, size_t symbols_capacity) {
+                                 uint16_t* symbols, size_t symbols_capacity, int threads) {
     if (!mn || !lengths || !stream_offsets) return fail(MNENC_ERR_ARG, "null argument");
-    MnParser P(mn, mn_bytes);
+    std::unique_ptr<HostPool> pool;
+    if (threads > 1) pool = std::make_unique<HostPool>(std::min(threads, 64));
+    MnParser P(mn, mn_bytes, pool.get());
     std::string err;
     if (P.readHeader(err)) return fail(MNENC_ERR_STREAM, err);
     if (lengths_capacity < 3 * P.nblocks) return fail(MNENC_ERR_ARG, "lengths buffer too small");
-    if (P.readLengths(lengths, err)) return fail(MNENC_ERR_STREAM, err);
-    for (int s = 0; s <= 6 * P.K; ++s) stream_offsets[s] = P.streamOffset[s];
-    if (!symbols) return MNENC_OK;  // sizes only
-    if (symbols_capacity < P.streamOffset[6 * P.K]) return fail(MNENC_ERR_ARG, "symbols buffer too small");
-    if (P.readStreams(symbols, err)) return fail(MNENC_ERR_STREAM, err);
-    return MNENC_OK;
+    int code = MNENC_OK;
+    P.withTeam([&] {
+        if (P.readLengths(lengths, err)) return code = MNENC_ERR_STREAM;
+        for (int s = 0; s <= 6 * P.K; ++s) stream_offsets[s] = P.streamOffset[s];
+        if (!symbols) return 0;  // sizes only
+        if (symbols_capacity < P.streamOffset[6 * P.K]) return err = "symbols buffer too small", code = MNENC_ERR_ARG;
+        if (P.readStreams(symbols, err)) return code = MNENC_ERR_STREAM;
+        return 0;
+    });
+    return code == MNENC_OK ? MNENC_OK : fail(code, err);
 }

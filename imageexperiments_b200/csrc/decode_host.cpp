@@ -14,11 +14,18 @@
 // symbols go straight into their final place in pinned memory, and the pixels are rebuilt on the GPU (decode_kernels.cu).
 //
 // Every length and count that the reference trusts is checked: a damaged stream gives an error, never an out-of-range access.
+#include <sched.h>
+
+#include <algorithm>
+#include <atomic>
 #include <bit>
+#include <cmath>
 #include <cstring>
+#include <functional>
 #include <string>
 #include <vector>
 
+#include "host_pool.h"
 #include "mnenc_internal.h"
 
 namespace mnenc {
@@ -52,6 +59,14 @@ public:
         return hi << 16 | static_cast<uint32_t>(read(16));
     }
     bool overrun() const { return cnt_ < 0; }
+    void seek(uint64_t bitPos) {  // absolute position; must lie inside the data
+        ptr_ = base_ + (bitPos >> 3);
+        buf_ = 0, cnt_ = 0;
+        if (bitPos & 7) {
+            refill();
+            skip(static_cast<int>(bitPos & 7));
+        }
+    }
     uint64_t position() const { return static_cast<uint64_t>(ptr_ - base_) * 8 - static_cast<uint64_t>(cnt_); }
     // number of leading one bits (unary quotient of a Golomb code), consumed together with the terminating zero
     uint32_t readUnaryOnes() {
@@ -124,6 +139,70 @@ inline uint32_t eliasFanoBound(uint32_t n, uint32_t maxSymbol) {
 }
 
 inline int32_t unzigzag(uint32_t x) { return static_cast<int32_t>((x >> 1) ^ -(static_cast<int64_t>(x) & 1)); }  // BitBuffer.h:112-114
+
+// The threads of a HostPool held inside ONE parallelFor for the duration of an image. A sequence's chunks are tiny (tens of
+// microseconds each), far below the wake-up latency of a condition variable, so the helpers spin on an atomic ticket
+// instead: ticket = generation << 32 | next index; a job is published by writing its slot (generation parity) and then
+// storing the new ticket. A helper that draws a stale ticket sees the slot's generation differ and backs off.
+class SpinTeam {
+public:
+    explicit SpinTeam(int threads) : threads_(threads) {}
+    int size() const { return threads_; }
+    void forEach(int n, const std::function<void(int)>& fn) {
+        if (n <= 0) return;
+        if (threads_ <= 1) {
+            for (int i = 0; i < n; ++i) fn(i);
+            return;
+        }
+        const uint64_t g = ++gen_;
+        Job& j = jobs_[g & 1];
+        j.fn.store(&fn, std::memory_order_relaxed);
+        j.n.store(n, std::memory_order_relaxed);
+        j.pending.store(n, std::memory_order_relaxed);
+        j.gen.store(g, std::memory_order_release);
+        ticket_.store(g << 32, std::memory_order_release);
+        drain();
+        while (j.pending.load(std::memory_order_acquire) > 0) pause();
+    }
+    void helper() {  // body of every pool thread but the caller's
+        for (unsigned idle = 0; !quit_.load(std::memory_order_acquire); ++idle) {
+            drain();
+            if ((idle & 63) == 63)
+                sched_yield();  // stay polite when there are more threads than cores
+            else
+                pause();
+        }
+    }
+    void finish() { quit_.store(true, std::memory_order_release); }
+
+private:
+    struct Job {
+        std::atomic<const std::function<void(int)>*> fn{nullptr};
+        std::atomic<int> n{0}, pending{0};
+        std::atomic<uint64_t> gen{0};
+    };
+    static void pause() { __builtin_ia32_pause(); }
+    void drain() {
+        for (;;) {
+            const uint64_t peek = ticket_.load(std::memory_order_acquire);
+            const uint64_t g = peek >> 32;
+            if (g == 0) return;
+            Job& j = jobs_[g & 1];
+            if (j.gen.load(std::memory_order_acquire) != g || static_cast<int>(peek & 0xFFFFFFFFu) >= j.n.load(std::memory_order_relaxed)) return;
+            const uint64_t t = ticket_.fetch_add(1, std::memory_order_acq_rel);
+            if ((t >> 32) != g) continue;  // a new job was published in between: look again
+            const int i = static_cast<int>(t & 0xFFFFFFFFu);
+            if (j.gen.load(std::memory_order_acquire) != g || i >= j.n.load(std::memory_order_relaxed)) return;
+            (*j.fn.load(std::memory_order_relaxed))(i);
+            j.pending.fetch_sub(1, std::memory_order_release);
+        }
+    }
+    int threads_;
+    std::atomic<uint64_t> ticket_{0};
+    std::atomic<bool> quit_{false};
+    uint64_t gen_ = 0;
+    Job jobs_[2];
+};
 
 constexpr int kLutBits = 12;
 constexpr int kMaxCodeLen = 48;
@@ -211,75 +290,240 @@ struct HuffTable {
         }
     }
 
-    // Payload codes up to the pseudo-EOF into out[0, cap); returns the number of symbols (Huffman.cpp:227-243).
-    // Fast loop: one unconditional 8-byte refill, then up to four table hits (4 x 12 <= 56 valid bits), each giving one or two
-    // symbols, without any end-of-stream or capacity test; everything else (long codes, the pseudo-EOF, the last bytes, the last symbols) goes through step().
-    size_t decode(BitReader& in, uint16_t* out, size_t cap) const {
-        size_t n = 0;
+    // Payload codes up to the pseudo-EOF into out[n0, cap); returns the number of symbols (Huffman.cpp:227-243).
+    // fastRun: one unconditional 8-byte refill, then up to four table hits (4 x 12 <= 56 valid bits), each giving one or two
+    // symbols, without any end-of-stream or capacity test; everything else (long codes, the pseudo-EOF, the last bytes, the
+    // last symbols) goes through step().
+    size_t decode(BitReader& in, uint16_t* out, size_t cap, size_t n0 = 0) const {
+        size_t n = n0;
         for (;;) {
-            while (in.end_ - in.ptr_ >= 8 && n + 8 <= cap && in.cnt_ >= 0) {
-                uint64_t w;
-                std::memcpy(&w, in.ptr_, 8);
-                uint64_t buf = in.buf_ | (__builtin_bswap64(w) >> in.cnt_);
-                in.ptr_ += (63 - in.cnt_) >> 3;
-                int cnt = in.cnt_ | 56;
-                bool special = false;
-                for (int k = 0; k < 4; ++k) {
-                    const uint64_t e = pair[buf >> (64 - kLutBits)];
-                    const uint32_t got = static_cast<uint32_t>(e >> 8) & 0xFF;
-                    if (got == 0) {
-                        special = true;
-                        break;
-                    }
-                    out[n] = static_cast<uint16_t>(e >> 16);
-                    out[n + 1] = static_cast<uint16_t>(e >> 32);  // junk when got == 1: overwritten by the next symbol
-                    n += got;
-                    buf <<= (e & 0xFF);
-                    cnt -= static_cast<int>(e & 0xFF);
-                }
-                in.buf_ = cnt < 64 ? buf & ~((1ull << (64 - cnt)) - 1ull) : buf;  // drop the partial byte (BitReader's invariant)
-                in.cnt_ = cnt;
-                if (special) break;
-            }
+            fastRun(in, out, n, cap, ~0ull);
             if (step(in, out, n, cap)) return n;
         }
+    }
+
+    // One sequence split over the threads of `pool` (see decodeParallel below).
+    struct Chunk {
+        uint64_t from = 0, until = 0;   // bit range the chunk's worker is responsible for
+        std::vector<uint16_t> syms;     // its symbols (chunk 0 writes straight into the output instead)
+        std::vector<uint64_t> bnd;      // bit position at which each of its first kBoundaries codes starts
+        size_t count = 0;               // symbols decoded
+        uint64_t endPos = 0;            // where it stopped: a code boundary of ITS walk at or after `until`
+        bool eof = false;               // it stopped at a pseudo-EOF code ...
+        uint64_t eofEnd = 0;            // ... which ends here
+        bool failed = false;            // chunk 0 only: invalid code, capacity exceeded
+        size_t lastBad = 0;             // blind workers: symbols decoded when they last met bits that are no code (0 = never)
+    };
+    static constexpr size_t kBoundaries = 2048;
+    static constexpr uint64_t kMinChunkBits = 1u << 16;
+
+    // Huffman payloads self-synchronise: a decoder started at an arbitrary bit usually falls into step with the true code
+    // boundaries after a few dozen codes. The payload's bit length is estimated from the table (sum over the codes of
+    // length x 2^-length, i.e. the symbol probabilities the lengths imply) and the expected symbol count; it is cut into
+    // chunks; chunk 0 is the true walk and writes into `out`, every other worker starts blind, keeps its symbols aside and
+    // records where its first codes begin. The chunks are then stitched in order: the true walk continues serially from the
+    // end of the previous chunk until it stands on one of the next worker's recorded boundaries — from there on that worker's
+    // symbols ARE the true walk's. A chunk that never falls into step (fixed-length-like codes) is walked serially; a wrong
+    // estimate costs a serial tail or some discarded work. The result is the serial decoder's, symbol for symbol; on
+    // anything unexpected the sequence is simply decoded again serially from its start (which also raises the proper error).
+    size_t decodeParallel(BitReader& in, uint16_t* out, size_t cap, size_t expect, SpinTeam& pool, std::vector<Chunk>& chunks) const {
+        const uint64_t start = in.position(), totalBits = static_cast<uint64_t>(in.end_ - in.base_) * 8;
+        double num = 0.0, den = 0.0;
+        int minLen = 0;
+        for (int l = 1; l <= maxLen; ++l) {
+            if (!count[l]) continue;
+            if (!minLen) minLen = l;
+            const double p = std::ldexp(1.0, -l);
+            num += count[l] * p * l, den += count[l] * p;
+        }
+        if (den <= 0.0 || in.cnt_ < 0) return decode(in, out, cap);
+        const uint64_t est = std::min<uint64_t>(static_cast<uint64_t>(static_cast<double>(expect) * (num / den) * 1.02) + 64, totalBits - std::min(totalBits, start));
+        const size_t nChunks = static_cast<size_t>(std::min<uint64_t>(2 * static_cast<uint64_t>(pool.size()), est / kMinChunkBits));
+        if (nChunks < 2) return decode(in, out, cap);
+        const uint64_t chunkBits = (est + nChunks - 1) / nChunks;
+        const size_t symCap = static_cast<size_t>(chunkBits / static_cast<uint64_t>(minLen)) + 64;
+        if (symCap * nChunks > (size_t{64} << 20)) return decode(in, out, cap);
+        if (chunks.size() < nChunks) chunks.resize(nChunks);
+        for (size_t k = 0; k < nChunks; ++k) {
+            chunks[k].from = start + k * chunkBits;
+            chunks[k].until = std::min(start + (k + 1) * chunkBits, totalBits);
+            if (k && chunks[k].syms.size() < symCap) chunks[k].syms.resize(symCap);
+        }
+        const BitReader proto = in;
+        pool.forEach(static_cast<int>(nChunks), [&](int k) {
+            Chunk& c = chunks[static_cast<size_t>(k)];
+            if (k == 0)
+                runChunk(proto, c, out, cap, 0);
+            else
+                runChunk(proto, c, c.syms.data(), symCap, kBoundaries);
+        });
+        // stitch
+        const Chunk& c0 = chunks[0];
+        if (c0.failed) {
+            in.seek(start);
+            return decode(in, out, cap);
+        }
+        size_t n = c0.count;
+        uint64_t pos = c0.endPos;
+        bool done = c0.eof, positioned = false;
+        uint64_t endBit = c0.eofEnd;
+        for (size_t k = 1; k < nChunks && !done; ++k) {
+            const Chunk& c = chunks[k];
+            size_t bi = 0;
+            bool synced = false;
+            while (pos < c.until) {
+                while (bi < c.bnd.size() && c.bnd[bi] < pos) ++bi;
+                if (bi < c.bnd.size() && c.bnd[bi] == pos && bi <= c.count) {
+                    synced = true;
+                    break;
+                }
+                if (!positioned) in.seek(pos), positioned = true;  // the true walk, one code
+                if (step(in, out, n, cap)) {
+                    done = true;
+                    endBit = in.position();
+                    break;
+                }
+                pos = in.position();
+            }
+            if (synced) {
+                if (c.lastBad > bi + 1) {  // bits that are no code AFTER the walks fell into step: the stream is damaged;
+                    in.seek(start);        // the serial decoder reports it
+                    return decode(in, out, cap);
+                }
+                const size_t add = c.count - bi;
+                if (n + add > cap) throw Bad{"sequence longer than the block counts allow"};
+                std::memcpy(out + n, c.syms.data() + bi, add * sizeof(uint16_t));
+                n += add;
+                pos = c.endPos;
+                positioned = false;
+                if (c.eof) done = true, endBit = c.eofEnd;
+            }
+        }
+        if (done) {
+            in.seek(endBit);
+            return n;
+        }
+        in.seek(pos);  // estimate too short: the rest serially
+        return decode(in, out, cap, n);
     }
 
     static constexpr uint32_t kSpecial = 1u << 24;  // `fast` entry: pseudo-EOF or a code longer than the table
 
 private:
-    // One symbol, all checks. Returns true at the pseudo-EOF.
-    bool step(BitReader& in, uint16_t* out, size_t& n, size_t cap) const {
-        const uint32_t eof = total - 1;
-        const uint64_t window = in.peek(kMaxCodeLen);
-        const uint32_t entry = lut[window >> (kMaxCodeLen - kLutBits)];
-        uint32_t index = 0, len;
-        if (entry) {
-            index = entry >> 8, len = entry & 0xFF;
-        } else {
-            len = 0;
-            for (int l = kLutBits + 1; l <= maxLen; ++l) {
-                const uint64_t v = window >> (kMaxCodeLen - l);
-                if (count[l] && v >= firstCode[l] && v - firstCode[l] < count[l]) {
-                    index = firstIndex[l] + static_cast<uint32_t>(v - firstCode[l]), len = static_cast<uint32_t>(l);
+    // Table hits only, while at least 8 input bytes and 8 output slots remain and the position is below `untilBit`.
+    void fastRun(BitReader& in, uint16_t* out, size_t& n, size_t cap, uint64_t untilBit) const {
+        while (in.end_ - in.ptr_ >= 8 && n + 8 <= cap && in.cnt_ >= 0 &&
+               static_cast<uint64_t>(in.ptr_ - in.base_) * 8 - static_cast<uint64_t>(in.cnt_) < untilBit) {
+            uint64_t w;
+            std::memcpy(&w, in.ptr_, 8);
+            uint64_t buf = in.buf_ | (__builtin_bswap64(w) >> in.cnt_);
+            in.ptr_ += (63 - in.cnt_) >> 3;
+            int cnt = in.cnt_ | 56;
+            bool special = false;
+            for (int k = 0; k < 4; ++k) {
+                const uint64_t e = pair[buf >> (64 - kLutBits)];
+                const uint32_t got = static_cast<uint32_t>(e >> 8) & 0xFF;
+                if (got == 0) {
+                    special = true;
                     break;
                 }
+                out[n] = static_cast<uint16_t>(e >> 16);
+                out[n + 1] = static_cast<uint16_t>(e >> 32);  // junk when got == 1: overwritten by the next symbol
+                n += got;
+                buf <<= (e & 0xFF);
+                cnt -= static_cast<int>(e & 0xFF);
             }
-            if (!len) throw Bad{"bit pattern is not a Huffman code"};
+            in.buf_ = cnt < 64 ? buf & ~((1ull << (64 - cnt)) - 1ull) : buf;  // drop the partial byte (BitReader's invariant)
+            in.cnt_ = cnt;
+            if (special) break;
         }
+    }
+
+    // Code at the head of `window` (kMaxCodeLen bits) -> symbol index and length; false when the bits are no code.
+    bool resolve(uint64_t window, uint32_t& index, uint32_t& len) const {
+        const uint32_t entry = lut[window >> (kMaxCodeLen - kLutBits)];
+        if (entry) {
+            index = entry >> 8, len = entry & 0xFF;
+            return true;
+        }
+        for (int l = kLutBits + 1; l <= maxLen; ++l) {
+            const uint64_t v = window >> (kMaxCodeLen - l);
+            if (count[l] && v >= firstCode[l] && v - firstCode[l] < count[l]) {
+                index = firstIndex[l] + static_cast<uint32_t>(v - firstCode[l]), len = static_cast<uint32_t>(l);
+                return true;
+            }
+        }
+        return false;
+    }
+
+    // One symbol, all checks. Returns true at the pseudo-EOF.
+    bool step(BitReader& in, uint16_t* out, size_t& n, size_t cap) const {
+        uint32_t index = 0, len = 0;
+        if (!resolve(in.peek(kMaxCodeLen), index, len)) throw Bad{"bit pattern is not a Huffman code"};
         in.skip(static_cast<int>(len));
         if (in.overrun()) throw Bad{"Huffman payload without pseudo-EOF"};
-        if (index == eof) return true;
+        if (index == total - 1) return true;
         if (n >= cap) throw Bad{"sequence longer than the block counts allow"};
         out[n++] = symbols[index];
         return false;
     }
+
+    // Worker of decodeParallel: walks [c.from, c.until) and stops at the first code boundary at or after c.until, at a
+    // pseudo-EOF, or at the end of the data. `record` > 0: a blind start — the first `record` code starts are noted, and bits
+    // that are no code are skipped one at a time (the walk is not in step yet). record == 0: the true walk (chunk 0).
+    void runChunk(const BitReader& proto, Chunk& c, uint16_t* dst, size_t dstCap, size_t record) const {
+        BitReader r = proto;
+        r.seek(c.from);
+        const uint64_t totalBits = static_cast<uint64_t>(r.end_ - r.base_) * 8;
+        size_t n = 0;
+        c.bnd.clear();
+        c.eof = c.failed = false;
+        c.lastBad = 0;
+        for (;;) {
+            if (n >= record) fastRun(r, dst, n, dstCap, c.until);
+            const uint64_t pos = r.position();
+            if (pos >= c.until || pos >= totalBits) break;
+            uint32_t index = 0, len = 0;
+            if (!resolve(r.peek(kMaxCodeLen), index, len)) {
+                if (!record) {
+                    c.failed = true;
+                    break;
+                }
+                r.skip(1);
+                c.lastBad = n + 1;  // the bad bits lie before the code that yields symbol n
+                continue;
+            }
+            r.skip(static_cast<int>(len));
+            if (r.overrun()) {
+                c.failed = !record;
+                break;
+            }
+            if (index == total - 1) {
+                c.eof = true;
+                c.eofEnd = r.position();
+                if (n < record) c.bnd.push_back(pos);  // the pseudo-EOF's own start: the true walk may arrive exactly here
+                break;
+            }
+            if (n >= dstCap) {
+                c.failed = !record;
+                break;
+            }
+            if (n < record) c.bnd.push_back(pos);
+            dst[n++] = symbols[index];
+        }
+        c.count = n;
+        c.endPos = r.position();
+    }
 };
 
+constexpr size_t kParallelMinSymbols = 32768;  // below this a sequence is decoded serially
+
 // readHuffmanOrGolomb (CompressedImage.cpp:392-401): `expect` symbols when Golomb coded; a Huffman payload carries its own end.
-size_t readSequence(BitReader& in, HuffTable& table, size_t expect, uint16_t* out, size_t cap) {
+size_t readSequence(BitReader& in, HuffTable& table, size_t expect, uint16_t* out, size_t cap, SpinTeam* pool,
+                    std::vector<HuffTable::Chunk>& chunks) {
     if (in.read(1) == 0) {
         table.read(in);
+        if (pool && pool->size() > 1 && expect >= kParallelMinSymbols) return table.decodeParallel(in, out, cap, expect, *pool, chunks);
         return table.decode(in, out, cap);
     }
     const uint32_t M = static_cast<uint32_t>(in.read(16));
@@ -326,10 +570,13 @@ struct MnParser::Impl {
     BitReader in;
     HuffTable table;
     std::vector<uint16_t> runs;
-    Impl(const uint8_t* p, size_t n) : in(p, n) {}
+    HostPool* pool;
+    SpinTeam* team = nullptr;  // set while readAll runs inside the pool
+    std::vector<HuffTable::Chunk> chunks;
+    Impl(const uint8_t* p, size_t n, HostPool* hp) : in(p, n), pool(hp) {}
 };
 
-MnParser::MnParser(const uint8_t* bytes, size_t n) : impl_(new Impl(bytes, n)), nbytes_(n) {}
+MnParser::MnParser(const uint8_t* bytes, size_t n, HostPool* pool) : impl_(new Impl(bytes, n, pool)), nbytes_(n) {}
 MnParser::~MnParser() { delete impl_; }
 
 int MnParser::readHeader(std::string& err, bool headerOnly) {
@@ -353,7 +600,7 @@ int MnParser::readHeader(std::string& err, bool headerOnly) {
 
 int MnParser::readLengths(uint16_t* counts, std::string& err) {
     try {
-        const size_t n = readSequence(impl_->in, impl_->table, 3 * nblocks, counts, 3 * nblocks);
+        const size_t n = readSequence(impl_->in, impl_->table, 3 * nblocks, counts, 3 * nblocks, impl_->team, impl_->chunks);
         if (n != 3 * nblocks) throw Bad{"`lengths` does not hold one count per block and channel"};
     } catch (const Bad& b) {
         return err = b.why, -1;
@@ -381,6 +628,20 @@ int MnParser::readLengths(uint16_t* counts, std::string& err) {
     return 0;
 }
 
+int MnParser::withTeam(const std::function<int()>& body) {
+    HostPool* pool = impl_->pool;
+    if (!pool || pool->size() < 2) return body();
+    SpinTeam team(pool->size());
+    int rc = 0;
+    pool->withHelpers([&] { team.helper(); }, [&] {
+        impl_->team = &team;
+        rc = body();
+        impl_->team = nullptr;
+        team.finish();
+    });
+    return rc;
+}
+
 int MnParser::readStreams(uint16_t* arena, std::string& err) {
     BitReader& in = impl_->in;
     try {
@@ -392,10 +653,10 @@ int MnParser::readStreams(uint16_t* arena, std::string& err) {
                 const size_t codeLength = in.read32();
                 if (codeLength > want + 4) throw Bad{"run-length coded stream longer than the plain one"};
                 impl_->runs.resize(codeLength + 1);
-                const size_t n = readSequence(in, impl_->table, codeLength, impl_->runs.data(), codeLength);
+                const size_t n = readSequence(in, impl_->table, codeLength, impl_->runs.data(), codeLength, impl_->team, impl_->chunks);
                 got = expandRuns(impl_->runs.data(), n, dst, want);
             } else {
-                got = readSequence(in, impl_->table, want, dst, want);
+                got = readSequence(in, impl_->table, want, dst, want, impl_->team, impl_->chunks);
             }
             if (got != want) throw Bad{"stream size differs from the block counts"};
         }

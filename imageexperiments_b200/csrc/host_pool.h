@@ -54,6 +54,30 @@ public:
         job_.reset();
     }
 
+    // body() on the calling thread while every other pool thread runs helper() (which must return once body is done —
+    // the caller arranges that, e.g. through a flag body sets last). Used by the decoder's spinning reader team.
+    void withHelpers(const std::function<void()>& helper, const std::function<void()>& body) {
+        if (workers_.empty()) {
+            body();
+            return;
+        }
+        const std::function<void(int)> fn = [&](int) { helper(); };
+        auto job = std::make_shared<Job>();
+        job->fn = &fn;
+        job->n = static_cast<int>(workers_.size());
+        job->pending = job->n;
+        {
+            std::lock_guard<std::mutex> g(m_);
+            job_ = job;
+            ++epoch_;
+        }
+        wake_.notify_all();
+        body();
+        std::unique_lock<std::mutex> g(m_);
+        done_.wait(g, [&] { return job->pending == 0; });
+        job_.reset();
+    }
+
 private:
     struct Job {  // late wakers hold their own reference, so a finished job can never be confused with the next one
         const std::function<void(int)>* fn = nullptr;

@@ -140,6 +140,7 @@ struct mnenc_ctx {
     // batch mode (batch_api.cu): extra lanes = contexts with their own stream and buffers that alias this dictionary
     std::vector<mnenc_ctx*> lanes;
     int hostThreads = 1;
+    bool inBatch = false;  // set on every lane for the duration of a batch call: per-image host parallelism off, the lanes are the parallelism
     std::string laneError;
 };
 

@@ -4,6 +4,7 @@
 
 #include <cstddef>
 #include <cstdint>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -131,15 +132,21 @@ int quantTables(int K, int blockSize, double bpp, float* out3K);
 // caller can size its (pinned) buffers between them and start uploading `lengths` while the streams are still being read.
 // Each step returns 0, or -1 with a message in `err`.
 // ------------------------------------------------------------------------------------------------
+class HostPool;
 class MnParser {
 public:
-    MnParser(const uint8_t* bytes, size_t n);
+    // pool: large Huffman payloads are decoded by its threads in parallel (speculative chunk starts, decode_host.cpp);
+    // nullptr or a pool of one thread = the serial reader. Same result either way.
+    MnParser(const uint8_t* bytes, size_t n, HostPool* pool = nullptr);
     ~MnParser();
     MnParser(const MnParser&) = delete;
     MnParser& operator=(const MnParser&) = delete;
     int readHeader(std::string& err, bool headerOnly = false);  // magic, dimensions, K, block size, 3K quantisers -> fields below
     int readLengths(uint16_t* counts, std::string& err);  // counts[3 * nblocks]; fills streamOffset
     int readStreams(uint16_t* arena, std::string& err);   // arena[streamOffset[6K]]: run lengths expanded, DC chains undone
+    // Runs body() (calls of readLengths / readStreams) with the pool's threads standing by as spinning helpers for the
+    // parallel reader; without a pool it just calls body().
+    int withTeam(const std::function<int()>& body);
 
     uint32_t width = 0, height = 0;
     int K = 0, blockSize = 0;

@@ -93,8 +93,9 @@ int mnenc_encode_batch_rgb8(mnenc_t* ctx, size_t n_images, const uint8_t* const*
  * The pixels are those of the reference's decoder, bit for bit. A stream the reference would reject (bad magic, no
  * pseudo-EOF) and any stream whose lengths are inconsistent — where the reference reads out of range — give
  * MNENC_ERR_STREAM; block sizes other than 8 and K > 32 give MNENC_ERR_STREAM as well (unsupported).
- * The entropy decode runs on the calling thread (one serial bit chain per image, see decode_host.cpp), the block loop
- * on the GPU. mnenc_last_timing afterwards: ms[0] = header + `lengths`, ms[1] = symbol streams, ms[2] = uploads + kernels +
+ * The entropy decode runs on the calling thread (one serial bit chain per image, see decode_host.cpp; environment
+ * MNENC_DECODE_THREADS=N > 1 lets the context's host threads help with large Huffman payloads — same result), the block
+ * loop on the GPU. mnenc_last_timing afterwards: ms[0] = header + `lengths`, ms[1] = symbol streams, ms[2] = uploads + kernels +
  * download (host clock), ms[3] = gather + reconstruct kernels (CUDA events), ms[7] = whole call.
  */
 int mnenc_decode_rgb8(mnenc_t* ctx, const uint8_t* mn, size_t mn_bytes, uint8_t** rgb, size_t* width, size_t* height);
@@ -113,10 +114,11 @@ int mnenc_stream_info(const uint8_t* mn, size_t mn_bytes, size_t* width, size_t*
 /*
  * Debug tap (host, no GPU): readCompressedFast's result. lengths[3 * nblocks]; stream_offsets[6K + 1] (stream s =
  * symbols[stream_offsets[s], stream_offsets[s + 1])); symbols may be NULL to obtain the sizes first. Run lengths are
- * expanded and the DC chains undone, as in the reference (:744-781).
+ * expanded and the DC chains undone, as in the reference (:744-781). threads > 1: large Huffman payloads are decoded by that
+ * many host threads (the decoder's parallel reader); the result does not depend on it.
  */
 int mnenc_debug_parse(const uint8_t* mn, size_t mn_bytes, uint16_t* lengths, size_t lengths_capacity, uint64_t* stream_offsets,
-                      uint16_t* symbols, size_t symbols_capacity);
+                      uint16_t* symbols, size_t symbols_capacity, int threads);
 
 /*
  * Debug taps for parity tests (the reference has no equivalent call; they expose the intermediates of

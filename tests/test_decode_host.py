@@ -89,6 +89,7 @@ def test_parse_reference_fixture(oraclelib):
     ms = (time.perf_counter() - t) * 1e3
     want = oraclelib.parse(data)
     same_parse(p, want["lengths"], want["streams"])
+    same_parse(mn.parseStream(data, threads=8), want["lengths"], want["streams"])  # parallel reader
     print(f"fixture: {len(data)} B, {sum(len(s) for s in p['streams'])} symbols parsed (twice) in {ms:.1f} ms")
 
 
@@ -149,3 +150,60 @@ def test_parse_crafted_symbol_distributions(oraclelib, kind, K):
     same_parse(p, counts.reshape(-1), expected_streams(K, counts, pairs))
     op = oraclelib.parse(data)  # and the oracle's own reader agrees
     same_parse(p, op["lengths"], op["streams"])
+
+
+@pytest.mark.parametrize("kind", ["uniform8", "uniform16", "bimodal", "skewed", "constant"])
+def test_parallel_reader_equals_serial(oraclelib, kind):
+    """The speculative multi-threaded Huffman reader (decode_host.cpp, MNENC_DECODE_THREADS) must return exactly what the serial
+    reader returns: payloads that fall into step quickly (skewed), late (bimodal: long codes) or never (fixed-length-like
+    codes of a uniform alphabet: every chunk is walked serially), and sequences too short or Golomb coded (left serial)."""
+    rng = np.random.default_rng(sum(map(ord, kind)))
+    K, bw, bh = 4, 300, 220
+    nb = bw * bh
+    counts = rng.integers(0, K + 1, (nb, 3)).astype(np.uint16) if kind != "constant" else np.full((nb, 3), K, np.uint16)
+    shape = (nb, 3, K, 2)
+    if kind == "uniform8":
+        pairs = rng.integers(0, 256, shape)
+    elif kind == "uniform16":
+        pairs = rng.integers(0, 65536, shape)
+    elif kind == "bimodal":
+        pairs = np.where(rng.random(shape) < 0.9, rng.integers(0, 3, shape), rng.integers(0, 40000, shape))
+    elif kind == "skewed":
+        pairs = np.minimum((rng.pareto(1.2, shape) * 3).astype(np.int64), 65535)
+    else:
+        pairs = np.full(shape, 77)
+    pairs = pairs.astype(np.uint16)
+    pairs[:, :, 0, 1] %= 16384
+    pairs[np.broadcast_to(np.arange(K)[None, None, :, None] >= counts[:, :, None, None], shape)] = 0
+    data = crafted(oraclelib, K, 8 * bw, 8 * bh, counts, pairs)
+    serial = mn.parseStream(data)
+    same_parse(serial, counts.reshape(-1), expected_streams(K, counts, pairs))
+    for threads in (2, 5):
+        par = mn.parseStream(data, threads=threads)
+        same_parse(par, serial["lengths"], serial["streams"])
+
+
+def test_parallel_reader_on_damaged_streams(gd, oracle_ctx_factory):
+    """Damage inside large payloads: the parallel reader reports an error or the serial reader's symbols, never anything else."""
+    from imageexperiments_b200.synth import synthetic_rgb
+    oc = oracle_ctx_factory(mn.createQuantizationTables(32, 8, 3.5))
+    data = np.frombuffer(oc.encode(synthetic_rgb(1400, 1000, 3)), np.uint8)
+    oc.close()
+    rng = np.random.default_rng(4)
+    same_parse(mn.parseStream(data.tobytes(), threads=4), *(lambda p: (p["lengths"], p["streams"]))(mn.parseStream(data.tobytes())))
+    for _ in range(40):
+        a = data.copy()
+        pos = rng.integers(206, a.size, 2)
+        a[pos] ^= rng.integers(1, 256, 2).astype(np.uint8)
+        try:
+            want = mn.parseStream(a.tobytes())
+        except mn.MnencError:
+            want = None
+        try:
+            got = mn.parseStream(a.tobytes(), threads=4)
+        except mn.MnencError as e:
+            assert e.code == -5
+            got = None
+        assert (want is None) == (got is None)
+        if want is not None:
+            same_parse(got, want["lengths"], want["streams"])
