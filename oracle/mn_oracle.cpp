@@ -1,13 +1,14 @@
 // TEST INFRASTRUCTURE — NOT PART OF THE PRODUCT PATH.
 //
-// CPU restatement ("port") of the reference's `.mn` encoder hot path, written from the reference's
-// behaviour, scalar and single-threaded per call. Only tests/, __graft_entry__.smoke() and bench.py's
+// CPU restatement ("port") of the reference's `.mn` encoder hot path and of its decoder, written from the
+// reference's behaviour, scalar and single-threaded per call. Only tests/, __graft_entry__.smoke() and bench.py's
 // cpu_baseline / --impl reference legs may load this library; the product (libmnenc.so) never does.
 //
-// Parity status: PINNED. tests/test_oracle_vs_reference.py checks every function below against the
-// unmodified reference compiled into oracle/_ref/libmnref.so (this container and the GPU box), and
-// tests/golden/ holds vectors generated from that reference build (tests/golden/make_golden.py) plus the
-// header known-answer of the reference's own fixture Data/r0c1de5e1t_3_5.mn.
+// Parity status: PINNED. tests/test_oracle.py (encoder) and tests/test_oracle_decode.py (decoder) check every
+// function below against the unmodified reference compiled into oracle/_ref/libmnref.so (this container and the
+// GPU box), and tests/golden/ holds vectors generated from that reference build (make_golden.py,
+// make_golden_decode.py) plus the known answers of the reference's own fixture Data/r0c1de5e1t_3_5.mn: its header
+// (quantiser tables) and the sha256 of its decoded pixels.
 //
 // All file:line citations are relative to the reference repository root.
 //
