@@ -4,12 +4,12 @@ Only the path BASELINE.json names lives here: csrc/ (CUDA kernels + C ABI, built
 host-side mirror of the reference's encoder interface (compressed.py; stripes.py shards one image over the GPUs of a
 process group).
 """
-from .compressed import (CompressionContextFast, MnBuffer, createCompressionContextFast, createQuantizationTables, encodeImageBatch, encodeImageFast,
+from .compressed import (calculatePSNR, CompressionContextFast, MnBuffer, createCompressionContextFast, createQuantizationTables, encodeImageBatch, encodeImageFast,
                          decodeImageBatch, decodeImageFast, parseStream, streamInfo, lastSymbols, packSymbols, planSequenceHost)
 from .dictionary import Dictionary
 from .stripes import TorchComm, ThreadComm, encodeImageStripes, stripeColumns
 from ._lib import MnencError
 
-__all__ = ["CompressionContextFast", "MnBuffer", "createCompressionContextFast", "createQuantizationTables", "encodeImageFast", "encodeImageBatch", "decodeImageBatch", "decodeImageFast", "parseStream", "streamInfo", "lastSymbols",
+__all__ = ["calculatePSNR", "CompressionContextFast", "MnBuffer", "createCompressionContextFast", "createQuantizationTables", "encodeImageFast", "encodeImageBatch", "decodeImageBatch", "decodeImageFast", "parseStream", "streamInfo", "lastSymbols",
            "packSymbols", "planSequenceHost", "Dictionary", "MnencError", "TorchComm", "ThreadComm", "encodeImageStripes",
            "stripeColumns"]

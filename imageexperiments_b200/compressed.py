@@ -208,6 +208,17 @@ def _pixels(rgb: _vp, w: int, h: int, zero_copy: bool) -> np.ndarray:
     return img if zero_copy else img.copy()
 
 
+def calculatePSNR(original: np.ndarray, decoded: np.ndarray) -> float:
+    """compressed::calculatePSNR (CompressedImage.cpp:343-357): 20 log10(3 * 255) - 10 log10(sum over R,G,B of squared error
+    / (width * height)) — the reference's own (non-standard) peak, kept so that figures compare with its `-n` output. Host."""
+    a = np.asarray(original, np.float64)
+    b = np.asarray(decoded, np.float64)
+    if a.shape != b.shape or a.ndim != 3 or a.shape[2] != 3:
+        raise ValueError("expected two HxWx3 images of the same size")
+    mse = float(((a - b) ** 2).sum()) / (a.shape[0] * a.shape[1])
+    return float(20.0 * np.log10(3.0 * 255.0) - 10.0 * np.log10(mse)) if mse > 0 else float("inf")
+
+
 def _stream(data):
     """bytes / bytearray / MnBuffer / uint8 array -> (pointer, size, keep-alive)."""
     if isinstance(data, MnBuffer):

@@ -26,3 +26,14 @@ def test_against_reference_sweep(reflib):
         assert (mn.createQuantizationTables(32, 8, float(q)) == reflib.quant_tables(32, 8, float(q))).all(), q
     for K in (1, 8, 16):
         assert (mn.createQuantizationTables(K, 8, 3.5) == reflib.quant_tables(K, 8, 3.5)).all(), K
+
+
+def test_calculate_psnr_equals_reference(reflib):
+    """compressed::calculatePSNR (CompressedImage.cpp:343-357), incl. its 3 * 255 peak."""
+    import imageexperiments_b200 as mn
+    from imageexperiments_b200.synth import synthetic_rgb
+    a = synthetic_rgb(96, 64, 1)
+    rng = np.random.default_rng(0)
+    b = np.clip(a.astype(int) + rng.integers(-6, 7, a.shape), 0, 255).astype(np.uint8)
+    assert abs(mn.calculatePSNR(a, b) - reflib.psnr(a, b)) < 1e-9
+    assert mn.calculatePSNR(a, a) == float("inf")
