@@ -31,11 +31,13 @@ int makeLane(mnenc_ctx* parent, int threads, mnenc_ctx** out) {
     return MNENC_OK;
 }
 
-// The context itself + up to MNENC_LANES - 1 (default 6, at most 8 in all) extra lanes, created on first use.
+constexpr int kMaxLanes = 16;
+
+// The context itself + up to MNENC_LANES - 1 (default 6, at most kMaxLanes in all) extra lanes, created on first use.
 int acquireLanes(mnenc_ctx* c, size_t nImages, std::vector<mnenc_ctx*>& lanes) {
     int want = 6;
     if (const char* e = std::getenv("MNENC_LANES")) want = std::atoi(e);
-    want = static_cast<int>(std::min<size_t>(static_cast<size_t>(std::clamp(want, 1, 8)), nImages));
+    want = static_cast<int>(std::min<size_t>(static_cast<size_t>(std::clamp(want, 1, kMaxLanes)), nImages));
     while (static_cast<int>(c->lanes.size()) + 1 < want) {
         mnenc_ctx* lane = nullptr;
         const int rc = makeLane(c, std::max(1, c->hostThreads / 2), &lane);
@@ -65,9 +67,9 @@ extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
     }
     std::atomic<size_t> next{0};
     std::atomic<int> firstError{MNENC_OK};
-    int launches[8] = {};
-    double flops[8] = {};
-    float mpMs[8] = {};
+    int launches[kMaxLanes] = {};
+    double flops[kMaxLanes] = {};
+    float mpMs[kMaxLanes] = {};
     auto work = [&](int li) {
         mnenc_ctx* l = lanes[li];
         cudaSetDevice(l->device);
@@ -118,7 +120,7 @@ extern "C" int mnenc_decode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
     const int want = static_cast<int>(lanes.size());
     std::atomic<size_t> next{0};
     std::atomic<int> firstError{MNENC_OK};
-    int launches[8] = {};
+    int launches[kMaxLanes] = {};
     auto work = [&](int li) {
         mnenc_ctx* l = lanes[li];
         cudaSetDevice(l->device);

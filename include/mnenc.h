@@ -72,7 +72,7 @@ void mnenc_free(uint8_t* p);
  * Batch / throughput mode (BASELINE.json configs[4]): n_images independent images -> n_images independent `.mn` streams,
  * what a caller of the reference gets from encodeImageFast in a loop (Compression.cpp:117-123), each stream byte-identical
  * to the one-at-a-time result. Inside, the images are pipelined over lanes (own stream + buffers, one shared dictionary in
- * HBM; MNENC_LANES, default 6) so that host stages, H2D and D2H of one image overlap the matching pursuit of another.
+ * HBM; MNENC_LANES, default 6, at most 16) so that host stages, H2D and D2H of one image overlap the matching pursuit of another.
  * rgb[i]: host pointers (on_device = 0) or pointers into the context's GPU (on_device = 1); out[i] from mnenc_free().
  * On error every out[i] is NULL. mnenc_last_timing/work afterwards describe the whole batch (ms[1] = summed kernel time,
  * ms[7] = wall time of the batch).
