@@ -11,13 +11,13 @@
 // std::priority_queue sift order. The same containers are therefore driven with the same
 // operation sequence: keys inserted in first-occurrence order then the pseudo-EOF, leaves pushed in map
 // iteration order, pop-two/push-merged. Only (frequency) takes part in heap comparisons, so light nodes with
-// parent links replace the reference's child vectors (O(n log n) instead of O(n * depth) vector churn).
+// parent links replace the reference's child vectors (O(n log n) instead of O(n * depth) vector churn); the heap itself is
+// libstdc++'s algorithm restated on 8-byte nodes (FreqHeap below).
 #include <algorithm>
 #include <bit>
 #include <cmath>
 #include <memory_resource>
 #include <numeric>
-#include <queue>
 #include <unordered_map>
 
 #include "mnenc_internal.h"
@@ -26,40 +26,50 @@
 namespace mnenc {
 
 void BitString::put(uint64_t value, int width) {
-    // MSB-first, byte at a time: the first chunk fills the open byte, the rest start fresh ones
+    // MSB-first. The open byte (if any) takes the leading bits, whole bytes follow, a trailing partial byte is opened.
+    if (width <= 0) return;
     if (width < 64) value &= (1ULL << width) - 1ULL;
-    while (width > 0) {
-        const int used = static_cast<int>(nbits & 7);
-        if (used == 0) bytes.push_back(0);
-        const int take = std::min(8 - used, width);
-        const uint8_t chunk = static_cast<uint8_t>((value >> (width - take)) & ((1u << take) - 1u));
-        bytes.back() |= static_cast<uint8_t>(chunk << (8 - used - take));
-        nbits += take;
-        width -= take;
+    const int used = static_cast<int>(nbits & 7);
+    nbits += static_cast<uint64_t>(width);
+    if (used) {
+        const int room = 8 - used;
+        if (width <= room) {
+            bytes.back() |= static_cast<uint8_t>(value << (room - width));
+            return;
+        }
+        bytes.back() |= static_cast<uint8_t>(value >> (width - room));
+        width -= room;
     }
+    while (width >= 8) {
+        width -= 8;
+        bytes.push_back(static_cast<uint8_t>(value >> width));
+    }
+    if (width) bytes.push_back(static_cast<uint8_t>(value << (8 - width)));
 }
 
 void BitString::append(const BitString& other) {
-    uint64_t left = other.nbits;
-    for (size_t i = 0; left > 0; ++i) {
-        const int take = static_cast<int>(std::min<uint64_t>(8, left));
-        put(other.bytes[i] >> (8 - take), take);
-        left -= take;
+    if (other.nbits == 0) return;
+    const int used = static_cast<int>(nbits & 7);
+    const size_t nOther = static_cast<size_t>((other.nbits + 7) / 8);  // unused bits of its last byte are zero
+    if (used == 0) {
+        bytes.insert(bytes.end(), other.bytes.begin(), other.bytes.begin() + static_cast<std::ptrdiff_t>(nOther));
+        nbits += other.nbits;
+        return;
     }
+    const uint64_t total = nbits + other.nbits;
+    bytes.reserve(static_cast<size_t>((total + 7) / 8));
+    for (size_t i = 0; i < nOther; ++i) {  // every source byte straddles two destination bytes
+        const uint8_t v = other.bytes[i];
+        bytes.back() |= static_cast<uint8_t>(v >> used);
+        bytes.push_back(static_cast<uint8_t>(v << (8 - used)));
+    }
+    nbits = total;
+    bytes.resize(static_cast<size_t>((total + 7) / 8));  // the last split may have opened a byte that holds no bit
 }
 
 namespace {
 
 constexpr uint32_t kEof = 0xFFFFFFFFu;  // Huffman.cpp:38
-
-struct HeapNode {
-    uint64_t freq;
-    uint32_t id;
-    uint32_t depth;
-};
-struct HeapGreater {
-    bool operator()(const HeapNode& a, const HeapNode& b) const { return a.freq > b.freq; }
-};
 
 struct Sym {
     uint32_t symbol;
@@ -68,13 +78,83 @@ struct Sym {
     int origin;  // index in the caller's stats vector, -1 for EOF
 };
 
+// order[] = 0..n-1 sorted by key(i), stable: LSD radix passes of 11 bits (the sequences have up to 65 536 distinct symbols;
+// comparison sorts were a fifth of the table build).
+template <class Key>
+void radixOrder(size_t n, Key key, std::vector<int>& order) {
+    order.resize(n);
+    std::iota(order.begin(), order.end(), 0);
+    uint32_t maxKey = 0;
+    bool sorted = true;
+    for (size_t i = 0; i < n; ++i) {
+        maxKey = std::max(maxKey, key(static_cast<int>(i)));
+        sorted = sorted && (i == 0 || key(static_cast<int>(i - 1)) <= key(static_cast<int>(i)));
+    }
+    if (sorted) return;
+    if (n < 48) {
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return key(a) < key(b); });
+        return;
+    }
+    std::vector<int> tmp(n);
+    uint32_t bucket[2049];
+    for (int shift = 0; shift < 32 && (maxKey >> shift) != 0; shift += 11) {
+        std::fill(std::begin(bucket), std::end(bucket), 0u);
+        for (size_t i = 0; i < n; ++i) ++bucket[((key(order[i]) >> shift) & 2047u) + 1];
+        for (int b = 0; b < 2048; ++b) bucket[b + 1] += bucket[b];
+        for (size_t i = 0; i < n; ++i) tmp[bucket[(key(order[i]) >> shift) & 2047u]++] = order[i];
+        order.swap(tmp);
+    }
+}
+
+// libstdc++'s binary heap (bits/stl_heap.h: __push_heap, __adjust_heap, as driven by std::priority_queue::push / pop) on
+// packed nodes: frequency << 20 | node id, compared on the frequency alone — ties must fall exactly as they do in the
+// reference's std::priority_queue<HuffmanNode, ..., NodeCompare>, so the sift loops are restated
+// move for move; only the node shrinks from the reference's vectors to 8 bytes.
+struct FreqHeap {
+    std::vector<uint64_t> a;
+    static bool greater(uint64_t x, uint64_t y) { return (x >> 20) > (y >> 20); }  // comp(x, y) of a min-heap on frequency
+    void siftUp(size_t hole, size_t top, uint64_t value) {  // __push_heap
+        while (hole > top) {
+            const size_t parent = (hole - 1) / 2;
+            if (!greater(a[parent], value)) break;
+            a[hole] = a[parent];
+            hole = parent;
+        }
+        a[hole] = value;
+    }
+    void push(uint64_t v) {
+        a.push_back(v);
+        siftUp(a.size() - 1, 0, v);
+    }
+    uint64_t top() const { return a.front(); }
+    void pop() {  // pop_heap + pop_back
+        const size_t len = a.size() - 1;
+        if (len > 0) {
+            const uint64_t value = a[len];
+            size_t hole = 0, child = 0;
+            while (child < (len - 1) / 2) {  // __adjust_heap(first, 0, len, value)
+                child = 2 * (child + 1);
+                if (greater(a[child], a[child - 1])) --child;
+                a[hole] = a[child];
+                hole = child;
+            }
+            if ((len & 1) == 0 && child == (len - 2) / 2) {
+                child = 2 * (child + 1);
+                a[hole] = a[child - 1];
+                hole = child - 1;
+            }
+            siftUp(hole, 0, value);
+        }
+        a.pop_back();
+    }
+};
+
 }  // namespace
 
 void planSequence(const std::vector<SymbolStat>& stats, SequencePlan& plan) {
     const size_t n = stats.size();
-    std::vector<int> order(n);
-    std::iota(order.begin(), order.end(), 0);
-    std::sort(order.begin(), order.end(), [&](int a, int b) { return stats[a].firstPos < stats[b].firstPos; });
+    std::vector<int> order;
+    radixOrder(n, [&](int i) { return stats[i].firstPos; }, order);
 
     // --- frequency map in the reference's insertion order (Huffman.cpp:47-71) ---
     // Same libstdc++ hashtable as the reference's std::unordered_map (only the node allocator differs: one arena per
@@ -98,31 +178,43 @@ void planSequence(const std::vector<SymbolStat>& stats, SequencePlan& plan) {
     // --- code lengths (Huffman.cpp:72-103) ---
     std::vector<int32_t> parent(nLeaves, -1);
     parent.reserve(2 * nLeaves);
-    std::priority_queue<HeapNode, std::vector<HeapNode>, HeapGreater> heap;
-    for (const auto& kv : slot) heap.push(HeapNode{leafFreq[kv.second], kv.second, 0});
-    while (heap.size() > 1) {
-        const HeapNode a = heap.top();
+    std::vector<uint8_t> height(nLeaves, 0);  // HuffmanNode::depth: max(children) + 1 (Huffman.cpp:96)
+    height.reserve(2 * nLeaves);
+    FreqHeap heap;
+    heap.a.reserve(nLeaves);
+    for (const auto& kv : slot) heap.push(leafFreq[kv.second] << 20 | kv.second);
+    while (heap.a.size() > 1) {
+        const uint64_t a = heap.top();
         heap.pop();
-        const HeapNode b = heap.top();
+        const uint64_t b = heap.top();
         heap.pop();
+        const uint32_t ia = static_cast<uint32_t>(a & 0xFFFFFu), ib = static_cast<uint32_t>(b & 0xFFFFFu);
         const uint32_t id = static_cast<uint32_t>(parent.size());
         parent.push_back(-1);
-        parent[a.id] = static_cast<int32_t>(id);
-        parent[b.id] = static_cast<int32_t>(id);
-        heap.push(HeapNode{a.freq + b.freq, id, std::max(a.depth, b.depth) + 1});
+        height.push_back(static_cast<uint8_t>(std::max(height[ia], height[ib]) + 1));
+        parent[ia] = static_cast<int32_t>(id);
+        parent[ib] = static_cast<int32_t>(id);
+        heap.push(((a >> 20) + (b >> 20)) << 20 | id);
     }
-    const uint32_t maxLen = std::max<uint32_t>(heap.top().depth, 1);  // :110
+    const uint32_t maxLen = std::max<uint32_t>(height[heap.top() & 0xFFFFFu], 1);  // :110
     // depth of every node from the root down (ids are created bottom-up, so parents have larger ids)
     std::vector<uint32_t> depth(parent.size(), 0);
     for (size_t i = parent.size(); i-- > 0;)
         if (parent[i] >= 0) depth[i] = depth[parent[i]] + 1;
 
+    // sort by (length, symbol) (:28-36): by symbol first (radix, usually already in order), then a stable counting sort by length
+    std::vector<int> bySymbol;
+    radixOrder(n, [&](int k) { return stats[order[k]].symbol; }, bySymbol);  // k = leaf id
+    const uint32_t eofLen = dataCount == 0 ? 1u : depth[n];  // empty input: EOF gets length 1 (:66-71)
+    uint32_t longestLen = eofLen;
+    for (size_t k = 0; k < n; ++k) longestLen = std::max(longestLen, depth[k]);
+    std::vector<uint32_t> lenStart(longestLen + 2, 0);
+    for (size_t k = 0; k < n; ++k) ++lenStart[depth[k] + 1];
+    ++lenStart[eofLen + 1];
+    for (uint32_t l = 0; l <= longestLen; ++l) lenStart[l + 1] += lenStart[l];
     std::vector<Sym> sorted(nLeaves);
-    for (size_t k = 0; k < n; ++k) sorted[k] = Sym{stats[order[k]].symbol, depth[k], 0, order[k]};
-    sorted[n] = Sym{kEof, dataCount == 0 ? 1u : depth[n], 0, -1};  // empty input: EOF gets length 1 (:66-71)
-    std::sort(sorted.begin(), sorted.end(), [](const Sym& a, const Sym& b) {  // :28-36
-        return a.len == b.len ? a.symbol < b.symbol : a.len < b.len;
-    });
+    for (int k : bySymbol) sorted[lenStart[depth[k]]++] = Sym{stats[order[k]].symbol, depth[k], 0, order[k]};
+    sorted[lenStart[eofLen]++] = Sym{kEof, eofLen, 0, -1};  // 0xFFFFFFFF: the largest symbol of its length
 
     // --- canonical codes + header (Huffman.cpp:107-156) ---
     BitString huff;
@@ -201,10 +293,14 @@ void planSequence(const std::vector<SymbolStat>& stats, SequencePlan& plan) {
         const uint32_t limit = (1u << (b + 1)) - M;
         const uint64_t inv = (1ull << 32) / M + 1;
         uint64_t est = 16;
-        for (const SymbolStat& s : stats) {
-            const uint32_t q = s.symbol < 65536u ? static_cast<uint32_t>((s.symbol * inv) >> 32) : s.symbol / M;
-            const uint32_t rem = s.symbol - q * M;
-            est += static_cast<uint64_t>(s.freq) * (b + q + 1 + (rem >= limit ? 1u : 0u));
+        for (size_t i = 0; i < n && est < best;) {  // the estimate only grows: stop once it can no longer win
+            const size_t stop = std::min(n, i + 64);
+            for (; i < stop; ++i) {
+                const SymbolStat& s = stats[i];
+                const uint32_t q = s.symbol < 65536u ? static_cast<uint32_t>((s.symbol * inv) >> 32) : s.symbol / M;
+                const uint32_t rem = s.symbol - q * M;
+                est += static_cast<uint64_t>(s.freq) * (b + q + 1 + (rem >= limit ? 1u : 0u));
+            }
         }
         if (est < best) {
             best = est;

@@ -70,3 +70,17 @@ def test_first_occurrence_order_matters(reflib):
         assert got.size == nbits and (got == bits_of(blob, nbits)).all()
         seen.add(blob[:12])
     assert len(seen) > 1
+
+
+def test_ties_vs_reference(reflib):
+    """Equal and power-of-two frequencies: the code lengths then depend only on how libstdc++'s heap breaks ties
+     — the planner's restated heap (FreqHeap) and radix / counting sorts must fall the same way."""
+    rng = np.random.default_rng(21)
+    for t in range(40):
+        n = int(rng.integers(2, 1500))
+        syms = rng.choice(65536 if t % 2 else 300 + n, n, replace=False).astype(np.uint16)
+        reps = [np.ones(n, int), rng.integers(1, 3, n), 2 ** rng.integers(0, 5, n), np.full(n, 3)][t % 4]
+        d = rng.permutation(np.repeat(syms, reps))
+        blob, nbits = reflib.huffman_or_golomb(d)
+        got = code_with_plan(d)
+        assert got.size == nbits and (got == bits_of(blob, nbits)).all(), (t, n)
