@@ -9,6 +9,7 @@
 // copies up to 2 463 x 64 floats per block-channel): an absolute atom index is resolved to a row by walking the block's
 // earlier picks, exactly as the encoder's kernel does.
 #include <algorithm>
+#include <cstdlib>
 
 #include "backend_kernels.cuh"
 #include "decode_kernels.cuh"
@@ -136,6 +137,87 @@ __global__ void __launch_bounds__(64 * kBlocksPerCta) reconstructKernel(const De
     }
 }
 
+// Variant 2 (MNENC_RECON=2; NOT the default: written after the round's last GPU-box minutes, to be verified and measured
+// first thing next round with `MNENC_RECON=2 python -m pytest tests/test_gpu_decode.py`). Same arithmetic in the same order;
+// what changes is the dependency structure: lane i resolves the row pointer and coefficient of pick i (the walks over
+// the block's picks run in parallel instead of one after the other on every lane), then the rows are loaded four picks at a
+// time before the ordered adds, so four L2 round trips overlap instead of one per pick.
+__global__ void __launch_bounds__(64 * kBlocksPerCta) reconstructKernelV2(const DecodeParams p) {
+    __shared__ int absIdx[2 * kBlocksPerCta][kMaxK];
+    __shared__ const float* rowPtr[2 * kBlocksPerCta][kMaxK];
+    __shared__ float coef[2 * kBlocksPerCta][kMaxK];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int j = threadIdx.x & 63;
+    const int dx = j & 7, dy = j >> 3;
+    const uint32_t ngroups = (p.nblocks + kBlocksPerCta - 1) / kBlocksPerCta;
+    for (uint32_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
+        const uint32_t blk = g * kBlocksPerCta + (threadIdx.x >> 6);
+        if (blk >= p.nblocks) continue;
+        float yuv[3];
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            const int count = p.counts[3 * blk + ch];
+            const uint32_t* pp = p.pairs + (static_cast<size_t>(3) * blk + ch) * p.K;
+            __syncwarp();
+            const uint32_t pr = lane < count ? __ldg(pp + lane) : 0u;
+            int v = 0;
+            if (lane < count) v = lane ? unzigzag(pr & 0xFFFFu) : static_cast<int>(pr & 0xFFFFu);
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const int up = __shfl_up_sync(kFull, v, off);
+                if (lane >= off) v += up;
+            }
+            absIdx[warp][lane] = v;
+            __syncwarp();
+            bool bad = false;
+            if (lane < count) {
+                const float* row = nullptr;
+                if (v >= 0 && v < p.nBase) {
+                    row = p.rows32 + static_cast<size_t>(v) * kN;
+                } else if (v >= p.nBase) {
+                    int off = v - p.nBase;
+                    for (int e = 0; e < count; ++e) {
+                        const int c = absIdx[warp][e];
+                        if (c < 0 || c >= p.nBase) continue;
+                        const int rows = p.detRows[c];
+                        if (off < rows) {
+                            row = p.rows32 + (static_cast<size_t>(kRowsPad) + (static_cast<size_t>(ch) * p.nBase + c) * 64 + off) * kN;
+                            break;
+                        }
+                        off -= rows;
+                    }
+                }
+                bad = row == nullptr;
+                rowPtr[warp][lane] = bad ? p.rows32 : row;  // a damaged pick adds 0 * (some row); the call fails anyway
+                coef[warp][lane] = bad ? 0.0f : __fmul_rn(__ldg(p.quant + ch * p.K + lane), static_cast<float>(unzigzag(pr >> 16)));
+            }
+            if (__any_sync(kFull, bad) && lane == 0) atomicExch(p.error, 1u);
+            __syncwarp();
+            float r = 0.0f;
+            int i = 0;
+            for (; i + 4 <= count; i += 4) {
+                const float x0 = __ldg(rowPtr[warp][i] + j), x1 = __ldg(rowPtr[warp][i + 1] + j);
+                const float x2 = __ldg(rowPtr[warp][i + 2] + j), x3 = __ldg(rowPtr[warp][i + 3] + j);
+                r = __fadd_rn(r, __fmul_rn(coef[warp][i], x0));
+                r = __fadd_rn(r, __fmul_rn(coef[warp][i + 1], x1));
+                r = __fadd_rn(r, __fmul_rn(coef[warp][i + 2], x2));
+                r = __fadd_rn(r, __fmul_rn(coef[warp][i + 3], x3));
+            }
+            for (; i < count; ++i) r = __fadd_rn(r, __fmul_rn(coef[warp][i], __ldg(rowPtr[warp][i] + j)));
+            yuv[ch] = r;
+        }
+        const uint32_t bx = blk / p.nby, by = blk - bx * p.nby;
+        const uint32_t x = bx * 8 + dx, y = by * 8 + dy;
+        if (x < p.width && y < p.height) {
+            const double Y = yuv[0], U = yuv[1], V = yuv[2];
+            uint8_t* px = p.rgb + static_cast<size_t>(y) * p.stride + 3 * static_cast<size_t>(x);
+            px[0] = toByte(__dadd_rn(Y, __dmul_rn(1.13983, V)));
+            px[1] = toByte(__dsub_rn(__dsub_rn(Y, __dmul_rn(0.39466, U)), __dmul_rn(0.58060, V)));
+            px[2] = toByte(__dadd_rn(Y, __dmul_rn(2.03211, U)));
+        }
+    }
+}
+
 }  // namespace
 
 int launchGather(const BackendBuffers& b, const StreamOffsets& so, uint32_t* pairsOut, cudaStream_t st) {
@@ -146,7 +228,14 @@ int launchGather(const BackendBuffers& b, const StreamOffsets& so, uint32_t* pai
 int launchReconstruct(const DecodeParams& p, int numSMs, cudaStream_t st) {
     const uint32_t ngroups = (p.nblocks + kBlocksPerCta - 1) / kBlocksPerCta;
     const uint32_t grid = std::min<uint32_t>(ngroups, static_cast<uint32_t>(numSMs) * 8u);  // 8 x 256 threads fill an SM
-    reconstructKernel<<<grid, 64 * kBlocksPerCta, 0, st>>>(p);
+    static const int variant = [] {
+        const char* e = std::getenv("MNENC_RECON");
+        return e ? std::atoi(e) : 1;
+    }();
+    if (variant == 2)
+        reconstructKernelV2<<<grid, 64 * kBlocksPerCta, 0, st>>>(p);
+    else
+        reconstructKernel<<<grid, 64 * kBlocksPerCta, 0, st>>>(p);
     return 1;
 }
 
