@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--cpu", type=int, default=1)
+    ap.add_argument("--batch", type=int, default=32, help="streams per decodeImageBatch call (0: skip the batch pass)")
     a = ap.parse_args()
     import torch
     W, H = 4928, 3264
@@ -44,22 +45,23 @@ def main():
     ms_host, ph_host = run(lambda d: mn.decodeImageFast(d, ctx, zero_copy=True))
     ms_dev, ph_dev = run(lambda d: mn.decodeImageFast(d, ctx, out=out))
     # throughput mode: 32 streams per call over the lanes (host threads run the entropy decode of different streams in parallel)
-    batch = [ring[i % 4] for i in range(32)]
+    batch = [ring[i % 4] for i in range(a.batch)]
     imgs = None
-    for _ in range(2):
+    for _ in range(2 if a.batch else 0):
         imgs = None  # hand the 32 pinned blocks back before the next batch asks for 32
         imgs = mn.decodeImageBatch(batch, ctx, zero_copy=True)
-    reps = max(1, a.steps // 3)
+    reps = max(1, a.steps // 3) if a.batch else 0
     t = time.perf_counter()
     for _ in range(reps):
         imgs = None
         imgs = mn.decodeImageBatch(batch, ctx, zero_copy=True)
-    ms_batch = (time.perf_counter() - t) / reps * 1e3
+    ms_batch = (time.perf_counter() - t) / max(reps, 1) * 1e3
     imgs = None
     line = {"metric": "decode_throughput", "unit": "MP/s", "workload": f"{W}x{H} q3.5 K32, stream from the GPU encoder ({len(ring[0])} B)",
             "e2e": {"value": round(mp / ms_host * 1e3, 1), "ms": round(ms_host, 3), "h2d_bytes_per_step": len(ring[0]), "d2h_bytes_per_step": 3 * W * H},
             "pixels_on_device": {"value": round(mp / ms_dev * 1e3, 1), "ms": round(ms_dev, 3)},
-            "batch32_e2e": {"value": round(32 * mp / ms_batch * 1e3, 1), "ms_per_batch": round(ms_batch, 2), "lanes": int(os.environ.get("MNENC_LANES", 6))},
+            "batch_e2e": {"streams": a.batch, "value": round(a.batch * mp / ms_batch * 1e3, 1) if a.batch else None, "ms_per_batch": round(ms_batch, 2),
+                          "lanes": int(os.environ.get("MNENC_LANES", 6))},
             "phases_ms": {"lengths_host": round(float(ph_dev[0]), 3), "streams_host": round(float(ph_dev[1]), 3),
                           "upload_kernels_host_clock": round(float(ph_dev[2]), 3), "kernels_gather_reconstruct": round(float(ph_dev[3]), 3)},
             "kernel_roofline": {"bound": "hbm", "algorithmic_bytes": None}, "steps": a.steps, "warmup": a.warmup}
