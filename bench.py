@@ -82,8 +82,10 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_baseline_sample():
-    """The reference's own encodeImageFast (oracle/_ref, unmodified sources) on one core, bounded sample."""
+def cpu_baseline_sample(gpu_ctx=None):
+    """The reference's own encodeImageFast (oracle/_ref, unmodified sources) on one core, bounded sample. With `gpu_ctx` the
+    same crop also goes through the GPU encoder (outside the timed region): BASELINE.json's "PSNR delta" is reported from the
+    reference decoder's pixels of both streams (exactly 0 when the streams are byte-identical)."""
     from imageexperiments_b200.synth import synthetic_rgb
     from oracle.bindings import RefLib, ref_available
     if not ref_available():
@@ -96,9 +98,23 @@ def cpu_baseline_sample():
     data = R.encode(ctx, img)
     dt = time.perf_counter() - t
     R.destroy(ctx)
-    return {"value": round(sw * sh / 1e6 / dt, 4), "unit": "MP/s", "cores": 1, "kind": "reference",
-            "sample": f"top-left {sw}x{sh} crop of the workload image, encodeImageFast of the unmodified reference (g++ -O2), "
-                      f"1 thread, {dt:.1f} s, {len(data)} B", "host_cores": os.cpu_count()}
+    out = {"value": round(sw * sh / 1e6 / dt, 4), "unit": "MP/s", "cores": 1, "kind": "reference",
+           "sample": f"top-left {sw}x{sh} crop of the workload image, encodeImageFast of the unmodified reference (g++ -O2), "
+                     f"1 thread, {dt:.1f} s, {len(data)} B", "host_cores": os.cpu_count()}
+    if gpu_ctx is not None:
+        try:  # the checker must never break the bench line
+            import imageexperiments_b200 as mn
+            ours = bytes(mn.encodeImageFast(img, gpu_ctx))
+            same = ours == data
+            psnr_ref = R.psnr(img, R.decode(data))
+            psnr_ours = psnr_ref if same else R.psnr(img, R.decode(ours))
+            out["parity"] = {"stream_identical": bool(same), "psnr_reference_db": round(psnr_ref, 4), "psnr_gpu_db": round(psnr_ours, 4),
+                             "psnr_delta_db": round(psnr_ours - psnr_ref, 4), "bar_db": 0.01,
+                             "note": "same crop through the GPU encoder; both streams decoded by the unmodified reference decoder, "
+                                     "calculatePSNR of the reference (3*255 peak, CompressedImage.cpp:343-357)"}
+        except Exception as e:  # noqa: BLE001
+            out["parity"] = {"error": repr(e)}
+    return out
 
 
 _REF = {}
@@ -317,7 +333,7 @@ def run_ours(args):
             "single_image_latency_ms": round(lat_s * 1e3, 3),
         }
         if world == 1:
-            line["cpu_baseline"] = cpu_baseline_sample()
+            line["cpu_baseline"] = cpu_baseline_sample(ctx)
             line["decode"] = decode_sample(ctx, pinned)
         print(json.dumps(line))
     if world > 1:
