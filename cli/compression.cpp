@@ -1,21 +1,27 @@
 // Linux `Compression` front end on the C ABI: the -c / -d / -n modes of the reference's
-// Compression/Compression.cpp:96-182, same arguments, same lines on stdout, the GPU library behind them.
+// Compression/Compression.cpp:96-182 and the matching-pursuit half of its -g sweep (:303-357), same arguments, same lines
+// on stdout, the GPU library behind them.
 //
 //   Compression -c <quality 1.0-8.0 | max> <input.ppm> <output.mn>        Compression.cpp:102-133
 //   Compression -d <input.mn> <output.ppm>                                 Compression.cpp:134-146
 //   Compression -n <quality 1.0-8.0 | max> <input.ppm> [output.ppm]        Compression.cpp:147-182
+//   Compression -g <input folder> <output statistics.csv>                  Compression.cpp:303-357 (MP rows only)
 //
 // Differences, all forced by the platform: images are binary PPM (P6) — the reference loads and saves through GDI+
 // (ImageHelper/src/imgloader.cpp), which does not exist here; its own PNM code path (ImageHelper/src/pnmfile.cpp) is the
 // format kept. The dictionary is imported data (MNENC_DICT, default imageexperiments_b200/data/dict_bs8.mndict next to the
-// library), not rebuilt per run. -j / -s / -g (JPEG comparison, statistics, curves) are out of scope.
+// library), not rebuilt per run. -g walks the folder for .ppm files (the reference: .jpg / .tif) in sorted
+// order and writes the "MP" rows of the reference's CSV; its "JPEG" rows, -j and -s (JPEG comparison through GDI+, training
+// statistics of the double-precision twin) are out of scope.
 // There is no CPU path: without a B200 every mode fails with the library's error text.
 #include <chrono>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
+#include <filesystem>
 #include <format>
 #include <fstream>
 #include <iostream>
@@ -139,6 +145,18 @@ double psnr(const Image& a, const uint8_t* b) {
     return 20.0 * std::log10(3.0 * 255.0) - 10.0 * std::log10(mse);
 }
 
+// Every regular file below `path`, sub-folders included (readFiles, Compression.cpp:31-52); sorted so that the report does
+// not depend on the file system's directory order.
+std::vector<std::string> readFiles(const std::string& path) {
+    std::vector<std::string> results;
+    std::error_code ec;
+    for (std::filesystem::recursive_directory_iterator it(path, ec), end; !ec && it != end; it.increment(ec))
+        if (it->is_regular_file(ec)) results.push_back(it->path().string());
+    if (ec) die("cannot read folder " + path + ": " + ec.message());
+    std::sort(results.begin(), results.end());
+    return results;
+}
+
 void usage() {  // Compression.cpp:75-89, the modes kept
     std::cout << "To compress to file" << std::endl;
     std::cout << "usage: Compression -c <quality 1.0-8.0> <input PPM file path> <output compressed file path>" << std::endl;
@@ -146,6 +164,8 @@ void usage() {  // Compression.cpp:75-89, the modes kept
     std::cout << "usage: Compression -d <input compressed file path> <output PPM file path>" << std::endl;
     std::cout << "To display psnr and bpp of compression cycle" << std::endl;
     std::cout << "usage: Compression -n  <quality 1.0-8.0> <input PPM file path> [optional output PPM path]" << std::endl;
+    std::cout << "Enumerate all .PPM files in folder and calclulate compression curves for them" << std::endl;
+    std::cout << "Compression -g <input folder path> <outputs statistics file path>" << std::endl;
 }
 
 std::string dirOf(const char* argv0) {
@@ -219,6 +239,45 @@ int main(int argc, char* argv[]) {
         mnenc_free(px);
         mnenc_free(bytes);
         mnenc_destroy(ctx);
+    } else if (mode == "-g") {
+        if (argc != 4) {
+            usage();
+            return -1;
+        }
+        const std::vector<std::string> files = readFiles(argv[2]);
+        std::ofstream fileOut(argv[3], std::ios::out | std::ios::trunc);
+        if (!fileOut) die(std::string("cannot write ") + argv[3]);
+        fileOut << "File, Mode, Quality, Size, BPP, PSNR" << std::endl;
+        mnenc_t* ctx = nullptr;  // created at the first image: an empty folder needs no GPU
+        for (size_t count = 0; count < files.size(); ++count) {
+            const std::string& file = files[count];
+            std::string lowerCaseName(file.size(), 0);
+            std::transform(file.cbegin(), file.cend(), lowerCaseName.begin(), [](unsigned char c) { return static_cast<char>(std::tolower(c)); });
+            if (!lowerCaseName.ends_with(".ppm")) continue;
+            const Image in = loadPpm(file);
+            if (!ctx) ctx = createContext(exeDir);
+            // one context per quality in the reference (Compression.cpp:332); only the quantisers differ between them
+            for (double bppAllocation = 8.0; bppAllocation >= 1.0; bppAllocation -= 1.0) {
+                std::vector<float> quant(3 * kK);
+                if (mnenc_quant_tables(kK, kBlockSize, bppAllocation, quant.data()) != MNENC_OK) dieLib("mnenc_quant_tables");
+                if (mnenc_set_quant(ctx, quant.data()) != MNENC_OK) dieLib("mnenc_set_quant");
+                std::cout << std::format("MP processing: {} {}%", file, (100L * static_cast<long>(count)) / static_cast<long>(files.size())) << std::endl;
+                uint8_t* bytes = nullptr;
+                size_t n = 0;
+                if (mnenc_encode_rgb8(ctx, in.px.data(), in.w, in.h, 3 * in.w, &bytes, &n) != MNENC_OK) dieLib("mnenc_encode_rgb8");
+                uint8_t* px = nullptr;
+                size_t w = 0, h = 0;
+                if (mnenc_decode_rgb8(ctx, bytes, n, &px, &w, &h) != MNENC_OK) dieLib("mnenc_decode_rgb8");
+                const double p = psnr(in, px);
+                mnenc_free(px);
+                mnenc_free(bytes);
+                const double bpp = static_cast<double>(8ULL * n) / static_cast<double>(in.w * in.h);
+                std::cout << std::format("MP Quality {} PSNR {} bpp {} total KB {}", bppAllocation, p, bpp, n) << std::endl;  // bytes, as :353
+                fileOut << std::format("{}, {}, {}, {}, {}, {}", file, "MP", bppAllocation, n, bpp, p) << std::endl;
+            }
+            fileOut.flush();
+        }
+        if (ctx) mnenc_destroy(ctx);
     } else {
         usage();
         return -1;

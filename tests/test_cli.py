@@ -37,7 +37,7 @@ def exe():
 
 
 def test_usage_and_argument_errors(exe, tmp_path):
-    for args in ([], ["-x"], ["-c", "3.5"], ["-d", "a"], ["-n", "3.5"]):
+    for args in ([], ["-x"], ["-c", "3.5"], ["-d", "a"], ["-n", "3.5"], ["-g", "a"], ["-g", "a", "b", "c"]):
         r = run(*args)
         assert r.returncode == 255 and "usage: Compression -c" in r.stdout  # return -1, Compression.cpp:92-95
     r = run("-c", "3.5", str(tmp_path / "missing.ppm"), str(tmp_path / "o.mn"))
@@ -58,6 +58,29 @@ def test_fails_loudly_without_a_gpu(exe, tmp_path):
     write_ppm(tmp_path / "i.ppm", synthetic_rgb(16, 16, 1), comment=True)
     r = run("-c", "3.5", str(tmp_path / "i.ppm"), str(tmp_path / "o.mn"))
     assert r.returncode == 1 and "mnenc_create" in r.stderr and not (tmp_path / "o.mn").exists()
+
+
+def test_sweep_without_images_needs_no_gpu(exe, tmp_path):
+    """-g (Compression.cpp:303-357): recursive walk, only image files are processed, the CSV header is always written."""
+    (tmp_path / "in" / "sub").mkdir(parents=True)
+    (tmp_path / "in" / "notes.txt").write_text("not an image")
+    (tmp_path / "in" / "sub" / "x.mn").write_bytes(b"MN24")
+    r = run("-g", str(tmp_path / "in"), str(tmp_path / "stats.csv"))
+    assert r.returncode == 0, r.stderr
+    assert (tmp_path / "stats.csv").read_text() == "File, Mode, Quality, Size, BPP, PSNR\n"
+    r = run("-g", str(tmp_path / "missing"), str(tmp_path / "stats.csv"))
+    assert r.returncode == 1 and "cannot read folder" in r.stderr
+
+
+def test_sweep_fails_loudly_without_a_gpu(exe, tmp_path):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from imageexperiments_b200.synth import synthetic_rgb
+    (tmp_path / "in").mkdir()
+    write_ppm(tmp_path / "in" / "I.PPM", synthetic_rgb(16, 16, 1))  # extension compared in lower case (:313-315)
+    r = run("-g", str(tmp_path / "in"), str(tmp_path / "stats.csv"))
+    assert r.returncode == 1 and "mnenc_create" in r.stderr
 
 
 @pytest.mark.gpu
