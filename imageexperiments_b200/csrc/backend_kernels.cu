@@ -2,8 +2,10 @@
 // All kernels are HBM/L2-bound integer work: coalesced accesses, warp-shuffle prefix sums, grids sized by
 // the data (a few MB per image), no tensor-core shaping.
 #include "backend_kernels.cuh"
+#include "word_acc.h"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace mnenc {
 
@@ -596,6 +598,74 @@ struct PackOut {
     __device__ void total(unsigned long long, uint32_t) const {}
 };
 
+// Variant 2 of the pack scan's apply phase (MNENC_PACK=2; NOT the default: written after the round's last GPU-box minutes,
+// to be verified with `MNENC_PACK=2 python -m pytest tests/test_gpu_parity.py tests/test_gpu_stripes.py` and measured against
+// the default first thing next round). Same positions, same bits; what changes is the traffic to L2:
+//  * a thread's eight consecutive codes are merged in a register (WordAcc, csrc/word_acc.h — the host build of that header
+//    is checked against a bit-by-bit writer by tests/test_word_acc.py) and leave as one atomicOr per output word touched
+//    instead of one or two per code (mean code ≈ 4.6 bits: ≈2.2 atomics per thread instead of ≈9);
+//  * the sequence of an item is found once per thread (binary search) and then advanced, its descriptor and code plan are
+//    reloaded only when it changes, and the table entry fetched for the length is kept for the emission.
+struct OrSink {
+    uint32_t* out;
+    __device__ __forceinline__ void operator()(unsigned long long w, uint32_t v) const { atomicOr(&out[w], v); }
+};
+__global__ void __launch_bounds__(kScanThreads) packApplyKernelV2(PackOut p, uint32_t n, const unsigned long long* blockSums) {
+    const uint32_t base = blockIdx.x * kScanTile;
+    if (base >= n) return;
+    const uint32_t first = base + threadIdx.x * kScanItems;
+    const uint32_t* start = p.v.table->start;
+    unsigned long long code[kScanItems];  // Huffman: length << 32 | bits (the table entry); Golomb: length << 32 | symbol
+    int seqOf[kScanItems];
+    unsigned long long sum = 0;
+    int q = first < n ? findSeq(start, p.nSeq, first) : 0, qLoaded = -1;
+    SeqDesc d{};
+    uint32_t golombM = 0, seqStart = 0, seqEnd = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        const uint32_t g = first + k;
+        code[k] = 0;
+        seqOf[k] = 0;
+        if (g >= n) continue;
+        if (qLoaded >= 0 && g >= seqEnd) {  // largest q with start[q] <= g, as findSeq: empty sequences are stepped over
+            while (q + 1 < p.nSeq && start[q + 1] <= g) ++q;
+        }
+        if (q != qLoaded) {
+            d = p.v.table->desc[q];
+            golombM = p.codes->seq[q].golombM;
+            seqStart = start[q];
+            seqEnd = q + 1 < p.nSeq ? start[q + 1] : 0xFFFFFFFFu;  // > g: q is the LARGEST index with start[q] <= g
+            qLoaded = q;
+        }
+        const uint32_t sym = loadSym(p.v, d, g - seqStart);
+        seqOf[k] = q;
+        code[k] = golombM ? (static_cast<unsigned long long>(golombLength(sym, golombM)) << 32) | sym
+                          : p.entryCodes[p.symToEntry[static_cast<size_t>(q) * kHistBins + sym]];
+        sum += code[k] >> 32;
+    }
+    unsigned long long total;
+    unsigned long long prefix = blockExclusive(sum, &total) + blockSums[blockIdx.x];
+    WordAcc<OrSink> acc(OrSink{p.out});
+    qLoaded = -1;
+    unsigned long long bitBase = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        if (first + k < n) {
+            if (seqOf[k] != qLoaded) {
+                const SeqCode c = p.codes->seq[seqOf[k]];
+                bitBase = c.bitBase;
+                golombM = c.golombM;
+                qLoaded = seqOf[k];
+            }
+            const unsigned long long pos = bitBase + prefix;
+            if (golombM == 0) acc.put(pos, static_cast<uint32_t>(code[k]), static_cast<int>(code[k] >> 32));
+            else acc.putGolomb(pos, static_cast<uint32_t>(code[k]), golombM, 32 - __clz(golombM));
+        }
+        prefix += code[k] >> 32;
+    }
+    acc.flush();
+}
+
 
 // Stripe path: payload bits this rank contributes to every sequence (sum of the code lengths of its slice).
 __global__ void __launch_bounds__(256) seqBitsKernel(CodeLenIn in, uint32_t M, unsigned long long* seqBits) {
@@ -730,6 +800,18 @@ int launchFillU32(uint32_t* p, size_t n, uint32_t value, cudaStream_t st) {
 
 int launchPack(const BackendBuffers& b, uint32_t M, int nSeq, cudaStream_t st) {
     SeqView v{b.seqTable, b.counts, b.arena, b.rleArena};
+    static const int variant = [] {
+        const char* e = std::getenv("MNENC_PACK");
+        return e ? std::atoi(e) : 1;
+    }();
+    if (variant == 2 && M) {
+        const uint32_t nTiles = (M + kScanTile - 1) / kScanTile;
+        const CodeLenIn in{v, nSeq, b.codeTable, b.firstPos, b.entryCodes};
+        scanReduceKernel<unsigned long long, CodeLenIn><<<nTiles, kScanThreads, 0, st>>>(in, M, nullptr, b.blockSums64);
+        scanBlockSumsKernel<unsigned long long><<<1, 1024, 0, st>>>(b.blockSums64, nTiles);
+        packApplyKernelV2<<<nTiles, kScanThreads, 0, st>>>(PackOut{v, nSeq, b.codeTable, b.firstPos, b.entryCodes, b.outWords}, M, b.blockSums64);
+        return 3;
+    }
     return deviceScan<unsigned long long>(CodeLenIn{v, nSeq, b.codeTable, b.firstPos, b.entryCodes},
                                           PackOut{v, nSeq, b.codeTable, b.firstPos, b.entryCodes, b.outWords}, M, nullptr, b.blockSums64, st);
 }

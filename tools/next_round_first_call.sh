@@ -1,7 +1,7 @@
 #!/bin/bash
 # First GPU-box call of the next round: everything that was written after round 1's GPU minutes ran out,
 # verified and A/B-measured in one go. Usage:
-#   gpurun --timeout 420 -- 'bash tools/next_round_first_call.sh'
+#   gpurun --timeout 900 -- 'bash tools/next_round_first_call.sh'
 # Writes gpurun_out/r02_first_call.log (+ the ncu report of the reconstruct kernel). Each step has its own timeout.
 mkdir -p gpurun_out
 L=gpurun_out/r02_first_call.log
@@ -13,6 +13,9 @@ step "decode tests, default"            timeout 120 python -m pytest tests/test_
 step "decode tests, MNENC_RECON=2"      env MNENC_RECON=2 timeout 120 python -m pytest tests/test_gpu_decode.py -x -q
 step "decode tests, parallel reader"    env MNENC_DECODE_THREADS=8 timeout 120 python -m pytest tests/test_gpu_decode.py -x -q
 
+step "encode tests, MNENC_PACK=2"       env MNENC_PACK=2 timeout 300 python -m pytest tests/test_gpu_parity.py tests/test_gpu_stripes.py -x -q
+step "CLI sweep (-g), first GPU run"    timeout 120 python -m pytest tests/test_zz_cli_sweep.py -x -q -m gpu
+
 # 2. A/B of the decoder (same box, back to back): serial vs parallel reader, kernel variants, lanes of the batch path
 step "decode bench, default"            timeout 90 python tools/decode_bench.py --cpu 0
 step "decode bench, MNENC_RECON=2"      env MNENC_RECON=2 timeout 90 python tools/decode_bench.py --cpu 0
@@ -22,6 +25,8 @@ step "decode bench, 16 lanes"           env MNENC_LANES=16 timeout 90 python too
 
 # 3. encoder after the host table builder rework (host stage = ms[4] of mnenc_last_timing; bench line for the record)
 step "bench.py"                         timeout 240 python bench.py --steps 3 --warmup 3
+
+step "bench.py, MNENC_PACK=2"           env MNENC_PACK=2 timeout 240 python bench.py --steps 3 --warmup 3
 
 # 4. ncu of the decode kernels: one lane, no batch pass worth mentioning under the profiler
 step "ncu reconstruct"                  env MNENC_LANES=1 timeout 150 ncu --set full --clock-control none --import-source on \
