@@ -618,25 +618,24 @@ __global__ void __launch_bounds__(kScanThreads) packApplyKernelV2(PackOut p, uin
     unsigned long long code[kScanItems];  // Huffman: length << 32 | bits (the table entry); Golomb: length << 32 | symbol
     int seqOf[kScanItems];
     unsigned long long sum = 0;
-    int q = first < n ? findSeq(start, p.nSeq, first) : 0, qLoaded = -1;
+    SeqWalk walk(start, p.nSeq, first < n ? first : 0u);
+    int qLoaded = -1;
     SeqDesc d{};
-    uint32_t golombM = 0, seqStart = 0, seqEnd = 0;
+    uint32_t golombM = 0;
 #pragma unroll
     for (int k = 0; k < kScanItems; ++k) {
         const uint32_t g = first + k;
         code[k] = 0;
         seqOf[k] = 0;
         if (g >= n) continue;
-        if (qLoaded >= 0 && g >= seqEnd) {  // largest q with start[q] <= g, as findSeq: empty sequences are stepped over
-            while (q + 1 < p.nSeq && start[q + 1] <= g) ++q;
-        }
+        walk.advance(g);
+        const int q = walk.q;
         if (q != qLoaded) {
             d = p.v.table->desc[q];
             golombM = p.codes->seq[q].golombM;
-            seqStart = start[q];
-            seqEnd = q + 1 < p.nSeq ? start[q + 1] : 0xFFFFFFFFu;  // > g: q is the LARGEST index with start[q] <= g
             qLoaded = q;
         }
+        const uint32_t seqStart = walk.seqStart;
         const uint32_t sym = loadSym(p.v, d, g - seqStart);
         seqOf[k] = q;
         code[k] = golombM ? (static_cast<unsigned long long>(golombLength(sym, golombM)) << 32) | sym

@@ -74,4 +74,36 @@ struct WordAcc {
     }
 };
 
+// Which sequence of the concatenation an element belongs to: start[0 .. nSeq] ascending, empty sequences repeat their
+// successor's start, the owner of element g is the LARGEST q < nSeq with start[q] <= g. A thread that walks consecutive
+// elements searches once and then only steps forward.
+struct SeqWalk {
+    const uint32_t* start;
+    int nSeq;
+    int q;
+    uint32_t seqStart, seqEnd;  // elements [seqStart, seqEnd) belong to q
+
+    MNENC_HD SeqWalk(const uint32_t* s, int n, uint32_t g) : start(s), nSeq(n), q(0), seqStart(0), seqEnd(0) {
+        int lo = 0, hi = n;
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (start[mid] <= g) lo = mid;
+            else hi = mid;
+        }
+        q = lo;
+        load();
+    }
+    MNENC_HD void load() {
+        seqStart = start[q];
+        seqEnd = q + 1 < nSeq ? start[q + 1] : 0xFFFFFFFFu;
+    }
+    // move to the owner of g (g not below the previous element); true when the sequence changed
+    MNENC_HD bool advance(uint32_t g) {
+        if (g < seqEnd) return false;
+        while (q + 1 < nSeq && start[q + 1] <= g) ++q;
+        load();
+        return true;
+    }
+};
+
 }  // namespace mnenc

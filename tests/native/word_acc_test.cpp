@@ -102,6 +102,31 @@ int main() {
             return 1;
         }
     }
+    // SeqWalk: one search, then forward steps, against "largest q with start[q] <= g" computed the slow way
+    for (int round = 0; round < 2000; ++round) {
+        const int nSeq = 1 + static_cast<int>(rng() % 193);
+        std::vector<uint32_t> start(nSeq + 1, 0);
+        for (int q = 0; q < nSeq; ++q) {
+            const uint32_t len = (rng() % 3 == 0) ? 0u : (rng() % 4 == 0 ? rng() % 40 : rng() % 4);  // many empty and tiny sequences
+            start[q + 1] = start[q] + len;
+        }
+        const uint32_t total = start[nSeq];
+        if (total == 0) continue;
+        for (int t = 0; t < 64; ++t) {
+            const uint32_t first = rng() % total;
+            mnenc::SeqWalk walk(start.data(), nSeq, first);
+            for (uint32_t g = first; g < std::min(total, first + 8); ++g) {
+                walk.advance(g);
+                int want = 0;
+                for (int q = 0; q < nSeq; ++q)
+                    if (start[q] <= g) want = q;
+                if (walk.q != want || walk.seqStart != start[want] || g < walk.seqStart || g >= walk.seqEnd) {
+                    std::printf("SeqWalk round %d: element %u -> sequence %d, want %d\n", round, g, walk.q, want);
+                    return 1;
+                }
+            }
+        }
+    }
     std::puts("word_acc OK");
     return 0;
 }
