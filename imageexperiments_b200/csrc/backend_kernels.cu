@@ -610,15 +610,12 @@ struct OrSink {
     uint32_t* out;
     __device__ __forceinline__ void operator()(unsigned long long w, uint32_t v) const { atomicOr(&out[w], v); }
 };
-__global__ void __launch_bounds__(kScanThreads) packApplyKernelV2(PackOut p, uint32_t n, const unsigned long long* blockSums) {
-    const uint32_t base = blockIdx.x * kScanTile;
-    if (base >= n) return;
-    const uint32_t first = base + threadIdx.x * kScanItems;
-    const uint32_t* start = p.v.table->start;
-    unsigned long long code[kScanItems];  // Huffman: length << 32 | bits (the table entry); Golomb: length << 32 | symbol
-    int seqOf[kScanItems];
+// Codes of the eight consecutive elements a thread owns (Huffman: length << 32 | bits, i.e. the table entry; Golomb:
+// length << 32 | symbol) and their sequences; returns the sum of the lengths.
+__device__ __forceinline__ unsigned long long packThreadCodes(const PackOut& p, uint32_t first, uint32_t n, unsigned long long (&code)[kScanItems],
+                                                              int (&seqOf)[kScanItems]) {
     unsigned long long sum = 0;
-    SeqWalk walk(start, p.nSeq, first < n ? first : 0u);
+    SeqWalk walk(p.v.table->start, p.nSeq, first < n ? first : 0u);
     int qLoaded = -1;
     SeqDesc d{};
     uint32_t golombM = 0;
@@ -635,17 +632,41 @@ __global__ void __launch_bounds__(kScanThreads) packApplyKernelV2(PackOut p, uin
             golombM = p.codes->seq[q].golombM;
             qLoaded = q;
         }
-        const uint32_t seqStart = walk.seqStart;
-        const uint32_t sym = loadSym(p.v, d, g - seqStart);
+        const uint32_t sym = loadSym(p.v, d, g - walk.seqStart);
         seqOf[k] = q;
         code[k] = golombM ? (static_cast<unsigned long long>(golombLength(sym, golombM)) << 32) | sym
                           : p.entryCodes[p.symToEntry[static_cast<size_t>(q) * kHistBins + sym]];
         sum += code[k] >> 32;
     }
+    return sum;
+}
+// MNENC_PACK=3 adds the reduce phase in the same blocked arrangement (one sequence search per thread instead of one per
+// element; a sum does not care about the arrangement).
+__global__ void __launch_bounds__(kScanThreads) packReduceKernelV2(PackOut p, uint32_t n, unsigned long long* blockSums) {
+    const uint32_t base = blockIdx.x * kScanTile;
+    if (base >= n) {
+        if (threadIdx.x == 0) blockSums[blockIdx.x] = 0ull;
+        return;
+    }
+    unsigned long long code[kScanItems];
+    int seqOf[kScanItems];
+    const unsigned long long sum = packThreadCodes(p, base + threadIdx.x * kScanItems, n, code, seqOf);
+    unsigned long long total;
+    blockExclusive(sum, &total);
+    if (threadIdx.x == 0) blockSums[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(kScanThreads) packApplyKernelV2(PackOut p, uint32_t n, const unsigned long long* blockSums) {
+    const uint32_t base = blockIdx.x * kScanTile;
+    if (base >= n) return;
+    const uint32_t first = base + threadIdx.x * kScanItems;
+    unsigned long long code[kScanItems];
+    int seqOf[kScanItems];
+    const unsigned long long sum = packThreadCodes(p, first, n, code, seqOf);
+    int qLoaded = -1;
+    uint32_t golombM = 0;
     unsigned long long total;
     unsigned long long prefix = blockExclusive(sum, &total) + blockSums[blockIdx.x];
     WordAcc<OrSink> acc(OrSink{p.out});
-    qLoaded = -1;
     unsigned long long bitBase = 0;
 #pragma unroll
     for (int k = 0; k < kScanItems; ++k) {
@@ -803,12 +824,16 @@ int launchPack(const BackendBuffers& b, uint32_t M, int nSeq, cudaStream_t st) {
         const char* e = std::getenv("MNENC_PACK");
         return e ? std::atoi(e) : 1;
     }();
-    if (variant == 2 && M) {
+    if ((variant == 2 || variant == 3) && M) {
         const uint32_t nTiles = (M + kScanTile - 1) / kScanTile;
-        const CodeLenIn in{v, nSeq, b.codeTable, b.firstPos, b.entryCodes};
-        scanReduceKernel<unsigned long long, CodeLenIn><<<nTiles, kScanThreads, 0, st>>>(in, M, nullptr, b.blockSums64);
+        const PackOut out{v, nSeq, b.codeTable, b.firstPos, b.entryCodes, b.outWords};
+        if (variant == 3)
+            packReduceKernelV2<<<nTiles, kScanThreads, 0, st>>>(out, M, b.blockSums64);
+        else
+            scanReduceKernel<unsigned long long, CodeLenIn><<<nTiles, kScanThreads, 0, st>>>(CodeLenIn{v, nSeq, b.codeTable, b.firstPos, b.entryCodes}, M,
+                                                                                              nullptr, b.blockSums64);
         scanBlockSumsKernel<unsigned long long><<<1, 1024, 0, st>>>(b.blockSums64, nTiles);
-        packApplyKernelV2<<<nTiles, kScanThreads, 0, st>>>(PackOut{v, nSeq, b.codeTable, b.firstPos, b.entryCodes, b.outWords}, M, b.blockSums64);
+        packApplyKernelV2<<<nTiles, kScanThreads, 0, st>>>(out, M, b.blockSums64);
         return 3;
     }
     return deviceScan<unsigned long long>(CodeLenIn{v, nSeq, b.codeTable, b.firstPos, b.entryCodes},

@@ -14,6 +14,7 @@ step "decode tests, MNENC_RECON=2"      env MNENC_RECON=2 timeout 120 python -m 
 step "decode tests, parallel reader"    env MNENC_DECODE_THREADS=8 timeout 120 python -m pytest tests/test_gpu_decode.py -x -q
 
 step "encode tests, MNENC_PACK=2"       env MNENC_PACK=2 timeout 300 python -m pytest tests/test_gpu_parity.py tests/test_gpu_stripes.py -x -q
+step "encode tests, MNENC_PACK=3"       env MNENC_PACK=3 timeout 300 python -m pytest tests/test_gpu_parity.py tests/test_gpu_stripes.py -x -q
 step "CLI sweep (-g), first GPU run"    timeout 120 python -m pytest tests/test_zz_cli_sweep.py -x -q -m gpu
 
 # 2. A/B of the decoder (same box, back to back): serial vs parallel reader, kernel variants, lanes of the batch path
@@ -27,6 +28,7 @@ step "decode bench, 16 lanes"           env MNENC_LANES=16 timeout 90 python too
 step "bench.py"                         timeout 240 python bench.py --steps 3 --warmup 3
 
 step "bench.py, MNENC_PACK=2"           env MNENC_PACK=2 timeout 240 python bench.py --steps 3 --warmup 3
+step "bench.py, MNENC_PACK=3"           env MNENC_PACK=3 timeout 240 python bench.py --steps 3 --warmup 3
 
 # 4. ncu of the decode kernels: one lane, no batch pass worth mentioning under the profiler
 step "ncu reconstruct"                  env MNENC_LANES=1 timeout 150 ncu --set full --clock-control none --import-source on \
