@@ -52,7 +52,7 @@ int acquireLanes(mnenc_ctx* c, size_t nImages, std::vector<mnenc_ctx*>& lanes) {
 }  // namespace
 
 extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_t* const* rgb, int on_device, const size_t* width,
-                                       const size_t* height, const size_t* row_stride_bytes, uint8_t** out, size_t* out_bytes) {
+                                       const size_t* height, const size_t* row_stride_bytes, uint8_t** out, size_t* out_bytes) try {
     if (!c || (n_images && (!rgb || !width || !height || !row_stride_bytes || !out || !out_bytes))) return fail(MNENC_ERR_ARG, "null argument");
     if (!c->quantSet) return fail(MNENC_ERR_STATE, "mnenc_set_quant has not been called");
     for (size_t i = 0; i < n_images; ++i) out[i] = nullptr, out_bytes[i] = 0;
@@ -105,12 +105,14 @@ extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
     for (int li = 0; li < want; ++li) c->launches += launches[li], c->mpFlops += flops[li], c->ms[1] += mpMs[li];
     c->ms[7] = static_cast<float>(nowMs() - t0);
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 // Decoder twin: n independent `.mn` streams -> n images (decodeImageFast in a loop). The entropy decode of one stream is one
 // serial chain on one host thread (decode_host.cpp), so the lanes here buy host parallelism first, copy/kernel overlap second.
 extern "C" int mnenc_decode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_t* const* mn, const size_t* mn_bytes, uint8_t** rgb,
-                                       size_t* width, size_t* height) {
+                                       size_t* width, size_t* height) try {
     if (!c || (n_images && (!mn || !mn_bytes || !rgb || !width || !height))) return fail(MNENC_ERR_ARG, "null argument");
     for (size_t i = 0; i < n_images; ++i) rgb[i] = nullptr, width[i] = height[i] = 0;
     if (n_images == 0) return MNENC_OK;
@@ -158,4 +160,6 @@ extern "C" int mnenc_decode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
     for (auto& m : c->ms) m = 0;
     c->ms[7] = static_cast<float>(nowMs() - t0);
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }

@@ -137,18 +137,22 @@ int decodeImage(mnenc_ctx* c, const uint8_t* mn, size_t mnBytes, uint8_t* rgbDev
 
 }  // namespace
 
-extern "C" int mnenc_decode_rgb8(mnenc_t* c, const uint8_t* mn, size_t mn_bytes, uint8_t** rgb, size_t* width, size_t* height) {
+extern "C" int mnenc_decode_rgb8(mnenc_t* c, const uint8_t* mn, size_t mn_bytes, uint8_t** rgb, size_t* width, size_t* height) try {
     if (!rgb) return fail(MNENC_ERR_ARG, "null argument");
     return decodeImage(c, mn, mn_bytes, nullptr, 0, 0, rgb, width, height);
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 extern "C" int mnenc_decode_rgb8_device(mnenc_t* c, const uint8_t* mn, size_t mn_bytes, uint8_t* rgb_dev, size_t capacity_bytes,
-                                        size_t row_stride_bytes, size_t* width, size_t* height) {
+                                        size_t row_stride_bytes, size_t* width, size_t* height) try {
     if (!rgb_dev) return fail(MNENC_ERR_ARG, "null argument");
     return decodeImage(c, mn, mn_bytes, rgb_dev, capacity_bytes, row_stride_bytes, nullptr, width, height);
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-extern "C" int mnenc_stream_info(const uint8_t* mn, size_t mn_bytes, size_t* width, size_t* height, int* K, int* block_size, float* quant) {
+extern "C" int mnenc_stream_info(const uint8_t* mn, size_t mn_bytes, size_t* width, size_t* height, int* K, int* block_size, float* quant) try {
     if (!mn) return fail(MNENC_ERR_ARG, "null argument");
     MnParser P(mn, mn_bytes);
     std::string err;
@@ -159,10 +163,12 @@ extern "C" int mnenc_stream_info(const uint8_t* mn, size_t mn_bytes, size_t* wid
     if (block_size) *block_size = P.blockSize;
     if (quant) std::memcpy(quant, P.quant, sizeof(float) * 3 * P.K);
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 extern "C" int mnenc_debug_parse(const uint8_t* mn, size_t mn_bytes, uint16_t* lengths, size_t lengths_capacity, uint64_t* stream_offsets,
-                                 uint16_t* symbols, size_t symbols_capacity, int threads) {
+                                 uint16_t* symbols, size_t symbols_capacity, int threads) try {
     if (!mn || !lengths || !stream_offsets) return fail(MNENC_ERR_ARG, "null argument");
     std::unique_ptr<HostPool> pool;
     if (threads > 1) pool = std::make_unique<HostPool>(std::min(threads, 64));
@@ -180,4 +186,6 @@ extern "C" int mnenc_debug_parse(const uint8_t* mn, size_t mn_bytes, uint16_t* l
         return 0;
     });
     return code == MNENC_OK ? MNENC_OK : fail(code, err);
+} catch (...) {
+    return mnenc::abiCaught();
 }

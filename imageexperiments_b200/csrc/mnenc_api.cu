@@ -31,6 +31,25 @@ int fail(int code, const std::string& msg) {
     return code;
 }
 
+// No exception crosses the ABI (include/mnenc.h): every int-returning entry point is a function-try-block that ends here.
+// The context may be left mid-call (its scratch buffers are rewritten by the next call; the histogram may hold stale bins
+// after an exception between the histogram and its reset, so the caller should destroy the context after MNENC_ERR_INTERNAL).
+int abiCaught() noexcept {
+    try {
+        try {
+            throw;
+        } catch (const std::bad_alloc&) {
+            return fail(MNENC_ERR_INTERNAL, "out of host memory");
+        } catch (const std::exception& e) {
+            return fail(MNENC_ERR_INTERNAL, std::string("unexpected exception: ") + e.what());
+        } catch (...) {
+            return fail(MNENC_ERR_INTERNAL, "unexpected exception");
+        }
+    } catch (...) {  // not even the text could be stored
+        return MNENC_ERR_INTERNAL;
+    }
+}
+
 void mergeOverlays(uint8_t* res, const std::vector<Overlay>& overlays) {
     for (const Overlay& o : overlays) {
         const uint64_t shift = o.bitPos & 7;
@@ -449,14 +468,16 @@ const char* mnenc_last_error(void) { return g_error.c_str(); }
 
 void mnenc_free(uint8_t* p) { resultRelease(p); }
 
-int mnenc_quant_tables(int K, int block_size, double bpp_allocation, float* out_3K) {
+int mnenc_quant_tables(int K, int block_size, double bpp_allocation, float* out_3K) try {
     if (!out_3K) return fail(MNENC_ERR_ARG, "null argument");
     if (mnenc::quantTables(K, block_size, bpp_allocation, out_3K) != 0) return fail(MNENC_ERR_ARG, "unsupported K / block size");
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* base, int n_base, const int32_t* detail_rows,
-                 const float* detailY, const float* detailU, const float* detailV) {
+                 const float* detailY, const float* detailU, const float* detailV) try {
     using namespace mnenc;
     if (!out || !base || !detail_rows || !detailY || !detailU || !detailV) return fail(MNENC_ERR_ARG, "null argument");
     if (block_size != 8) return fail(MNENC_ERR_ARG, "only block_size 8 is supported");
@@ -562,6 +583,8 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
 #undef CUB
     *out = c;
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 void mnenc_destroy(mnenc_t* c) {
@@ -577,7 +600,7 @@ void mnenc_destroy(mnenc_t* c) {
     delete c;
 }
 
-int mnenc_set_quant(mnenc_t* c, const float* q) {
+int mnenc_set_quant(mnenc_t* c, const float* q) try {
     if (!c || !q) return fail(MNENC_ERR_ARG, "null argument");
     for (int i = 0; i < 3 * c->K; ++i)
         if (!(q[i] >= 1.0f) || q[i] > 65535.0f) return fail(MNENC_ERR_ARG, "quantisers must be in [1,65535]");
@@ -589,6 +612,8 @@ int mnenc_set_quant(mnenc_t* c, const float* q) {
     CU(cudaStreamSynchronize(c->stream));
     c->quantSet = true;
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 static int encodeDevice(mnenc_t* c, const uint8_t* rgbDev, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes,
@@ -600,16 +625,18 @@ static int encodeDevice(mnenc_t* c, const uint8_t* rgbDev, size_t w, size_t h, s
     return MNENC_OK;
 }
 
-int mnenc_encode_rgb8_device(mnenc_t* c, const uint8_t* rgb_dev, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes) {
+int mnenc_encode_rgb8_device(mnenc_t* c, const uint8_t* rgb_dev, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes) try {
     if (int rc = checkEncodeArgs(c, rgb_dev, w, h, stride, out, outBytes)) return rc;
     CU(cudaSetDevice(c->device));
     const double t0 = nowMs();
     c->launches = 0;
     c->ms[0] = 0;
     return encodeDevice(c, rgb_dev, w, h, stride, out, outBytes, t0);
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-int mnenc_encode_rgb8(mnenc_t* c, const uint8_t* rgb, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes) {
+int mnenc_encode_rgb8(mnenc_t* c, const uint8_t* rgb, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes) try {
     if (int rc = checkEncodeArgs(c, rgb, w, h, stride, out, outBytes)) return rc;
     CU(cudaSetDevice(c->device));
     const double t0 = nowMs();
@@ -620,9 +647,11 @@ int mnenc_encode_rgb8(mnenc_t* c, const uint8_t* rgb, size_t w, size_t h, size_t
     c->ms[0] = 0;
     int rc = encodeDevice(c, c->rgb.as<uint8_t>(), w, h, 3 * w, out, outBytes, t0);
     return rc;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-int mnenc_get_symbols(mnenc_t* c, uint16_t* counts, uint16_t* pairs) {
+int mnenc_get_symbols(mnenc_t* c, uint16_t* counts, uint16_t* pairs) try {
     if (!c || !counts || !pairs) return fail(MNENC_ERR_ARG, "null argument");
     if (!c->haveSymbols) return fail(MNENC_ERR_STATE, "no encode has run on this context");
     CU(cudaSetDevice(c->device));
@@ -631,9 +660,11 @@ int mnenc_get_symbols(mnenc_t* c, uint16_t* counts, uint16_t* pairs) {
     CU(cudaMemcpyAsync(pairs, c->pairs.p, nbc * c->K * 4, cudaMemcpyDeviceToHost, c->stream));  // u32 = {deltaId, intCoeff} little-endian
     CU(cudaStreamSynchronize(c->stream));
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-int mnenc_pack_symbols(mnenc_t* c, size_t w, size_t h, const uint16_t* counts, const uint16_t* pairs, uint8_t** out, size_t* outBytes) {
+int mnenc_pack_symbols(mnenc_t* c, size_t w, size_t h, const uint16_t* counts, const uint16_t* pairs, uint8_t** out, size_t* outBytes) try {
     if (!c || !counts || !pairs || !out || !outBytes) return fail(MNENC_ERR_ARG, "null argument");
     if (w == 0 || h == 0) return fail(MNENC_ERR_ARG, "bad image geometry");
     if (!c->quantSet) return fail(MNENC_ERR_STATE, "mnenc_set_quant has not been called");
@@ -655,25 +686,31 @@ int mnenc_pack_symbols(mnenc_t* c, size_t w, size_t h, const uint16_t* counts, c
     int rc = runBackend(c, w, h, out, outBytes);
     c->ms[7] = static_cast<float>(nowMs() - t0);
     return rc;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-int mnenc_last_timing(mnenc_t* c, float* ms8) {
+int mnenc_last_timing(mnenc_t* c, float* ms8) try {
     if (!c || !ms8) return fail(MNENC_ERR_ARG, "null argument");
     std::memcpy(ms8, c->ms, sizeof(c->ms));
     return c->launches;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-int mnenc_last_work(mnenc_t* c, double* mp_flops, uint64_t* n_symbols, uint64_t* n_bits) {
+int mnenc_last_work(mnenc_t* c, double* mp_flops, uint64_t* n_symbols, uint64_t* n_bits) try {
     if (!c) return fail(MNENC_ERR_ARG, "null argument");
     if (mp_flops) *mp_flops = c->mpFlops;
     if (n_symbols) *n_symbols = c->nSymbols;
     if (n_bits) *n_bits = c->nBits;
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 int mnenc_debug_plan_sequence(const uint32_t* symbols, const uint32_t* freqs, const uint32_t* first_pos, size_t n, uint32_t* golomb_m,
                               uint32_t* codes, uint8_t* lens, uint32_t* eof_code, uint8_t* eof_len, uint8_t* header_bytes,
-                              size_t header_cap, uint64_t* header_bits, uint64_t* payload_bits) {
+                              size_t header_cap, uint64_t* header_bits, uint64_t* payload_bits) try {
     if (!golomb_m || !eof_code || !eof_len || !header_bits || !payload_bits || (n && (!symbols || !freqs || !first_pos || !codes || !lens)))
         return fail(MNENC_ERR_ARG, "null argument");
     std::vector<mnenc::SymbolStat> stats(n);
@@ -692,14 +729,18 @@ int mnenc_debug_plan_sequence(const uint32_t* symbols, const uint32_t* freqs, co
     if (plan.header.bytes.size() > header_cap) return fail(MNENC_ERR_ARG, "header buffer too small");
     if (header_bytes) std::memcpy(header_bytes, plan.header.bytes.data(), plan.header.bytes.size());
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-int mnenc_debug_stitch_runs(const uint32_t* records, int nranks, int n_streams, int rank, uint32_t* carry_in, uint32_t* extend_out) {
+int mnenc_debug_stitch_runs(const uint32_t* records, int nranks, int n_streams, int rank, uint32_t* carry_in, uint32_t* extend_out) try {
     if (!records || !carry_in || !extend_out || nranks < 1 || n_streams < 0 || rank < 0 || rank >= nranks)
         return fail(MNENC_ERR_ARG, "bad argument");
     static_assert(sizeof(mnenc::StripeBoundary) == 6 * sizeof(uint32_t), "record layout");
     mnenc::stitchRuns(reinterpret_cast<const mnenc::StripeBoundary*>(records), nranks, n_streams, rank, carry_in, extend_out);
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 uint32_t mnenc_debug_rle_chunk_size(uint32_t carry, uint32_t len, uint64_t total) { return mnenc::rleChunkedSize(carry, len, total); }

@@ -23,6 +23,7 @@
 namespace mnenc {
 
 int fail(int code, const std::string& msg);  // records the thread-local error text and returns `code`
+int abiCaught() noexcept;                    // inside a catch (...) of a C-ABI entry point: the exception becomes an error code + text
 
 #define CU(expr)                                                                                                          \
     do {                                                                                                                  \

@@ -69,7 +69,7 @@ using namespace mnenc;
 extern "C" {
 
 int mnenc_stripe_begin(mnenc_t* c, const uint8_t* rgb_stripe, int on_device, size_t width, size_t height, size_t row_stride_bytes, int rank,
-                       int nranks, uint32_t bx0, uint32_t bx1, uint32_t* rec1) {
+                       int nranks, uint32_t bx0, uint32_t bx1, uint32_t* rec1) try {
     if (!c || !rec1) return fail(MNENC_ERR_ARG, "null argument");
     if (width == 0 || height == 0 || width > 0xFFFFFFFFull || height > 0xFFFFFFFFull) return fail(MNENC_ERR_ARG, "bad image geometry");
     if (!c->quantSet) return fail(MNENC_ERR_STATE, "mnenc_set_quant has not been called");
@@ -174,9 +174,11 @@ int mnenc_stripe_begin(mnenc_t* c, const uint8_t* rgb_stripe, int on_device, siz
     c->ms[7] = static_cast<float>(nowMs() - t0);
     s->phase = 1;
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-int mnenc_stripe_rle(mnenc_t* c, const uint32_t* all_rec1, uint32_t* rec2) {
+int mnenc_stripe_rle(mnenc_t* c, const uint32_t* all_rec1, uint32_t* rec2) try {
     if (int rc = needPhase(c, 1)) return rc;
     if (!all_rec1 || !rec2) return fail(MNENC_ERR_ARG, "null argument");
     CU(cudaSetDevice(c->device));
@@ -202,10 +204,12 @@ int mnenc_stripe_rle(mnenc_t* c, const uint32_t* all_rec1, uint32_t* rec2) {
     c->ms[7] += static_cast<float>(nowMs() - t0);
     s->phase = 2;
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 int mnenc_stripe_histogram(mnenc_t* c, const uint32_t* all_rec2, void** hist_dev, void** first_pos_dev, size_t* hist_elems,
-                           void** max_sym_dev, size_t* max_sym_elems) {
+                           void** max_sym_dev, size_t* max_sym_elems) try {
     if (int rc = needPhase(c, 2)) return rc;
     if (!all_rec2 || !hist_dev || !first_pos_dev || !hist_elems || !max_sym_dev || !max_sym_elems) return fail(MNENC_ERR_ARG, "null argument");
     CU(cudaSetDevice(c->device));
@@ -295,9 +299,11 @@ int mnenc_stripe_histogram(mnenc_t* c, const uint32_t* all_rec2, void** hist_dev
     c->ms[7] += static_cast<float>(nowMs() - t0);
     s->phase = 3;
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-int mnenc_stripe_plan(mnenc_t* c, uint64_t* seq_bits) {
+int mnenc_stripe_plan(mnenc_t* c, uint64_t* seq_bits) try {
     if (int rc = needPhase(c, 3)) return rc;
     if (!seq_bits) return fail(MNENC_ERR_ARG, "null argument");
     CU(cudaSetDevice(c->device));
@@ -366,9 +372,11 @@ int mnenc_stripe_plan(mnenc_t* c, uint64_t* seq_bits) {
     c->ms[7] += static_cast<float>(nowMs() - t0);
     s->phase = 4;
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-int mnenc_stripe_pack(mnenc_t* c, const uint64_t* all_seq_bits, void** out_dev, size_t* out_words, size_t* out_bytes) {
+int mnenc_stripe_pack(mnenc_t* c, const uint64_t* all_seq_bits, void** out_dev, size_t* out_words, size_t* out_bytes) try {
     if (int rc = needPhase(c, 4)) return rc;
     if (!all_seq_bits || !out_dev || !out_words || !out_bytes) return fail(MNENC_ERR_ARG, "null argument");
     CU(cudaSetDevice(c->device));
@@ -450,9 +458,11 @@ int mnenc_stripe_pack(mnenc_t* c, const uint64_t* all_seq_bits, void** out_dev, 
     c->ms[7] += static_cast<float>(nowMs() - t0);
     s->phase = 5;
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
-int mnenc_stripe_finish(mnenc_t* c, uint8_t** out, size_t* out_bytes) {
+int mnenc_stripe_finish(mnenc_t* c, uint8_t** out, size_t* out_bytes) try {
     if (int rc = needPhase(c, 5)) return rc;
     if (!out || !out_bytes) return fail(MNENC_ERR_ARG, "null argument");
     CU(cudaSetDevice(c->device));
@@ -480,10 +490,12 @@ int mnenc_stripe_finish(mnenc_t* c, uint8_t** out, size_t* out_bytes) {
     c->ms[7] += c->ms[6];
     s->phase = 0;
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 int mnenc_debug_plan_stripes(const uint32_t* records, int nranks, int n_streams, uint32_t* emitted, uint8_t* use_rle, uint64_t* raw_len,
-                             uint64_t* rle_len) {
+                             uint64_t* rle_len) try {
     if (!records || !emitted || !use_rle || !raw_len || !rle_len || nranks < 1 || n_streams < 0) return fail(MNENC_ERR_ARG, "bad argument");
     StripePlan plan;
     planStripes(reinterpret_cast<const StripeBoundary*>(records), nranks, n_streams, plan);
@@ -492,6 +504,8 @@ int mnenc_debug_plan_stripes(const uint32_t* records, int nranks, int n_streams,
     std::copy(plan.rawLen.begin(), plan.rawLen.end(), raw_len);
     std::copy(plan.rleLen.begin(), plan.rleLen.end(), rle_len);
     return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
 }
 
 }  // extern "C"

@@ -93,3 +93,16 @@ def test_python_host_fails_loudly_without_library(monkeypatch, tmp_path):
     monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "libmnenc.so"))
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         _lib.load()
+
+
+def test_no_exception_crosses_the_abi():
+    """include/mnenc.h: "No exception crosses the ABI" — a host-side std::length_error / bad_alloc comes back as an error code."""
+    L = _lib.load()
+    buf = (C.c_uint32 * 16)()
+    b8 = (C.c_uint8 * 64)()
+    u64 = (C.c_uint64 * 2)()
+    p = lambda x: C.cast(x, C.c_void_p)  # noqa: E731
+    rc = L.mnenc_debug_plan_sequence(p(buf), p(buf), p(buf), 1 << 62, p(buf), p(buf), p(b8), p(buf), p(b8), p(b8), 64, p(u64), p(u64))
+    assert rc == -4, rc  # MNENC_ERR_INTERNAL
+    text = L.mnenc_last_error().decode()
+    assert "exception" in text or "memory" in text, text
