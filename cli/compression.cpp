@@ -86,9 +86,12 @@ void savePpm(const std::string& path, const uint8_t* px, size_t w, size_t h) {
 }
 
 std::vector<uint8_t> loadFile(const std::string& path) {
+    std::error_code ec;
+    if (!std::filesystem::is_regular_file(path, ec)) die("cannot open " + path);
     std::ifstream f(path, std::ios::binary | std::ios::ate);
     if (!f) die("cannot open " + path);
     const std::streamsize n = f.tellg();
+    if (n < 0) die("cannot read " + path);
     std::vector<uint8_t> b(static_cast<size_t>(n));
     f.seekg(0);
     f.read(reinterpret_cast<char*>(b.data()), n);

@@ -42,6 +42,8 @@ def test_usage_and_argument_errors(exe, tmp_path):
         assert r.returncode == 255 and "usage: Compression -c" in r.stdout  # return -1, Compression.cpp:92-95
     r = run("-c", "3.5", str(tmp_path / "missing.ppm"), str(tmp_path / "o.mn"))
     assert r.returncode == 1 and "cannot open" in r.stderr
+    r = run("-d", str(tmp_path), str(tmp_path / "o.ppm"))  # a folder is not a stream
+    assert r.returncode == 1 and "cannot open" in r.stderr
     (tmp_path / "bad.ppm").write_bytes(b"P5\n4 4\n255\n" + bytes(16))
     r = run("-c", "3.5", str(tmp_path / "bad.ppm"), str(tmp_path / "o.mn"))
     assert r.returncode == 1 and "not a binary PPM" in r.stderr
