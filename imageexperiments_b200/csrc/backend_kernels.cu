@@ -602,7 +602,7 @@ struct PackOut {
 // to be verified with `MNENC_PACK=2 python -m pytest tests/test_gpu_parity.py tests/test_gpu_stripes.py` and measured against
 // the default first thing next round). Same positions, same bits; what changes is the traffic to L2:
 //  * a thread's eight consecutive codes are merged in a register (WordAcc, csrc/word_acc.h — the host build of that header
-//    is checked against a bit-by-bit writer by tests/test_word_acc.py) and leave as one atomicOr per output word touched
+//    is checked against a bit-by-bit writer by tests/test_native.py) and leave as one atomicOr per output word touched
 //    instead of one or two per code (mean code ≈ 4.6 bits: ≈2.2 atomics per thread instead of ≈9);
 //  * the sequence of an item is found once per thread (binary search) and then advanced, its descriptor and code plan are
 //    reloaded only when it changes, and the table entry fetched for the length is kept for the emission.

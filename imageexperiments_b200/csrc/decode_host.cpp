@@ -634,10 +634,16 @@ int MnParser::withTeam(const std::function<int()>& body) {
     SpinTeam team(pool->size());
     int rc = 0;
     pool->withHelpers([&] { team.helper(); }, [&] {
+        struct Release {  // on every path out of body(), an exception included: the helpers spin until finish()
+            Impl* impl;
+            SpinTeam* team;
+            ~Release() {
+                impl->team = nullptr;
+                team->finish();
+            }
+        } release{impl_, &team};
         impl_->team = &team;
         rc = body();
-        impl_->team = nullptr;
-        team.finish();
     });
     return rc;
 }

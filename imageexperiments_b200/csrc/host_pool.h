@@ -5,6 +5,7 @@
 
 #include <atomic>
 #include <condition_variable>
+#include <exception>
 #include <functional>
 #include <memory>
 #include <mutex>
@@ -52,6 +53,7 @@ public:
         std::unique_lock<std::mutex> g(m_);
         done_.wait(g, [&] { return job->pending == 0; });
         job_.reset();
+        if (job->error) std::rethrow_exception(job->error);  // first exception of any index, on the calling thread
     }
 
     // body() on the calling thread while every other pool thread runs helper() (which must return once body is done —
@@ -72,10 +74,17 @@ public:
             ++epoch_;
         }
         wake_.notify_all();
-        body();
+        std::exception_ptr bodyError;
+        try {
+            body();
+        } catch (...) {  // the helpers still hold `fn`: wait for them first (the caller's body must release them on every path)
+            bodyError = std::current_exception();
+        }
         std::unique_lock<std::mutex> g(m_);
         done_.wait(g, [&] { return job->pending == 0; });
         job_.reset();
+        if (bodyError) std::rethrow_exception(bodyError);
+        if (job->error) std::rethrow_exception(job->error);
     }
 
 private:
@@ -84,13 +93,19 @@ private:
         int n = 0;
         std::atomic<int> next{0};
         int pending = 0;  // guarded by m_
+        std::exception_ptr error;  // guarded by m_: first exception thrown by fn on any thread
     };
     void drain(Job& job) {
         int ran = 0;
         while (true) {
             const int i = job.next.fetch_add(1, std::memory_order_relaxed);
             if (i >= job.n) break;
-            (*job.fn)(i);
+            try {
+                (*job.fn)(i);
+            } catch (...) {  // never out of a worker thread (std::terminate) and never past a job the others still run
+                std::lock_guard<std::mutex> g(m_);
+                if (!job.error) job.error = std::current_exception();
+            }
             ++ran;
         }
         if (ran) {
