@@ -218,8 +218,8 @@ struct HuffTable {
     uint32_t count[kMaxCodeLen + 2] = {};
     std::vector<uint32_t> lut;               // [1 << kLutBits]: index << 8 | length, 0 = not resolved by the table
     std::vector<uint32_t> fast;              // same slots: symbol << 8 | length, or kSpecial (pseudo-EOF, long code, no code)
-    std::vector<uint64_t> pair;              // same slots, up to TWO codes: bits 0-7 total length, 8-15 symbols (0 = special),
-                                             // 16-31 first symbol, 32-47 second symbol
+    std::vector<uint64_t> pair;              // same slots, up to THREE codes: bits 0-7 total length, 8-15 symbols (0 = special),
+                                             // 16-31 first symbol, 32-47 second, 48-63 third
 
     void read(BitReader& in) {
         maxLen = static_cast<int>(in.read(8));
@@ -284,14 +284,20 @@ struct HuffTable {
             const uint32_t l0 = e0 & 0xFF;
             uint64_t v = static_cast<uint64_t>(e0 >> 8) << 16 | 1u << 8 | l0;
             const uint32_t e1 = fast[(slot << l0) & ((1u << kLutBits) - 1u)];
-            if (e1 < kSpecial && l0 + (e1 & 0xFF) <= static_cast<uint32_t>(kLutBits))
-                v = static_cast<uint64_t>(e1 >> 8) << 32 | static_cast<uint64_t>(e0 >> 8) << 16 | 2u << 8 | (l0 + (e1 & 0xFF));
+            if (e1 < kSpecial && l0 + (e1 & 0xFF) <= static_cast<uint32_t>(kLutBits)) {
+                const uint32_t l01 = l0 + (e1 & 0xFF);
+                v = static_cast<uint64_t>(e1 >> 8) << 32 | static_cast<uint64_t>(e0 >> 8) << 16 | 2u << 8 | l01;
+                const uint32_t e2 = fast[(slot << l01) & ((1u << kLutBits) - 1u)];
+                if (e2 < kSpecial && l01 + (e2 & 0xFF) <= static_cast<uint32_t>(kLutBits))
+                    v = static_cast<uint64_t>(e2 >> 8) << 48 | static_cast<uint64_t>(e1 >> 8) << 32 | static_cast<uint64_t>(e0 >> 8) << 16 | 3u << 8 |
+                        (l01 + (e2 & 0xFF));
+            }
             pair[slot] = v;
         }
     }
 
     // Payload codes up to the pseudo-EOF into out[n0, cap); returns the number of symbols (Huffman.cpp:227-243).
-    // fastRun: one unconditional 8-byte refill, then up to four table hits (4 x 12 <= 56 valid bits), each giving one or two
+    // fastRun: one unconditional 8-byte refill, then up to four table hits (4 x 12 <= 56 valid bits), each giving one to three
     // symbols, without any end-of-stream or capacity test; everything else (long codes, the pseudo-EOF, the last bytes, the
     // last symbols) goes through step().
     size_t decode(BitReader& in, uint16_t* out, size_t cap, size_t n0 = 0) const {
@@ -412,7 +418,7 @@ struct HuffTable {
 private:
     // Table hits only, while at least 8 input bytes and 8 output slots remain and the position is below `untilBit`.
     void fastRun(BitReader& in, uint16_t* out, size_t& n, size_t cap, uint64_t untilBit) const {
-        while (in.end_ - in.ptr_ >= 8 && n + 8 <= cap && in.cnt_ >= 0 &&
+        while (in.end_ - in.ptr_ >= 8 && n + 16 <= cap && in.cnt_ >= 0 &&
                static_cast<uint64_t>(in.ptr_ - in.base_) * 8 - static_cast<uint64_t>(in.cnt_) < untilBit) {
             uint64_t w;
             std::memcpy(&w, in.ptr_, 8);
@@ -427,8 +433,8 @@ private:
                     special = true;
                     break;
                 }
-                out[n] = static_cast<uint16_t>(e >> 16);
-                out[n + 1] = static_cast<uint16_t>(e >> 32);  // junk when got == 1: overwritten by the next symbol
+                const uint64_t syms = e >> 16;  // one 8-byte store: the symbols beyond `got` are junk, overwritten by the next hit
+                std::memcpy(out + n, &syms, 8);
                 n += got;
                 buf <<= (e & 0xFF);
                 cnt -= static_cast<int>(e & 0xFF);
