@@ -17,9 +17,9 @@ namespace {
 int makeLane(mnenc_ctx* parent, int threads, mnenc_ctx** out) {
     mnenc_ctx* l = new mnenc_ctx;
     l->device = parent->device, l->K = parent->K, l->nBase = parent->nBase, l->numSMs = parent->numSMs;
-    l->epsRel = parent->epsRel, l->epsRel16 = parent->epsRel16, l->epsAbs16 = parent->epsAbs16, l->mpMode = parent->mpMode;
+    l->epsRel16 = parent->epsRel16, l->epsAbs16 = parent->epsAbs16, l->mpMode = parent->mpMode;
     l->epsRel16Hi = parent->epsRel16Hi, l->residualLo = parent->residualLo;
-    l->baseT.alias(parent->baseT), l->baseUm.alias(parent->baseUm), l->detT.alias(parent->detT), l->detRows.alias(parent->detRows);
+    l->detRows.alias(parent->detRows);
     l->baseUm16.alias(parent->baseUm16), l->detUm16.alias(parent->detUm16), l->rows32.alias(parent->rows32);
     l->quant.alias(parent->quant);
     l->hostThreads = threads;
@@ -28,6 +28,7 @@ int makeLane(mnenc_ctx* parent, int threads, mnenc_ctx** out) {
     CU(cudaStreamCreateWithFlags(&l->stream, cudaStreamNonBlocking));
     for (auto& e : l->ev) CU(cudaEventCreate(&e));
     CU(cudaEventCreateWithFlags(&l->evSync, cudaEventDisableTiming));
+    for (auto& e : l->evWave) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming | cudaEventBlockingSync));
     return MNENC_OK;
 }
 

@@ -21,11 +21,14 @@
 #include <bit>
 #include <cmath>
 #include <cstring>
+#include <exception>
 #include <functional>
+#include <mutex>
 #include <string>
 #include <vector>
 
 #include "host_pool.h"
+#include "spin_team.h"
 #include "mnenc_internal.h"
 
 namespace mnenc {
@@ -139,70 +142,6 @@ inline uint32_t eliasFanoBound(uint32_t n, uint32_t maxSymbol) {
 }
 
 inline int32_t unzigzag(uint32_t x) { return static_cast<int32_t>((x >> 1) ^ -(static_cast<int64_t>(x) & 1)); }  // BitBuffer.h:112-114
-
-// The threads of a HostPool held inside ONE parallelFor for the duration of an image. A sequence's chunks are tiny (tens of
-// microseconds each), far below the wake-up latency of a condition variable, so the helpers spin on an atomic ticket
-// instead: ticket = generation << 32 | next index; a job is published by writing its slot (generation parity) and then
-// storing the new ticket. A helper that draws a stale ticket sees the slot's generation differ and backs off.
-class SpinTeam {
-public:
-    explicit SpinTeam(int threads) : threads_(threads) {}
-    int size() const { return threads_; }
-    void forEach(int n, const std::function<void(int)>& fn) {
-        if (n <= 0) return;
-        if (threads_ <= 1) {
-            for (int i = 0; i < n; ++i) fn(i);
-            return;
-        }
-        const uint64_t g = ++gen_;
-        Job& j = jobs_[g & 1];
-        j.fn.store(&fn, std::memory_order_relaxed);
-        j.n.store(n, std::memory_order_relaxed);
-        j.pending.store(n, std::memory_order_relaxed);
-        j.gen.store(g, std::memory_order_release);
-        ticket_.store(g << 32, std::memory_order_release);
-        drain();
-        while (j.pending.load(std::memory_order_acquire) > 0) pause();
-    }
-    void helper() {  // body of every pool thread but the caller's
-        for (unsigned idle = 0; !quit_.load(std::memory_order_acquire); ++idle) {
-            drain();
-            if ((idle & 63) == 63)
-                sched_yield();  // stay polite when there are more threads than cores
-            else
-                pause();
-        }
-    }
-    void finish() { quit_.store(true, std::memory_order_release); }
-
-private:
-    struct Job {
-        std::atomic<const std::function<void(int)>*> fn{nullptr};
-        std::atomic<int> n{0}, pending{0};
-        std::atomic<uint64_t> gen{0};
-    };
-    static void pause() { __builtin_ia32_pause(); }
-    void drain() {
-        for (;;) {
-            const uint64_t peek = ticket_.load(std::memory_order_acquire);
-            const uint64_t g = peek >> 32;
-            if (g == 0) return;
-            Job& j = jobs_[g & 1];
-            if (j.gen.load(std::memory_order_acquire) != g || static_cast<int>(peek & 0xFFFFFFFFu) >= j.n.load(std::memory_order_relaxed)) return;
-            const uint64_t t = ticket_.fetch_add(1, std::memory_order_acq_rel);
-            if ((t >> 32) != g) continue;  // a new job was published in between: look again
-            const int i = static_cast<int>(t & 0xFFFFFFFFu);
-            if (j.gen.load(std::memory_order_acquire) != g || i >= j.n.load(std::memory_order_relaxed)) return;
-            (*j.fn.load(std::memory_order_relaxed))(i);
-            j.pending.fetch_sub(1, std::memory_order_release);
-        }
-    }
-    int threads_;
-    std::atomic<uint64_t> ticket_{0};
-    std::atomic<bool> quit_{false};
-    uint64_t gen_ = 0;
-    Job jobs_[2];
-};
 
 constexpr int kLutBits = 12;
 constexpr int kMaxCodeLen = 48;

@@ -141,6 +141,7 @@ void resultRelease(uint8_t* p) {
 }
 
 int ensureHistogram(mnenc_ctx* c) {
+    if (c->histDirty) c->histReady = false, c->histDirty = false;  // an earlier encode failed between the histogram and its reset
     if (c->histReady) return MNENC_OK;
     const size_t bins = static_cast<size_t>(kMaxSeq) * kHistBins;
     CU(c->hist.ensure(bins * 4));
@@ -234,6 +235,7 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     c->launches += launchRleAndDecide(b, so, N, st);
     c->launches += launchDecide(b, so, nullptr, st);
     CU(cudaEventRecord(c->ev[3], st));
+    c->histDirty = true;  // until the touched bins have been reset: an early return leaves stale counts (ensureHistogram)
     c->launches += launchHistogram(b, upperM, nSeq, st);
     CU(cudaEventRecord(c->ev[4], st));
     const uint32_t firstChunk = 1u << 16;
@@ -249,6 +251,7 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
         CU(c->entries.ensure(static_cast<size_t>(c->entryCap) * sizeof(HistEntry)));
         c->histReady = false;
         if (int rc = ensureHistogram(c)) return rc;
+        c->histDirty = true;
         b.entries = c->entries.as<HistEntry>();
         b.entryCap = c->entryCap;
         c->launches += launchHistogram(b, upperM, nSeq, st);
@@ -357,6 +360,7 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     CU(cudaEventRecord(c->ev[5], st));
     c->launches += launchPack(b, M, nSeq, st);
     c->launches += launchResetHistogram(b, nEntries, st);
+    c->histDirty = false;
     CU(cudaEventRecord(c->ev[6], st));
     uint8_t* res = resultAcquire(totalBytes);
     if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
@@ -387,6 +391,84 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     return MNENC_OK;
 }
 
+// Level-synchronous matching pursuit: one round of kernels per greedy iteration (mp_wave.cu). The host queues rounds
+// kWaveLookahead iterations ahead of the GPU and stops as soon as a finished round reports no active block-channel.
+static int runWavePursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride, uint32_t nbx, uint32_t nby,
+                          uint32_t nbc) {
+    constexpr int kWaveLookahead = 3;
+    if (nbc > 0x07FFFFFFu) return fail(MNENC_ERR_ARG, "image too large: more than 2^27 block-channels");
+    const int K = c->K, nbins = 3 * c->nBase;
+    const size_t n = nbc;
+    CU(c->wRes32.ensure(n * kN * 4));
+    CU(c->wRes16.ensure(n * kN * 2));
+    CU(c->wState.ensure(n * 16));
+    CU(c->wGroups.ensure(n * kMaxK * 2));
+    CU(c->wBest.ensure(n * 8));
+    CU(c->wAmax.ensure(n * 4));
+    CU(c->wNcand.ensure(n * 4));
+    CU(c->wCand.ensure(n * kCandSlots * 4));
+    CU(c->wAct0.ensure(n * 4));
+    CU(c->wAct1.ensure(n * 4));
+    CU(c->wMembers.ensure(waveMembersCapacity(nbc, K) * 4));
+    const size_t binWords = static_cast<size_t>(4 * nbins + 2), headWords = kMaxK + 2;  // nAct[K + 1] | binCount | binCursor | binOffset | binTileStart
+    CU(c->wBins.ensure((headWords + binWords) * 4));
+    CU(c->hWaveAct.ensure((kMaxK + 2) * 4));
+    CU(cudaMemsetAsync(c->wBins.p, 0, (headWords + binWords) * 4, c->stream));
+    WaveParams p{};
+    p.rgb = rgbDev;
+    p.stride = stride;
+    p.width = static_cast<int>(width);
+    p.height = static_cast<int>(height);
+    p.nbx = static_cast<int>(nbx);
+    p.nby = static_cast<int>(nby);
+    p.K = K;
+    p.nBase = c->nBase;
+    p.baseUm16 = c->baseUm16.as<uint16_t>();
+    p.detUm16 = c->detUm16.as<uint16_t>();
+    p.rows32 = c->rows32.as<float>();
+    p.detRows = c->detRows.as<uint8_t>();
+    p.quant = c->quant.as<float>();
+    p.epsRel16 = c->epsRel16Hi;
+    p.epsAbs16 = c->epsAbs16;
+    p.counts = c->counts.as<uint16_t>();
+    p.pairs = c->pairs.as<uint32_t>();
+    p.res32 = c->wRes32.as<float>();
+    p.res16 = c->wRes16.as<uint16_t>();
+    p.state = c->wState.as<uint4>();
+    p.groups = c->wGroups.as<uint16_t>();
+    p.best = c->wBest.as<unsigned long long>();
+    p.amax = c->wAmax.as<uint32_t>();
+    p.ncand = c->wNcand.as<uint32_t>();
+    p.cand = c->wCand.as<uint32_t>();
+    p.act[0] = c->wAct0.as<uint32_t>();
+    p.act[1] = c->wAct1.as<uint32_t>();
+    uint32_t* words = c->wBins.as<uint32_t>();
+    p.nAct = words;
+    p.binCount = words + headWords;
+    p.binCursor = p.binCount + nbins;
+    p.binOffset = p.binCursor + nbins;
+    p.binTileStart = p.binOffset + nbins + 1;
+    p.members = c->wMembers.as<uint32_t>();
+    p.stats = reinterpret_cast<unsigned long long*>(c->mpScratch.as<unsigned char>() + 16);
+    p.nbc = nbc;
+    CU(launchWaveInit(p, c->stream));
+    c->launches += 1;
+    uint32_t* hAct = c->hWaveAct.as<uint32_t>();
+    CU(cudaMemcpyAsync(hAct, p.nAct, 4, cudaMemcpyDeviceToHost, c->stream));
+    uint32_t hint = nbc;
+    for (int r = 0; r < K; ++r) {
+        if (r >= kWaveLookahead) {  // round r - kWaveLookahead has finished or is about to: its survivor count bounds this round's work
+            CU(cudaEventSynchronize(c->evWave[r - kWaveLookahead]));
+            hint = hAct[r - kWaveLookahead + 1];
+            if (hint == 0) break;
+        }
+        CU(launchWaveIteration(p, r, hint, c->numSMs, c->stream, &c->launches));
+        CU(cudaMemcpyAsync(hAct + r + 1, p.nAct + r + 1, 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaEventRecord(c->evWave[r], c->stream));
+    }
+    return MNENC_OK;
+}
+
 int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride) {
     const uint32_t nbx = static_cast<uint32_t>((width + 7) / 8), nby = static_cast<uint32_t>((height + 7) / 8);
     const uint64_t nbc64 = 3ull * nbx * nby;
@@ -397,39 +479,36 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     CU(c->mpScratch.ensure(64));
     CU(c->hStats.ensure(64));
     CU(cudaMemsetAsync(c->mpScratch.p, 0, 64, c->stream));
-    MpParams p{};
-    p.rgb = rgbDev;
-    p.stride = stride;
-    p.width = static_cast<int>(width);
-    p.height = static_cast<int>(height);
-    p.nbx = static_cast<int>(nbx);
-    p.nby = static_cast<int>(nby);
-    p.K = c->K;
-    p.nBase = c->nBase;
-    p.baseT = c->baseT.as<float>();
-    p.baseUm = c->baseUm.as<float>();
-    p.epsRel = c->epsRel;
-    p.detT = c->detT.as<float>();
-    p.detRows = c->detRows.as<uint8_t>();
-    p.quant = c->quant.as<float>();
-    p.counts = c->counts.as<uint16_t>();
-    p.pairs = c->pairs.as<uint32_t>();
-    p.workCounter = c->mpScratch.as<unsigned int>();
-    p.stats = reinterpret_cast<unsigned long long*>(c->mpScratch.as<unsigned char>() + 16);
-    p.nbc = nbc;
     CU(cudaEventRecord(c->ev[0], c->stream));
-    p.baseUm16 = c->baseUm16.as<uint16_t>();
-    p.detUm16 = c->detUm16.as<uint16_t>();
-    p.rows32 = c->rows32.as<float>();
-    p.epsRel16 = (c->mpMode == 3 && !c->residualLo) ? c->epsRel16Hi : c->epsRel16;
-    p.residualLo = c->residualLo;
-    p.epsAbs16 = c->epsAbs16;
-    p.debugTiming = std::getenv("MNENC_MP_TIMING") != nullptr;
-    if (c->mpMode == 3) CU(launchMatchingPursuitTeams(p, c->numSMs, c->stream));
-    else if (c->mpMode == 2) CU(launchMatchingPursuitF16(p, c->numSMs, c->stream));
-    else if (c->mpMode == 1) CU(launchMatchingPursuitTc(p, c->numSMs, c->stream));
-    else CU(launchMatchingPursuit(p, c->numSMs, c->stream));
-    c->launches += nbc ? 1 : 0;
+    if (c->mpMode == 4) {
+        if (int rc = runWavePursuit(c, rgbDev, width, height, stride, nbx, nby, nbc)) return rc;
+    } else {
+        MpParams p{};
+        p.rgb = rgbDev;
+        p.stride = stride;
+        p.width = static_cast<int>(width);
+        p.height = static_cast<int>(height);
+        p.nbx = static_cast<int>(nbx);
+        p.nby = static_cast<int>(nby);
+        p.K = c->K;
+        p.nBase = c->nBase;
+        p.detRows = c->detRows.as<uint8_t>();
+        p.quant = c->quant.as<float>();
+        p.counts = c->counts.as<uint16_t>();
+        p.pairs = c->pairs.as<uint32_t>();
+        p.workCounter = c->mpScratch.as<unsigned int>();
+        p.stats = reinterpret_cast<unsigned long long*>(c->mpScratch.as<unsigned char>() + 16);
+        p.nbc = nbc;
+        p.baseUm16 = c->baseUm16.as<uint16_t>();
+        p.detUm16 = c->detUm16.as<uint16_t>();
+        p.rows32 = c->rows32.as<float>();
+        p.epsRel16 = !c->residualLo ? c->epsRel16Hi : c->epsRel16;
+        p.residualLo = c->residualLo;
+        p.epsAbs16 = c->epsAbs16;
+        p.debugTiming = std::getenv("MNENC_MP_TIMING") != nullptr;
+        CU(launchMatchingPursuitTeams(p, c->numSMs, c->stream));
+        c->launches += nbc ? 1 : 0;
+    }
     CU(cudaEventRecord(c->ev[1], c->stream));
     CU(cudaMemcpyAsync(c->hStats.p, c->mpScratch.as<unsigned char>() + 16, 16, cudaMemcpyDeviceToHost, c->stream));
     c->lastW = width;
@@ -509,27 +588,8 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
     CUB(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     for (auto& e : c->ev) CUB(cudaEventCreate(&e));
     CUB(cudaEventCreateWithFlags(&c->evSync, cudaEventDisableTiming));
-    // base atoms transposed + zero padded: baseT[j*512 + atom]
-    std::vector<float> baseT(static_cast<size_t>(kN) * kRowsPad, 0.0f);
-    for (int a = 0; a < n_base; ++a)
-        for (int j = 0; j < kN; ++j) baseT[static_cast<size_t>(j) * kRowsPad + a] = base[static_cast<size_t>(a) * kN + j];
-    CUB(c->baseT.ensure(baseT.size() * 4));
-    CUB(cudaMemcpy(c->baseT.p, baseT.data(), baseT.size() * 4, cudaMemcpyHostToDevice));
-    // the same atoms as the canonical K-major UMMA operand image for the tensor-core pre-filter
-    std::vector<float> baseUm(static_cast<size_t>(kN) * kRowsPad);
-    buildUmmaImage(base, n_base, baseUm.data());
-    CUB(c->baseUm.ensure(baseUm.size() * 4));
-    CUB(cudaMemcpy(c->baseUm.p, baseUm.data(), baseUm.size() * 4, cudaMemcpyHostToDevice));
-    {   // pre-filter error bound: |tf32 score - oracle fp32 score| <= (2*2^-10 + 2^-20 + 6e-6) * ||d|| * ||r||, 15 % margin
-        double maxNorm = 0.0;
-        for (int a = 0; a < n_base; ++a) {
-            double ss = 0.0;
-            for (int j = 0; j < kN; ++j) ss += static_cast<double>(base[static_cast<size_t>(a) * kN + j]) * base[static_cast<size_t>(a) * kN + j];
-            maxNorm = std::max(maxNorm, std::sqrt(ss));
-        }
-        c->epsRel = static_cast<float>((2.0 / 1024.0 + 1.0 / 1048576.0 + 6e-6) * maxNorm * 1.15);
-    }
-    if (const char* mode = std::getenv("MNENC_MP")) c->mpMode = std::string(mode) == "fp32" ? 0 : (std::string(mode) == "tf32" ? 1 : (std::string(mode) == "f16" ? 2 : 3));
+    for (auto& e : c->evWave) CUB(cudaEventCreateWithFlags(&e, cudaEventDisableTiming | cudaEventBlockingSync));
+    if (const char* mode = std::getenv("MNENC_MP")) c->mpMode = std::string(mode) == "teams" ? 3 : 4;
     {   // fp16 operand images + exact row table of the fp16 tensor-core kernel, and its rigorous pre-filter bound:
         //   |p~ - p_oracle| <= ||d - fp16(d)|| ||r||  (dictionary rounding, Cauchy-Schwarz)
         //                    + ||d|| ||r|| (2^-22 residual hi/lo split + 4e-5 tensor-core accumulation + 64 * 2^-24 oracle rounding)
@@ -561,22 +621,8 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
         c->hostThreads = std::clamp(threads, 1, 16);
         c->pool = std::make_unique<HostPool>(c->hostThreads);
     }
-    // detail groups transposed per group: detT[((ch*nBase + atom)*64 + j)*64 + row], rows padded with zeros
     std::vector<uint8_t> rows(kRowsPad, 0);
-    std::vector<float> detT(static_cast<size_t>(3) * n_base * kN * 64, 0.0f);
-    const float* det[3] = {detailY, detailU, detailV};
-    for (int ch = 0; ch < 3; ++ch) {
-        size_t rowOff = 0;
-        for (int a = 0; a < n_base; ++a) {
-            rows[a] = static_cast<uint8_t>(detail_rows[a]);
-            float* g = detT.data() + (static_cast<size_t>(ch) * n_base + a) * kN * 64;
-            for (int r = 0; r < detail_rows[a]; ++r)
-                for (int j = 0; j < kN; ++j) g[j * 64 + r] = det[ch][(rowOff + r) * kN + j];
-            rowOff += detail_rows[a];
-        }
-    }
-    CUB(c->detT.ensure(detT.size() * 4));
-    CUB(cudaMemcpy(c->detT.p, detT.data(), detT.size() * 4, cudaMemcpyHostToDevice));
+    for (int a = 0; a < n_base; ++a) rows[a] = static_cast<uint8_t>(detail_rows[a]);
     CUB(c->detRows.ensure(kRowsPad));
     CUB(cudaMemcpy(c->detRows.p, rows.data(), kRowsPad, cudaMemcpyHostToDevice));
     CUB(c->quant.ensure(3 * kMaxK * 4));
@@ -596,6 +642,8 @@ void mnenc_destroy(mnenc_t* c) {
     for (auto& e : c->ev)
         if (e) cudaEventDestroy(e);
     if (c->evSync) cudaEventDestroy(c->evSync);
+    for (auto& e : c->evWave)
+        if (e) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -659,6 +707,9 @@ int mnenc_get_symbols(mnenc_t* c, uint16_t* counts, uint16_t* pairs) try {
     CU(cudaMemcpyAsync(counts, c->counts.p, nbc * 2, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(pairs, c->pairs.p, nbc * c->K * 4, cudaMemcpyDeviceToHost, c->stream));  // u32 = {deltaId, intCoeff} little-endian
     CU(cudaStreamSynchronize(c->stream));
+    // the kernels write only the `count` pairs of a block-channel (the back end reads no others): 0 beyond, as documented
+    for (size_t bc = 0; bc < nbc; ++bc)
+        for (int i = counts[bc]; i < c->K; ++i) pairs[(bc * c->K + i) * 2] = pairs[(bc * c->K + i) * 2 + 1] = 0;
     return MNENC_OK;
 } catch (...) {
     return mnenc::abiCaught();

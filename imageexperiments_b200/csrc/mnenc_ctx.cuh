@@ -112,13 +112,16 @@ struct mnenc_ctx {
     bool quantSet = false;
     float hQuant[3 * mnenc::kMaxK] = {};
     // dictionary
-    mnenc::DevBuf baseT, baseUm, detT, detRows, quant, baseUm16, detUm16, rows32;
-    float epsRel = 0.0f, epsRel16 = 0.0f, epsAbs16 = 0.0f, epsRel16Hi = 0.0f;
+    mnenc::DevBuf detRows, quant, baseUm16, detUm16, rows32;
+    float epsRel16 = 0.0f, epsAbs16 = 0.0f, epsRel16Hi = 0.0f;
     int residualLo = 0;  // MNENC_MP_LO=1 restores the hi + lo residual split (tighter pre-filter bound, twice the MMAs; measured slower)
-    int mpMode = 3;  // 3 = two-team fp16 tensor-core kernel (default); MNENC_MP=f16 / tf32 / fp32 select the earlier
-                     // kernels (single team / base-only TF32 pre-filter / exact full scan) for A/B validation
+    int mpMode = 4;  // 4 = level-synchronous kernels (mp_wave.cu); MNENC_MP=teams = slot-persistent two-team kernel (mp_kernel_teams.cu)
     // image + symbols
     mnenc::DevBuf rgb, counts, pairs, mpScratch;
+    // level-synchronous matching pursuit (mp_wave.cu): per block-channel state, work lists, (channel, atom) bins
+    mnenc::DevBuf wRes32, wRes16, wState, wGroups, wBest, wAmax, wNcand, wCand, wAct0, wAct1, wBins, wMembers;
+    mnenc::PinBuf hWaveAct;              // active block-channels per iteration, read back while later iterations are queued
+    cudaEvent_t evWave[mnenc::kMaxK] = {};
     size_t lastW = 0, lastH = 0;
     bool haveSymbols = false;
     // back end
@@ -126,6 +129,7 @@ struct mnenc_ctx {
         maxSym, entries, nEntries, entryCodes, codeTable, outWords;
     uint32_t entryCap = 0;
     bool histReady = false;
+    bool histDirty = false;  // the histogram holds counts of an encode that has not reset them yet
     mnenc::PinBuf hTotals, hSeqTable, hEntries, hNEntries, hEntryCodes, hCodeTable, hStats;
     std::unique_ptr<mnenc::HostPool> pool;  // code-table builds of one image run on these threads
     // decoder (decode_api.cu): parsed `lengths` / streams in pinned memory, the stream's quantisers + error flag on the device

@@ -18,11 +18,10 @@ constexpr int kN = 64;        // pixels per 8x8 block (only block_size 8 is supp
 constexpr int kMaxK = 32;     // greedy iterations per block-channel (Compression.cpp:28)
 constexpr int kRowsPad = 512; // base dictionary rows padded (510 real atoms)
 constexpr int kSlots = 32;    // block-channels in flight per CTA of the matching-pursuit kernel
-constexpr int kMpThreads = 512;
 constexpr int kMaxSeq = 6 * kMaxK + 1;  // coded sequences: `lengths` + 6K symbol streams
 
 // ------------------------------------------------------------------------------------------------
-// Matching pursuit kernel parameters (kernel: mp_kernel.cu)
+// Matching pursuit kernel parameters (slot-persistent kernel: mp_kernel_teams.cu)
 // ------------------------------------------------------------------------------------------------
 struct MpParams {
     const uint8_t* rgb;      // device, packed RGB8
@@ -31,14 +30,10 @@ struct MpParams {
     int nbx, nby;            // blocks per row / column; block index = bx*nby + by (column-major walk)
     int K;
     int nBase;               // 510
-    const float* baseT;      // [64][512]  base atoms transposed: baseT[j*512 + atom], zero padded (FP32 kernel)
-    const float* baseUm;     // [512][64] base atoms in the canonical UMMA K-major image (tensor-core kernel)
-    float epsRel;            // pre-filter error bound relative to ||r||_2 (TF32 tensor-core kernel)
     const uint16_t* baseUm16; // [512][64] fp16 base atoms, canonical UMMA K-major image (fp16 tensor-core kernel)
     const uint16_t* detUm16;  // [3][nBase] fp16 images of the detail groups, 64 rows x 64, 8 KB each, zero padded rows
     const float* rows32;      // [512 + 3*nBase*64][64] exact FP32 rows: base atoms, then detail rows (64 per group)
     float epsRel16, epsAbs16; // pre-filter error bound of the fp16 kernel: eps = epsRel16 * ||r||_2 + epsAbs16
-    const float* detT;       // [3][nBase][64][64]: detT[((ch*nBase+atom)*64 + j)*64 + row], zero padded rows
     const uint8_t* detRows;  // [nBase] rows of each detail group (62 or 63)
     const float* quant;      // [3][32]
     uint16_t* counts;        // [nbc] out: atoms per block-channel == the `lengths` stream
@@ -50,17 +45,64 @@ struct MpParams {
     int debugTiming;         // fp16 kernel: CTA 0 prints its per-phase cycle counts (MNENC_MP_TIMING=1)
 };
 
-void buildUmmaImage(const float* baseRowMajor, int nBase, float* image);  // host
 // host: fp16 operand images + exact row table of the fp16 kernel; returns max ||d - fp16(d)||_2 and max ||d||_2 over all atoms
 void buildF16Images(const float* baseRowMajor, int nBase, const int32_t* detailRows, const float* const detail[3], uint16_t* baseUm16,
                     uint16_t* detUm16, float* rows32, double* maxRoundingNorm, double* maxNorm);
 size_t f16Rows32Count(int nBase);
 #ifdef __CUDACC__
-cudaError_t launchMatchingPursuit(const MpParams& p, int numSMs, cudaStream_t stream);
-size_t matchingPursuitSmemBytes();
-cudaError_t launchMatchingPursuitTc(const MpParams& p, int numSMs, cudaStream_t stream);
-cudaError_t launchMatchingPursuitF16(const MpParams& p, int numSMs, cudaStream_t stream);
 cudaError_t launchMatchingPursuitTeams(const MpParams& p, int numSMs, cudaStream_t stream);
+#endif
+
+// ------------------------------------------------------------------------------------------------
+// Level-synchronous matching pursuit (mp_wave.cu): every greedy iteration of ALL active block-channels is one
+// round of kernels, so that dictionary tiles are shared by whole tiles of block-channels instead of being streamed
+// once per block-channel.
+// ------------------------------------------------------------------------------------------------
+constexpr int kCandSlots = 8;            // candidate slots per block-channel and iteration (more: re-scored on the spot)
+constexpr uint32_t kWaveNone = 0xFFFFFFFFu;
+constexpr int kWaveTile = 128;           // block-channels per MMA tile (M of tcgen05.mma)
+#ifdef __CUDACC__
+struct WaveParams {
+    // image
+    const uint8_t* rgb;
+    size_t stride;
+    int width, height, nbx, nby;
+    int K, nBase;
+    // dictionary (device)
+    const uint16_t* baseUm16;  // [512][64] fp16, canonical K-major UMMA image
+    const uint16_t* detUm16;   // [3][nBase] fp16 images of the KLT groups, 8 KB each
+    const float* rows32;       // exact FP32 rows: base atoms, then 64 per group
+    const uint8_t* detRows;    // [nBase] rows per group (62 / 63)
+    const float* quant;        // [3][32]
+    float epsRel16, epsAbs16;
+    // outputs
+    uint16_t* counts;          // [nbc]
+    uint32_t* pairs;           // [nbc][K]; entries >= counts[bc] are not written
+    // per block-channel state
+    float* res32;              // [nbc][64] exact residual
+    uint16_t* res16;           // [nbc][64] residual rounded to fp16 (MMA operand rows, 128 B each)
+    uint4* state;              // {prev | height << 16, reps | ngroups << 8, twoEps bits, 0}
+    uint16_t* groups;          // [nbc][32] base atoms picked so far, pick order (dynamicBasisFast, CompressedImage.cpp:252-289)
+    unsigned long long* best;  // [nbc] exact arg-max key of candidates that found no free slot
+    uint32_t* amax;            // [nbc] max |approximate base score| of the current iteration (float bits)
+    uint32_t* ncand;           // [nbc]
+    uint32_t* cand;            // [nbc][kCandSlots] dictionary index | row id in rows32 << 12
+    // work lists
+    uint32_t* act[2];          // active block-channels of the current / next iteration
+    uint32_t* nAct;            // [K + 1] active block-channels per iteration (zeroed before the launch)
+    uint32_t* binCount;        // [3 * nBase] (channel, atom) bins: groups in use by active block-channels
+    uint32_t* binCursor;       // [3 * nBase]
+    uint32_t* binOffset;       // [3 * nBase + 1] exclusive scan of binCount
+    uint32_t* binTileStart;    // [3 * nBase + 1] exclusive scan of ceil(binCount / 128)
+    uint32_t* members;         // bin member lists: block-channel | group position << 27
+    unsigned long long* stats; // [2]: sum of dictionary heights over all iterations, sum of counts
+    uint32_t nbc;
+};
+size_t waveMembersCapacity(uint32_t nbc, int K);
+cudaError_t launchWaveInit(const WaveParams& p, cudaStream_t st);
+// one greedy iteration of all active block-channels; nActHint >= the number of active block-channels (sizes the grids).
+// Returns the number of kernels launched through *launches.
+cudaError_t launchWaveIteration(const WaveParams& p, int iter, uint32_t nActHint, int numSMs, cudaStream_t st, int* launches);
 #endif
 
 // ------------------------------------------------------------------------------------------------

@@ -283,6 +283,7 @@ int mnenc_stripe_histogram(mnenc_t* c, const uint32_t* all_rec2, void** hist_dev
     b.nEntries = c->nEntries.as<uint32_t>();
     b.entryCap = c->entryCap;
     CU(cudaEventRecord(c->ev[3], st));
+    c->histDirty = true;  // until mnenc_stripe_pack has reset the touched bins
     c->launches += launchHistogramOnly(b, s->M, nSeq, st);
     CU(cudaEventRecord(c->ev[4], st));
     // consistency: the device's stitched RLE size must be what every rank derived from the records
@@ -448,6 +449,7 @@ int mnenc_stripe_pack(mnenc_t* c, const uint64_t* all_seq_bits, void** out_dev, 
     CU(cudaEventRecord(c->ev[5], st));
     c->launches += launchPack(b, s->M, nSeq, st);
     c->launches += launchResetHistogram(b, s->nEntries, st);
+    c->histDirty = false;
     CU(cudaEventRecord(c->ev[6], st));
     CU(waitStream(c));
     *out_dev = c->outWords.p;

@@ -1,7 +1,8 @@
 """Host builds of header-only pieces of the library, run as small native programs (tests/native/*.cpp):
   * csrc/word_acc.h — the per-thread bit accumulator and sequence walk of the MNENC_PACK=2/3 pack kernels — against a bit-by-bit
     MSB-first writer (BitBuffer::WriteBits, BitBuffer.cpp:78-110; writeGolombCode, :228-241) and the slow definition of the walk;
-  * csrc/host_pool.h — exceptions thrown by jobs reach the caller, never std::terminate, the pool stays usable."""
+  * csrc/host_pool.h — exceptions thrown by jobs reach the caller, never std::terminate, the pool stays usable;
+  * csrc/spin_team.h — the decoder's spinning helper team under oversubscription: no index of a job is ever lost."""
 import os
 import shutil
 import subprocess
@@ -26,3 +27,7 @@ def test_word_accumulator_equals_bitwise_writer(tmp_path):
 
 def test_host_pool_survives_throwing_jobs(tmp_path):
     build_and_run(tmp_path, "host_pool_test", ["-pthread"], "host_pool OK")
+
+
+def test_spin_team_oversubscribed(tmp_path):
+    build_and_run(tmp_path, "spin_team_test", ["-pthread"], "spin_team OK")
