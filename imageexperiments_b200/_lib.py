@@ -20,6 +20,8 @@ EXPORTS = (
     "mnenc_debug_plan_sequence", "mnenc_debug_stitch_runs", "mnenc_debug_rle_chunk_size", "mnenc_debug_plan_stripes",
     "mnenc_decode_rgb8", "mnenc_decode_rgb8_device", "mnenc_decode_batch_rgb8", "mnenc_stream_info", "mnenc_debug_parse",
     "mnenc_stripe_begin", "mnenc_stripe_rle", "mnenc_stripe_histogram", "mnenc_stripe_plan", "mnenc_stripe_pack", "mnenc_stripe_finish",
+    "mnenc_comm_unique_id", "mnenc_comm_init_rank", "mnenc_comm_destroy", "mnenc_encode_striped_rgb8", "mnenc_last_stripe_timing",
+    "mnenc_create_multi", "mnenc_last_plan",
 )
 
 
@@ -55,6 +57,7 @@ def load() -> C.CDLL:
     L.mnenc_pack_symbols.argtypes = [_vp, _sz, _sz, _vp, _vp, _vp, _vp]
     L.mnenc_last_timing.argtypes = [_vp, _vp]
     L.mnenc_last_work.argtypes = [_vp, _vp, _vp, _vp]
+    L.mnenc_last_plan.argtypes = [_vp, _vp, _vp, _vp]
     L.mnenc_debug_plan_sequence.argtypes = [_vp, _vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _vp]
     L.mnenc_debug_stitch_runs.argtypes = [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp]
     L.mnenc_debug_rle_chunk_size.argtypes = [C.c_uint32, C.c_uint32, C.c_uint64]
@@ -66,6 +69,12 @@ def load() -> C.CDLL:
     L.mnenc_stripe_plan.argtypes = [_vp, _vp]
     L.mnenc_stripe_pack.argtypes = [_vp, _vp, _vp, _vp, _vp]
     L.mnenc_stripe_finish.argtypes = [_vp, _vp, _vp]
+    L.mnenc_comm_unique_id.argtypes = [_vp]
+    L.mnenc_comm_init_rank.argtypes = [_vp, C.c_int, C.c_int, _vp]
+    L.mnenc_comm_destroy.argtypes = [_vp]
+    L.mnenc_encode_striped_rgb8.argtypes = [_vp, _vp, C.c_int, _sz, _sz, _sz, C.c_uint32, C.c_uint32, _vp, _vp]
+    L.mnenc_last_stripe_timing.argtypes = [_vp, _vp]
+    L.mnenc_create_multi.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp]
     L.mnenc_decode_rgb8.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp]
     L.mnenc_decode_rgb8_device.argtypes = [_vp, _vp, _sz, _vp, _sz, _sz, _vp, _vp]
     L.mnenc_decode_batch_rgb8.argtypes = [_vp, _sz, _vp, _vp, _vp, _vp, _vp]

@@ -35,14 +35,22 @@ def createQuantizationTables(K: int, blockSize: int, bppAllocation: float) -> np
 class CompressionContextFast:
     """compressed::CompressionContextFast (CompressedImage.h:46-55) living on one B200."""
 
-    def __init__(self, K: int, blockSize: int, quant: np.ndarray, dictionary: Dictionary, device: int = 0):
-        self.K, self.BlockSize, self.device = K, blockSize, device
+    def __init__(self, K: int, blockSize: int, quant: np.ndarray, dictionary: Dictionary, device=0):
+        """``device``: a CUDA ordinal, or a list of ordinals for ONE context over several GPUs of this process
+        (mnenc_create_multi): encodeImageFast on it shards every image by block columns over those GPUs."""
+        self.devices = [int(x) for x in device] if isinstance(device, (list, tuple)) else None
+        self.K, self.BlockSize, self.device = K, blockSize, (self.devices[0] if self.devices else int(device))
         self.dictionary = dictionary
         self._h = _vp()
         L = _lib.load()
         d = dictionary
-        _lib.check(L.mnenc_create(C.byref(self._h), device, K, blockSize, _p(d.base), d.n_base, _p(d.detail_rows), _p(d.detail[0]),
-                                  _p(d.detail[1]), _p(d.detail[2])))
+        if self.devices:
+            devs = np.asarray(self.devices, np.int32)
+            _lib.check(L.mnenc_create_multi(C.byref(self._h), _p(devs), len(self.devices), K, blockSize, _p(d.base), d.n_base, _p(d.detail_rows),
+                                            _p(d.detail[0]), _p(d.detail[1]), _p(d.detail[2])))
+        else:
+            _lib.check(L.mnenc_create(C.byref(self._h), self.device, K, blockSize, _p(d.base), d.n_base, _p(d.detail_rows), _p(d.detail[0]),
+                                      _p(d.detail[1]), _p(d.detail[2])))
         self.setQuant(quant)
 
     def setQuant(self, quant) -> None:
@@ -66,6 +74,12 @@ class CompressionContextFast:
         n = _lib.check(_lib.load().mnenc_last_timing(self._h, _p(ms)))
         return ms, n
 
+    def last_plan(self) -> Tuple[int, int, int]:
+        """(sequences written with a Huffman table, as Golomb codes, symbol streams run-length coded) of the last encode."""
+        a, b, c = C.c_int(), C.c_int(), C.c_int()
+        _lib.check(_lib.load().mnenc_last_plan(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
     def last_work(self) -> Tuple[float, int, int]:
         f, s, b = C.c_double(), C.c_uint64(), C.c_uint64()
         _lib.check(_lib.load().mnenc_last_work(self._h, C.byref(f), C.byref(s), C.byref(b)))
@@ -73,7 +87,7 @@ class CompressionContextFast:
 
 
 def createCompressionContextFast(K: int = 32, blockSize: int = 8, bppAllocation: Union[float, str] = 3.5,
-                                 dictionary: Optional[Dictionary] = None, device: int = 0) -> CompressionContextFast:
+                                 dictionary: Optional[Dictionary] = None, device=0) -> CompressionContextFast:
     """compressed::createCompressionContextFast (CompressedImage.cpp:317-341); the dictionary is imported data."""
     if dictionary is None:
         dictionary = Dictionary.load()

@@ -517,6 +517,20 @@ __global__ void __launch_bounds__(256) compactKernel(uint32_t* hist, uint32_t* f
         hist[bin] = 0;
     }
 }
+// Stripe path, sparse histogram exchange: the all-gathered entry lists of every rank ([nranks][nMax], counts[r] valid each) are
+// merged into the dense tables: SUM of the counts, MIN of the (global) first-occurrence positions, MAX of the largest symbol.
+__global__ void mergeEntriesKernel(const HistEntry* gathered, const uint32_t* counts, int nranks, uint32_t nMax, uint32_t* hist,
+                                   uint32_t* firstPos, uint32_t* maxSym) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = blockIdx.y;
+    if (r >= nranks || i >= counts[r]) return;
+    const HistEntry e = gathered[static_cast<size_t>(r) * nMax + i];
+    if (e.seq >= static_cast<uint32_t>(kMaxSeq) || e.symbol >= static_cast<uint32_t>(kHistBins)) return;
+    const size_t bin = static_cast<size_t>(e.seq) * kHistBins + e.symbol;
+    atomicAdd(&hist[bin], e.freq);
+    atomicMin(&firstPos[bin], e.firstPos);
+    atomicMax(&maxSym[e.seq], e.symbol);
+}
 __global__ void resetHistogramKernel(const HistEntry* entries, uint32_t n, uint32_t* firstPos, uint32_t* maxSym, uint32_t* nEntries) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) firstPos[static_cast<size_t>(entries[i].seq) * kHistBins + entries[i].symbol] = kNoPos;
@@ -535,17 +549,6 @@ __device__ __forceinline__ uint32_t golombLength(uint32_t v, uint32_t M) {
     const uint32_t limit = (1u << (b + 1)) - M;
     return rem < limit ? b + q + 1 : b + q + 2;
 }
-__device__ __forceinline__ void orBits(uint32_t* out, unsigned long long pos, uint32_t value, int width) {
-    // width <= 32 bits of `value`, placed MSB-first at absolute bit `pos`
-    if (width == 0) return;
-    const unsigned long long w = pos >> 5;
-    const int off = static_cast<int>(pos & 31);
-    const unsigned long long v = static_cast<unsigned long long>(value) << (64 - off - width);
-    const uint32_t hi = static_cast<uint32_t>(v >> 32), lo = static_cast<uint32_t>(v);
-    if (hi) atomicOr(&out[w], __byte_perm(hi, 0, 0x0123));
-    if (lo) atomicOr(&out[w + 1], __byte_perm(lo, 0, 0x0123));
-}
-
 struct CodeLenIn {
     SeqView v;
     int nSeq;
@@ -568,44 +571,16 @@ struct PackOut {
     const uint32_t* symToEntry;
     const unsigned long long* entryCodes;
     uint32_t* out;
-    __device__ void operator()(uint32_t g, unsigned long long prefix, unsigned long long /*len*/) const {
-        const int q = findSeq(v.table->start, nSeq, g);
-        const SeqDesc d = v.table->desc[q];
-        const uint32_t sym = loadSym(v, d, g - v.table->start[q]);
-        const SeqCode c = codes->seq[q];
-        unsigned long long pos = c.bitBase + prefix;
-        if (c.golombM == 0) {
-            const unsigned long long e = entryCodes[symToEntry[static_cast<size_t>(q) * kHistBins + sym]];
-            orBits(out, pos, static_cast<uint32_t>(e), static_cast<int>(e >> 32));
-        } else {
-            const uint32_t M = c.golombM;
-            uint32_t quo = sym / M;
-            const uint32_t rem = sym - quo * M;
-            while (quo >= 32) {
-                orBits(out, pos, 0xFFFFFFFFu, 32);
-                pos += 32;
-                quo -= 32;
-            }
-            // quo ones then a zero
-            orBits(out, pos, ((1u << quo) - 1u) << 1, static_cast<int>(quo) + 1);
-            pos += quo + 1;
-            const uint32_t b = 32 - __clz(M);
-            const uint32_t limit = (1u << (b + 1)) - M;
-            if (rem < limit) orBits(out, pos, rem, static_cast<int>(b));
-            else orBits(out, pos, rem + limit, static_cast<int>(b) + 1);
-        }
-    }
-    __device__ void total(unsigned long long, uint32_t) const {}
 };
 
-// Variant 2 of the pack scan's apply phase (MNENC_PACK=2; NOT the default: written after the round's last GPU-box minutes,
-// to be verified with `MNENC_PACK=2 python -m pytest tests/test_gpu_parity.py tests/test_gpu_stripes.py` and measured against
-// the default first thing next round). Same positions, same bits; what changes is the traffic to L2:
-//  * a thread's eight consecutive codes are merged in a register (WordAcc, csrc/word_acc.h — the host build of that header
-//    is checked against a bit-by-bit writer by tests/test_native.py) and leave as one atomicOr per output word touched
-//    instead of one or two per code (mean code ≈ 4.6 bits: ≈2.2 atomics per thread instead of ≈9);
+// Pack scan. A thread owns eight consecutive codes:
+//  * they are merged in a register (WordAcc, csrc/word_acc.h — the host build of that header is checked against a bit-by-bit
+//    writer by tests/test_native.py) and leave as one atomicOr per output word touched instead of one or two per code
+//    (mean code ≈ 4.6 bits: ≈2.2 atomics per thread instead of ≈9);
 //  * the sequence of an item is found once per thread (binary search) and then advanced, its descriptor and code plan are
 //    reloaded only when it changes, and the table entry fetched for the length is kept for the emission.
+// Measured on the 16 MP bench image (round 2, B200): 0.122 ms for the generic per-element scan + per-code atomicOr,
+// 0.088 ms with this apply phase alone, 0.072 ms with the reduce phase in the same arrangement — the only variant kept.
 struct OrSink {
     uint32_t* out;
     __device__ __forceinline__ void operator()(unsigned long long w, uint32_t v) const { atomicOr(&out[w], v); }
@@ -640,9 +615,8 @@ __device__ __forceinline__ unsigned long long packThreadCodes(const PackOut& p, 
     }
     return sum;
 }
-// MNENC_PACK=3 adds the reduce phase in the same blocked arrangement (one sequence search per thread instead of one per
-// element; a sum does not care about the arrangement).
-__global__ void __launch_bounds__(kScanThreads) packReduceKernelV2(PackOut p, uint32_t n, unsigned long long* blockSums) {
+// reduce phase in the same blocked arrangement (one sequence search per thread instead of one per element)
+__global__ void __launch_bounds__(kScanThreads) packReduceKernel(PackOut p, uint32_t n, unsigned long long* blockSums) {
     const uint32_t base = blockIdx.x * kScanTile;
     if (base >= n) {
         if (threadIdx.x == 0) blockSums[blockIdx.x] = 0ull;
@@ -655,7 +629,7 @@ __global__ void __launch_bounds__(kScanThreads) packReduceKernelV2(PackOut p, ui
     blockExclusive(sum, &total);
     if (threadIdx.x == 0) blockSums[blockIdx.x] = total;
 }
-__global__ void __launch_bounds__(kScanThreads) packApplyKernelV2(PackOut p, uint32_t n, const unsigned long long* blockSums) {
+__global__ void __launch_bounds__(kScanThreads) packApplyKernel(PackOut p, uint32_t n, const unsigned long long* blockSums) {
     const uint32_t base = blockIdx.x * kScanTile;
     if (base >= n) return;
     const uint32_t first = base + threadIdx.x * kScanItems;
@@ -819,25 +793,20 @@ int launchFillU32(uint32_t* p, size_t n, uint32_t value, cudaStream_t st) {
 }
 
 int launchPack(const BackendBuffers& b, uint32_t M, int nSeq, cudaStream_t st) {
+    if (!M) return 0;
     SeqView v{b.seqTable, b.counts, b.arena, b.rleArena};
-    static const int variant = [] {
-        const char* e = std::getenv("MNENC_PACK");
-        return e ? std::atoi(e) : 1;
-    }();
-    if ((variant == 2 || variant == 3) && M) {
-        const uint32_t nTiles = (M + kScanTile - 1) / kScanTile;
-        const PackOut out{v, nSeq, b.codeTable, b.firstPos, b.entryCodes, b.outWords};
-        if (variant == 3)
-            packReduceKernelV2<<<nTiles, kScanThreads, 0, st>>>(out, M, b.blockSums64);
-        else
-            scanReduceKernel<unsigned long long, CodeLenIn><<<nTiles, kScanThreads, 0, st>>>(CodeLenIn{v, nSeq, b.codeTable, b.firstPos, b.entryCodes}, M,
-                                                                                              nullptr, b.blockSums64);
-        scanBlockSumsKernel<unsigned long long><<<1, 1024, 0, st>>>(b.blockSums64, nTiles);
-        packApplyKernelV2<<<nTiles, kScanThreads, 0, st>>>(out, M, b.blockSums64);
-        return 3;
-    }
-    return deviceScan<unsigned long long>(CodeLenIn{v, nSeq, b.codeTable, b.firstPos, b.entryCodes},
-                                          PackOut{v, nSeq, b.codeTable, b.firstPos, b.entryCodes, b.outWords}, M, nullptr, b.blockSums64, st);
+    const uint32_t nTiles = (M + kScanTile - 1) / kScanTile;
+    const PackOut out{v, nSeq, b.codeTable, b.firstPos, b.entryCodes, b.outWords};
+    packReduceKernel<<<nTiles, kScanThreads, 0, st>>>(out, M, b.blockSums64);
+    scanBlockSumsKernel<unsigned long long><<<1, 1024, 0, st>>>(b.blockSums64, nTiles);
+    packApplyKernel<<<nTiles, kScanThreads, 0, st>>>(out, M, b.blockSums64);
+    return 3;
+}
+
+int launchMergeEntries(const BackendBuffers& b, const HistEntry* gathered, const uint32_t* counts, int nranks, uint32_t nMax, cudaStream_t st) {
+    if (!nMax) return 0;
+    mergeEntriesKernel<<<dim3((nMax + 255) / 256, static_cast<unsigned>(nranks)), 256, 0, st>>>(gathered, counts, nranks, nMax, b.hist, b.firstPos, b.maxSym);
+    return 1;
 }
 
 int launchResetHistogram(const BackendBuffers& b, uint32_t nEntries, cudaStream_t st) {

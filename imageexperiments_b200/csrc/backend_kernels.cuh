@@ -121,5 +121,6 @@ int launchDecide(const BackendBuffers& b, const StreamOffsets& so, SeqTable* hos
 int launchHistogram(const BackendBuffers& b, uint32_t upperBoundM, int nSeq, cudaStream_t st);
 int launchPack(const BackendBuffers& b, uint32_t M, int nSeq, cudaStream_t st);
 int launchResetHistogram(const BackendBuffers& b, uint32_t nEntries, cudaStream_t st);
+int launchMergeEntries(const BackendBuffers& b, const HistEntry* gathered, const uint32_t* counts, int nranks, uint32_t nMax, cudaStream_t st);
 
 }  // namespace mnenc

@@ -1,6 +1,6 @@
 // Device side of the decoder: symbol streams -> pixels. Replaces the block loop of
 //   compressed::decodeImageFast        CompressionLib/src/CompressedImage.cpp:837-889
-//   matching::FromCoeffsDynamicFast    CompressionLib/src/MatchingPursuit.cpp:152-169
+//   matching::FromCoeffsDynamicFast    CompressionLib/src/MatchingPursuit.cpp:130-147
 //   dynamicBasisFast (row lookup only) CompressionLib/src/CompressedImage.cpp:252-289
 //   img::RGBFromYUV                    ImageHelper/src/misc.cpp:28-36
 //
@@ -66,83 +66,11 @@ __device__ __forceinline__ uint8_t toByte(double v) {  // static_cast<uchar>(std
 constexpr int kBlocksPerCta = 4;  // 64 threads (one per pixel) per image block
 
 // One image block per 64 threads: thread j = dx + 8 * dy rebuilds pixel j of the three channels and converts it.
+// Lane i resolves the row pointer and coefficient of pick i (the walks over the block's picks run in parallel instead of one
+// after the other on every lane), then the rows are loaded four picks at a time before the ordered adds, so four L2 round
+// trips overlap instead of one per pick; the arithmetic and its order are FromCoeffsDynamicFast's (MatchingPursuit.cpp:130-147).
+// (Round 2, B200, 16 MP: 0.568 ms for gather + reconstruct against 0.602 ms with one dependent walk per pick.)
 __global__ void __launch_bounds__(64 * kBlocksPerCta) reconstructKernel(const DecodeParams p) {
-    __shared__ int absIdx[2 * kBlocksPerCta][kMaxK];  // per warp: absolute atom index of each pick of the current block-channel
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int j = threadIdx.x & 63;
-    const int dx = j & 7, dy = j >> 3;
-    const uint32_t ngroups = (p.nblocks + kBlocksPerCta - 1) / kBlocksPerCta;
-    for (uint32_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
-        const uint32_t blk = g * kBlocksPerCta + (threadIdx.x >> 6);
-        if (blk >= p.nblocks) continue;  // whole warps leave together (64 threads per block)
-        float yuv[3];
-#pragma unroll
-        for (int ch = 0; ch < 3; ++ch) {
-            const int count = p.counts[3 * blk + ch];
-            const uint32_t* pp = p.pairs + (static_cast<size_t>(3) * blk + ch) * p.K;
-            const float* quant = p.quant + ch * p.K;
-            float r = 0.0f;
-            // absolute atom indices: running sum of the zig-zag decoded deltaIds (MatchingPursuit.cpp:160-164), one pick per lane
-            __syncwarp();
-            int v = 0;
-            if (lane < count) {
-                const uint32_t id = __ldg(pp + lane) & 0xFFFFu;
-                v = lane ? unzigzag(id) : static_cast<int>(id);
-            }
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const int up = __shfl_up_sync(kFull, v, off);
-                if (lane >= off) v += up;
-            }
-            absIdx[warp][lane] = v;
-            __syncwarp();
-            for (int i = 0; i < count; ++i) {
-                const int choice = absIdx[warp][i];
-                const float coeff = __fmul_rn(__ldg(quant + i), static_cast<float>(unzigzag(__ldg(pp + i) >> 16)));  // :165
-                // row of the dictionary dynamicBasisFast builds from all `count` picks: base atoms, then the detail group of
-                // every pick below nBase, in pick order (CompressedImage.cpp:258-288)
-                const float* row = nullptr;
-                if (choice >= 0 && choice < p.nBase) {
-                    row = p.rows32 + static_cast<size_t>(choice) * kN;
-                } else if (choice >= p.nBase) {
-                    int off = choice - p.nBase;
-                    for (int e = 0; e < count; ++e) {
-                        const int c = absIdx[warp][e];
-                        if (c < 0 || c >= p.nBase) continue;
-                        const int rows = p.detRows[c];
-                        if (off < rows) {
-                            row = p.rows32 + (static_cast<size_t>(kRowsPad) + (static_cast<size_t>(ch) * p.nBase + c) * 64 + off) * kN;
-                            break;
-                        }
-                        off -= rows;
-                    }
-                }
-                if (row == nullptr) {  // index outside the block's dictionary: damaged stream (the reference reads out of range)
-                    if (j == 0) atomicExch(p.error, 1u);
-                    continue;
-                }
-                r = __fadd_rn(r, __fmul_rn(coeff, __ldg(row + j)));  // results += coeff * dictionary.row(choice), unfused, :166
-            }
-            yuv[ch] = r;
-        }
-        const uint32_t bx = blk / p.nby, by = blk - bx * p.nby;  // column-major block walk, CompressedImage.cpp:851-853
-        const uint32_t x = bx * 8 + dx, y = by * 8 + dy;
-        if (x < p.width && y < p.height) {
-            const double Y = yuv[0], U = yuv[1], V = yuv[2];
-            uint8_t* px = p.rgb + static_cast<size_t>(y) * p.stride + 3 * static_cast<size_t>(x);
-            px[0] = toByte(__dadd_rn(Y, __dmul_rn(1.13983, V)));
-            px[1] = toByte(__dsub_rn(__dsub_rn(Y, __dmul_rn(0.39466, U)), __dmul_rn(0.58060, V)));
-            px[2] = toByte(__dadd_rn(Y, __dmul_rn(2.03211, U)));
-        }
-    }
-}
-
-// Variant 2 (MNENC_RECON=2; NOT the default: written after the round's last GPU-box minutes, to be verified and measured
-// first thing next round with `MNENC_RECON=2 python -m pytest tests/test_gpu_decode.py`). Same arithmetic in the same order;
-// what changes is the dependency structure: lane i resolves the row pointer and coefficient of pick i (the walks over
-// the block's picks run in parallel instead of one after the other on every lane), then the rows are loaded four picks at a
-// time before the ordered adds, so four L2 round trips overlap instead of one per pick.
-__global__ void __launch_bounds__(64 * kBlocksPerCta) reconstructKernelV2(const DecodeParams p) {
     __shared__ int absIdx[2 * kBlocksPerCta][kMaxK];
     __shared__ const float* rowPtr[2 * kBlocksPerCta][kMaxK];
     __shared__ float coef[2 * kBlocksPerCta][kMaxK];
@@ -228,14 +156,7 @@ int launchGather(const BackendBuffers& b, const StreamOffsets& so, uint32_t* pai
 int launchReconstruct(const DecodeParams& p, int numSMs, cudaStream_t st) {
     const uint32_t ngroups = (p.nblocks + kBlocksPerCta - 1) / kBlocksPerCta;
     const uint32_t grid = std::min<uint32_t>(ngroups, static_cast<uint32_t>(numSMs) * 8u);  // 8 x 256 threads fill an SM
-    static const int variant = [] {
-        const char* e = std::getenv("MNENC_RECON");
-        return e ? std::atoi(e) : 1;
-    }();
-    if (variant == 2)
-        reconstructKernelV2<<<grid, 64 * kBlocksPerCta, 0, st>>>(p);
-    else
-        reconstructKernel<<<grid, 64 * kBlocksPerCta, 0, st>>>(p);
+    reconstructKernel<<<grid, 64 * kBlocksPerCta, 0, st>>>(p);
     return 1;
 }
 

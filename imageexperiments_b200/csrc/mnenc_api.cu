@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
@@ -343,6 +344,11 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
             for (size_t k = 0; k < entryOf[q].size(); ++k) hCodes[entryOf[q][k]] = 0;
         }
     }
+    c->planHuffman = c->planGolomb = c->planRle = 0;
+    for (int q = 0; q < nSeq; ++q) {
+        (plans[q].golomb ? c->planGolomb : c->planHuffman) += 1;
+        if (q > 0 && seq.desc[q].src == 2) c->planRle += 1;
+    }
     const uint64_t totalBits = cursor;
     const size_t totalBytes = static_cast<size_t>((totalBits + 7) / 8);
     const uint32_t M = seq.start[nSeq];
@@ -407,10 +413,15 @@ static int runWavePursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, siz
     CU(c->wAmax.ensure(n * 4));
     CU(c->wNcand.ensure(n * 4));
     CU(c->wCand.ensure(n * kCandSlots * 4));
+    CU(c->wNcandDetail.ensure(n * 4));
+    CU(c->wCandDetail.ensure(n * kCandSlotsDetail * 4));
     CU(c->wAct0.ensure(n * 4));
     CU(c->wAct1.ensure(n * 4));
     CU(c->wMembers.ensure(waveMembersCapacity(nbc, K) * 4));
-    const size_t binWords = static_cast<size_t>(4 * nbins + 2), headWords = kMaxK + 2;  // nAct[K + 1] | binCount | binCursor | binOffset | binTileStart
+    CU(c->wMemberInfo.ensure(waveMembersCapacity(nbc, K) * 8));
+    const uint32_t ovfCap = nbc / 2 + 65536;
+    CU(c->wOvf.ensure(static_cast<size_t>(ovfCap) * 8));
+    const size_t binWords = static_cast<size_t>(4 * nbins + 2), headWords = kMaxK + 4;  // nAct[K + 1] | overflow count | binCount | binCursor | binOffset | binTileStart
     CU(c->wBins.ensure((headWords + binWords) * 4));
     CU(c->hWaveAct.ensure((kMaxK + 2) * 4));
     CU(cudaMemsetAsync(c->wBins.p, 0, (headWords + binWords) * 4, c->stream));
@@ -440,10 +451,16 @@ static int runWavePursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, siz
     p.amax = c->wAmax.as<uint32_t>();
     p.ncand = c->wNcand.as<uint32_t>();
     p.cand = c->wCand.as<uint32_t>();
+    p.ncandDetail = c->wNcandDetail.as<uint32_t>();
+    p.candDetail = c->wCandDetail.as<uint32_t>();
     p.act[0] = c->wAct0.as<uint32_t>();
     p.act[1] = c->wAct1.as<uint32_t>();
     uint32_t* words = c->wBins.as<uint32_t>();
     p.nAct = words;
+    p.ovfCount = words + kMaxK + 2;
+    p.ovf = c->wOvf.as<uint2>();
+    p.ovfCap = ovfCap;
+    p.memberInfo = c->wMemberInfo.as<uint2>();
     p.binCount = words + headWords;
     p.binCursor = p.binCount + nbins;
     p.binOffset = p.binCursor + nbins;
@@ -456,15 +473,22 @@ static int runWavePursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, siz
     uint32_t* hAct = c->hWaveAct.as<uint32_t>();
     CU(cudaMemcpyAsync(hAct, p.nAct, 4, cudaMemcpyDeviceToHost, c->stream));
     uint32_t hint = nbc;
+    static const bool trace = std::getenv("MNENC_WAVE_TRACE") != nullptr;  // host clock per round (development aid)
+    const double tTrace = nowMs();
     for (int r = 0; r < K; ++r) {
+        double tWait = 0;
         if (r >= kWaveLookahead) {  // round r - kWaveLookahead has finished or is about to: its survivor count bounds this round's work
+            const double t0 = nowMs();
             CU(cudaEventSynchronize(c->evWave[r - kWaveLookahead]));
+            tWait = nowMs() - t0;
             hint = hAct[r - kWaveLookahead + 1];
             if (hint == 0) break;
         }
+        const double t1 = nowMs();
         CU(launchWaveIteration(p, r, hint, c->numSMs, c->stream, &c->launches));
         CU(cudaMemcpyAsync(hAct + r + 1, p.nAct + r + 1, 4, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaEventRecord(c->evWave[r], c->stream));
+        if (trace) std::fprintf(stderr, "wave round %d: at %.3f ms, waited %.3f ms, enqueue %.3f ms, hint %u\n", r, t1 - tTrace, tWait, nowMs() - t1, hint);
     }
     return MNENC_OK;
 }
@@ -510,7 +534,7 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
         c->launches += nbc ? 1 : 0;
     }
     CU(cudaEventRecord(c->ev[1], c->stream));
-    CU(cudaMemcpyAsync(c->hStats.p, c->mpScratch.as<unsigned char>() + 16, 16, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->hStats.p, c->mpScratch.as<unsigned char>() + 16, 48, cudaMemcpyDeviceToHost, c->stream));
     c->lastW = width;
     c->lastH = height;
     c->haveSymbols = true;
@@ -524,6 +548,8 @@ void finishMpAccounting(mnenc_ctx* c) {
     const unsigned long long* s = c->hStats.as<unsigned long long>();
     // F = sum over iterations of 2*64*D_r  +  2*64*count   
     c->mpFlops = 2.0 * kN * static_cast<double>(s[0]) + 2.0 * kN * static_cast<double>(s[1]);
+    if (std::getenv("MNENC_WAVE_TRACE"))
+        std::fprintf(stderr, "wave candidates: base %llu (no slot: %llu), groups %llu; block-channel iterations %llu\n", s[2], s[3], s[4], s[1]);
 }
 
 int checkEncodeArgs(mnenc_ctx* c, const void* rgb, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes) {
@@ -635,6 +661,8 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
 
 void mnenc_destroy(mnenc_t* c) {
     if (!c) return;
+    for (mnenc_ctx* peer : c->groupPeers) mnenc_destroy(peer);
+    c->groupPeers.clear();
     for (mnenc_ctx* lane : c->lanes) mnenc_destroy(lane);
     c->lanes.clear();
     cudaSetDevice(c->device);
@@ -659,6 +687,8 @@ int mnenc_set_quant(mnenc_t* c, const float* q) try {
     CU(cudaMemcpyAsync(c->quant.p, c->hQuant, sizeof(c->hQuant), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->quantSet = true;
+    for (mnenc_ctx* peer : c->groupPeers)
+        if (int rc = mnenc_set_quant(peer, q)) return rc;
     return MNENC_OK;
 } catch (...) {
     return mnenc::abiCaught();
@@ -686,6 +716,7 @@ int mnenc_encode_rgb8_device(mnenc_t* c, const uint8_t* rgb_dev, size_t w, size_
 
 int mnenc_encode_rgb8(mnenc_t* c, const uint8_t* rgb, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes) try {
     if (int rc = checkEncodeArgs(c, rgb, w, h, stride, out, outBytes)) return rc;
+    if (!c->groupPeers.empty()) return encodeGroup(c, rgb, w, h, stride, out, outBytes);  // mnenc_create_multi: block-column stripes over the GPUs
     CU(cudaSetDevice(c->device));
     const double t0 = nowMs();
     c->launches = 0;
@@ -754,6 +785,16 @@ int mnenc_last_work(mnenc_t* c, double* mp_flops, uint64_t* n_symbols, uint64_t*
     if (mp_flops) *mp_flops = c->mpFlops;
     if (n_symbols) *n_symbols = c->nSymbols;
     if (n_bits) *n_bits = c->nBits;
+    return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
+}
+
+int mnenc_last_plan(mnenc_t* c, int* n_huffman, int* n_golomb, int* n_rle) try {
+    if (!c) return fail(MNENC_ERR_ARG, "null argument");
+    if (n_huffman) *n_huffman = c->planHuffman;
+    if (n_golomb) *n_golomb = c->planGolomb;
+    if (n_rle) *n_rle = c->planRle;
     return MNENC_OK;
 } catch (...) {
     return mnenc::abiCaught();

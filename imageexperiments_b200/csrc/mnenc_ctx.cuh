@@ -101,6 +101,9 @@ void resultRelease(uint8_t* p);        // pool buffer -> back to the pool; anyth
 
 // State of one image sharded over ranks (stripe_api.cu), between the phases of the stripe protocol.
 struct StripeState;
+// NCCL communicator + staging buffers of the in-library stripe exchanges (stripe_comm.cu).
+struct StripeComm;
+void destroyStripeComm(StripeComm* sc);
 
 }  // namespace mnenc
 
@@ -119,7 +122,7 @@ struct mnenc_ctx {
     // image + symbols
     mnenc::DevBuf rgb, counts, pairs, mpScratch;
     // level-synchronous matching pursuit (mp_wave.cu): per block-channel state, work lists, (channel, atom) bins
-    mnenc::DevBuf wRes32, wRes16, wState, wGroups, wBest, wAmax, wNcand, wCand, wAct0, wAct1, wBins, wMembers;
+    mnenc::DevBuf wRes32, wRes16, wState, wGroups, wBest, wAmax, wNcand, wCand, wNcandDetail, wCandDetail, wAct0, wAct1, wBins, wMembers, wMemberInfo, wOvf;
     mnenc::PinBuf hWaveAct;              // active block-channels per iteration, read back while later iterations are queued
     cudaEvent_t evWave[mnenc::kMaxK] = {};
     size_t lastW = 0, lastH = 0;
@@ -140,8 +143,11 @@ struct mnenc_ctx {
     int launches = 0;
     double mpFlops = 0;
     uint64_t nSymbols = 0, nBits = 0;
+    int planHuffman = 0, planGolomb = 0, planRle = 0;  // coded sequences by mode, symbol streams that were run-length coded
     // stripe protocol
     std::unique_ptr<mnenc::StripeState, void (*)(mnenc::StripeState*)> stripe{nullptr, nullptr};
+    std::unique_ptr<mnenc::StripeComm, void (*)(mnenc::StripeComm*)> comm{nullptr, mnenc::destroyStripeComm};
+    std::vector<mnenc_ctx*> groupPeers;  // mnenc_create_multi: the contexts of the other GPUs (this one is rank 0)
     // batch mode (batch_api.cu): extra lanes = contexts with their own stream and buffers that alias this dictionary
     std::vector<mnenc_ctx*> lanes;
     int hostThreads = 1;
@@ -167,4 +173,10 @@ int ensureHistogram(mnenc_ctx* c);
 int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride);
 void finishMpAccounting(mnenc_ctx* c);
 int checkEncodeArgs(mnenc_ctx* c, const void* rgb, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes);
+// stripe_comm.cu / stripe_api.cu: exchanges of the stripe protocol inside the library
+int stripeExchangeHistogram(mnenc_ctx* c);
+int exchangeHistogramSparse(mnenc_ctx* c, BackendBuffers& b, int nSeq);
+int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats, std::vector<SequencePlan>& plans);
+int stripeRanks(const mnenc_ctx* c);  // ranks of the context's communicator (1 without one)
+int encodeGroup(mnenc_ctx* c, const uint8_t* rgb, size_t width, size_t height, size_t stride, uint8_t** out, size_t* outBytes);
 }  // namespace mnenc

@@ -58,7 +58,9 @@ cudaError_t launchMatchingPursuitTeams(const MpParams& p, int numSMs, cudaStream
 // round of kernels, so that dictionary tiles are shared by whole tiles of block-channels instead of being streamed
 // once per block-channel.
 // ------------------------------------------------------------------------------------------------
-constexpr int kCandSlots = 8;            // candidate slots per block-channel and iteration (more: re-scored on the spot)
+constexpr int kCandPerQuarter = 4;       // base-atom candidate slots per 128-atom quarter of the base scan
+constexpr int kCandSlots = 4 * kCandPerQuarter;
+constexpr int kCandSlotsDetail = 4;      // candidate slots for rows of the appended KLT groups
 constexpr uint32_t kWaveNone = 0xFFFFFFFFu;
 constexpr int kWaveTile = 128;           // block-channels per MMA tile (M of tcgen05.mma)
 #ifdef __CUDACC__
@@ -84,9 +86,15 @@ struct WaveParams {
     uint4* state;              // {prev | height << 16, reps | ngroups << 8, twoEps bits, 0}
     uint16_t* groups;          // [nbc][32] base atoms picked so far, pick order (dynamicBasisFast, CompressedImage.cpp:252-289)
     unsigned long long* best;  // [nbc] exact arg-max key of candidates that found no free slot
-    uint32_t* amax;            // [nbc] max |approximate base score| of the current iteration (float bits)
-    uint32_t* ncand;           // [nbc]
+    uint32_t* amax;            // [nbc] max |approximate base score| of the current iteration (float bits; atomicMax by the two
+                               // scanning threads of a block-channel, reset by the decide pass)
+    uint32_t* ncand;           // [nbc] four bytes: candidates in each quarter's sub-list (rewritten by every base pass)
     uint32_t* cand;            // [nbc][kCandSlots] dictionary index | row id in rows32 << 12
+    uint32_t* ncandDetail;     // [nbc] candidates among the rows of the appended groups (reset by the decide pass)
+    uint32_t* candDetail;      // [nbc][kCandSlotsDetail]
+    uint32_t* ovfCount;        // candidates that found no slot: queue re-scored by waveOverflowKernel (reset by the decide pass)
+    uint2* ovf;                // [ovfCap] {block-channel, dictionary index | row id << 12}
+    uint32_t ovfCap;
     // work lists
     uint32_t* act[2];          // active block-channels of the current / next iteration
     uint32_t* nAct;            // [K + 1] active block-channels per iteration (zeroed before the launch)
@@ -95,6 +103,8 @@ struct WaveParams {
     uint32_t* binOffset;       // [3 * nBase + 1] exclusive scan of binCount
     uint32_t* binTileStart;    // [3 * nBase + 1] exclusive scan of ceil(binCount / 128)
     uint32_t* members;         // bin member lists: block-channel | group position << 27
+    uint2* memberInfo;         // per member: {dictionary index of the group's row 0 | fp16(2 eps, rounded up) << 16,
+                               //              float bits of (max |base score| - 2 eps)}
     unsigned long long* stats; // [2]: sum of dictionary heights over all iterations, sum of counts
     uint32_t nbc;
 };

@@ -7,8 +7,8 @@
 //                      A = 128 residual rows (fp16), B = the base dictionary image (N = 256 per pass), D in TMEM with the
 //                      block-channel on the TMEM lane, so a block-channel's 512 scores belong to ONE thread: maximum and
 //                      the 2-eps candidate filter are thread-local loops, no cross-lane reduction
-//   waveBinKernel x2   the KLT groups appended so far, as (block-channel, group) items sorted by (channel, atom): counting
-//   waveScanKernel     sort = count, scan, fill
+//   waveScanKernel     the KLT groups appended so far, as (block-channel, group) items sorted by (channel, atom): counting
+//   waveBinFillKernel  sort = count (by the previous decide pass), scan, fill
 //   waveDetailKernel   per (channel, atom) bin, tiles of 128 member block-channels against the bin's 64-row group image:
 //                      the group is loaded ONCE per tile instead of once per block-channel (the streamed-group traffic of
 //                      the slot-persistent kernel was 18.7 GB per 16 MP image)
@@ -41,16 +41,32 @@ __host__ __device__ constexpr uint32_t idescF16(uint32_t M, uint32_t N) { return
 
 __device__ __forceinline__ float twoEpsOf(const WaveParams& p, float ss) { return 2.0f * (p.epsRel16 * sqrtf(ss) * 1.0001f + p.epsAbs16); }
 
-// Candidate -> a free slot of its block-channel, or (rare: near-tie floods) re-scored on the spot.
-__device__ __noinline__ void pushCandidate(const WaveParams& p, uint32_t bc, uint32_t idx, uint32_t rowId) {
-    const uint32_t pos = atomicAdd(&p.ncand[bc], 1u);
-    if (pos < static_cast<uint32_t>(kCandSlots)) {
-        p.cand[static_cast<size_t>(bc) * kCandSlots + pos] = idx | (rowId << 12);
-    } else {
-        const float a = exactDot(p.rows32 + static_cast<size_t>(rowId) * kN, p.res32 + static_cast<size_t>(bc) * kN);
-        atomicMax(&p.best[bc], makeKey(a, static_cast<int>(idx)));
+// A candidate that found no free slot (near-tie floods: ~1 % of the block-channel iterations) goes to a queue that
+// waveOverflowKernel re-scores before the decide pass: the scanning warps never wait for a dependent chain of loads.
+__device__ __noinline__ void queueOverflow(const WaveParams& p, uint32_t bc, uint32_t code) {
+    const uint32_t pos = atomicAdd(p.ovfCount, 1u);
+    if (pos < p.ovfCap) {
+        p.ovf[pos] = make_uint2(bc, code);
+    } else {  // queue full: re-score on the spot
+        const float a = exactDot(p.rows32 + static_cast<size_t>(code >> 12) * kN, p.res32 + static_cast<size_t>(bc) * kN);
+        atomicMax(&p.best[bc], makeKey(a, static_cast<int>(code & 0xFFFu)));
     }
 }
+// Thread-local candidate collector: the scan loops only fill registers (no memory round trip, no divergent atomics); the
+// candidates leave the thread in one convergent step after the loop.
+struct CandLocal {
+    uint32_t c[kCandPerQuarter];
+    int n = 0;
+    __device__ __forceinline__ void add(const WaveParams& p, uint32_t bc, uint32_t idx, uint32_t rowId) {
+        const uint32_t code = idx | (rowId << 12);
+        if (n == 0) c[0] = code;
+        else if (n == 1) c[1] = code;
+        else if (n == 2) c[2] = code;
+        else if (n == 3) c[3] = code;
+        else queueOverflow(p, bc, code);
+        ++n;
+    }
+};
 
 // ------------------------------------------------------------------------------------------------
 // Block gather + YUVFromRGB (CompressedImage.cpp:595-611, misc.cpp:12-21): 8 threads per image block, thread l8 owns
@@ -117,7 +133,8 @@ __global__ void __launch_bounds__(256) waveInitKernel(const __grid_constant__ Wa
         }
         if (l8 == 0) {
             p.best[bc] = 0ULL;
-            p.ncand[bc] = 0u;
+            p.ncandDetail[bc] = 0u;
+            p.amax[bc] = 0u;
             if (nonZero) {
                 p.state[bc] = make_uint4(static_cast<uint32_t>(p.nBase) << 16, 0u, __float_as_uint(twoEpsOf(p, ss)), 0u);
                 rank[ch] = atomicAdd(&sCount, 1u);
@@ -141,37 +158,25 @@ __global__ void __launch_bounds__(256) waveInitKernel(const __grid_constant__ Wa
 }
 
 // ------------------------------------------------------------------------------------------------
-// Base scores. 256 threads, 2 CTAs per SM (256 TMEM columns each).
+// Base scores. 288 threads: two groups of four scanning warps + one MMA-issuing warp; 2 CTAs per SM (256 TMEM columns each).
+// The 512 dictionary rows are scored in four quarters of 128 atoms (N = 128 per tcgen05.mma) that ping-pong between two
+// 128-column TMEM buffers: while group A (warps 0-3) scans quarter 0 in buffer 0, the tensor core fills buffer 1 with quarter
+// 1 for group B (warps 4-7), and so on. A thread owns ONE block-channel (TMEM lane) for a whole quarter: maximum, threshold
+// and candidate filter are thread-local, and nothing in the tile loop is a CTA-wide barrier - only mbarriers between the MMA
+// warp and a scanning group. The residual rows of the NEXT tile are fetched into registers between the two quarters of a
+// group and stored to the other operand buffer after the second, so their latency hides behind the scans.
 // ------------------------------------------------------------------------------------------------
+constexpr int kBaseThreads = 288;
 struct __align__(1024) BaseSmem {
-    __half D16[kRowsPad * kN];                 // 64 KB base dictionary image (B operand)
-    alignas(1024) __half A[kWaveTile * kN];    // 16 KB residual tile (A operand), canonical K-major image
-    uint32_t bc[kWaveTile];
-    float eps[kWaveTile];
-    float halfMax[2][kWaveTile];
-    unsigned long long mbarDict, mbarMma;
+    __half D16[kRowsPad * kN];                    // 64 KB base dictionary image (B operand)
+    alignas(1024) __half A[2][kWaveTile * kN];    // 2 x 16 KB residual tiles (A operand), canonical K-major images
+    uint32_t bc[2][kWaveTile];
+    float eps[2][kWaveTile];
+    unsigned long long mbarDict, aFull[2], bufFull[2], bufFree[2];
     uint32_t tmemBase;
 };
 
-// rows of res16 (128 B each) -> canonical K-major operand image; item = (row, pair of 16-byte chunks)
-__device__ __forceinline__ void gatherRows(const uint16_t* res16, const uint32_t* sBc, __half* A, int tid, int nthreads) {
-    unsigned char* dst = reinterpret_cast<unsigned char*>(A);
-    for (int it = tid; it < kWaveTile * 4; it += nthreads) {
-        const int row = it & (kWaveTile - 1), pair = it >> 7;
-        const uint32_t bc = sBc[row];
-        uint4 v0 = make_uint4(0u, 0u, 0u, 0u), v1 = v0;
-        if (bc != kWaveNone) {
-            const uint4* src = reinterpret_cast<const uint4*>(res16 + static_cast<size_t>(bc) * kN) + 2 * pair;
-            v0 = __ldg(src);
-            v1 = __ldg(src + 1);
-        }
-        unsigned char* d = dst + (row >> 3) * kSbo + (2 * pair) * kLbo + (row & 7) * 16;
-        *reinterpret_cast<uint4*>(d) = v0;
-        *reinterpret_cast<uint4*>(d + kLbo) = v1;
-    }
-}
-
-__global__ void __launch_bounds__(256, 2) waveBaseKernel(const __grid_constant__ WaveParams p, const int iter) {
+__global__ void __launch_bounds__(kBaseThreads, 2) waveBaseKernel(const __grid_constant__ WaveParams p, const int iter) {
     extern __shared__ __align__(1024) unsigned char smemRaw[];
     BaseSmem& s = *reinterpret_cast<BaseSmem*>(smemRaw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -179,10 +184,15 @@ __global__ void __launch_bounds__(256, 2) waveBaseKernel(const __grid_constant__
     const uint32_t ntiles = (nA + kWaveTile - 1) / kWaveTile;
     if (blockIdx.x >= ntiles) return;
     const uint32_t* act = p.act[iter & 1];
+    const uint32_t nMine = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;  // tiles blockIdx.x, + gridDim.x, ...
 
     if (tid == 0) {
         mbarInit(&s.mbarDict, 1);
-        mbarInit(&s.mbarMma, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbarInit(&s.aFull[i], 8);     // one arrival per scanning warp
+            mbarInit(&s.bufFull[i], 1);   // tcgen05.commit
+            mbarInit(&s.bufFree[i], 4);   // one arrival per warp of the group that read the buffer
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -193,85 +203,137 @@ __global__ void __launch_bounds__(256, 2) waveBaseKernel(const __grid_constant__
     __syncthreads();
     fenceAfter();
     const uint32_t tmem = s.tmemBase;
-    if (tid == 0) {
-        constexpr uint32_t total = kRowsPad * kN * sizeof(__half);
-        mbarExpectTx(&s.mbarDict, total);
-        for (uint32_t o = 0; o < total; o += 32768)
-            bulkCopy(reinterpret_cast<unsigned char*>(s.D16) + o, reinterpret_cast<const unsigned char*>(p.baseUm16) + o, 32768, &s.mbarDict);
-    }
-    bool dictReady = false;
-    uint32_t mmaPhase = 0;
-    const int q = warp & 3, h = warp >> 2;
-    const int slot = q * 32 + lane;
-    const uint32_t laneBase = static_cast<uint32_t>(q * 32) << 16;
 
-    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        if (tid < kWaveTile) {
-            const uint32_t e = tile * kWaveTile + tid;
-            const uint32_t bc = e < nA ? act[e] : kWaveNone;
-            s.bc[tid] = bc;
-            s.eps[tid] = bc != kWaveNone ? __uint_as_float(p.state[bc].z) : 0.0f;
+    if (warp == 8) {
+        // ================= MMA issuer: the whole warp runs the issue path with warp-uniform operands, one elected lane issues =====
+        if (lane == 0) {
+            constexpr uint32_t total = kRowsPad * kN * sizeof(__half);
+            mbarExpectTx(&s.mbarDict, total);
+            for (uint32_t o = 0; o < total; o += 32768)
+                bulkCopy(reinterpret_cast<unsigned char*>(s.D16) + o, reinterpret_cast<const unsigned char*>(p.baseUm16) + o, 32768, &s.mbarDict);
         }
-        __syncthreads();
-        gatherRows(p.res16, s.bc, s.A, tid, 256);
-        fenceProxyAsync();
-        __syncthreads();
-        const uint32_t myBc = s.bc[slot];
-        float mrun = 0.0f;
+        __syncwarp();
+        mbarWait(&s.mbarDict, 0);
+        const uint32_t dAddr = warpUniform(smemAddr(s.D16));
+        const uint32_t tm = warpUniform(tmem);
+        for (uint32_t i = 0; i < nMine; ++i) {
+            const uint32_t ab = i & 1u;
+            mbarWait(&s.aFull[ab], (i >> 1) & 1u);
+            const unsigned long long descA = umDesc(warpUniform(smemAddr(s.A[ab])), kLbo, kSbo);
 #pragma unroll 1
-        for (int half = 0; half < 2; ++half) {
-            if (warp == 0) {  // whole warp on the issue path, one elected lane issues (see ummaF16Elect)
-                if (!dictReady) mbarWait(&s.mbarDict, 0), dictReady = true;
+            for (uint32_t k = 0; k < 4; ++k) {
+                const uint32_t b = k & 1u, use = 2u * i + (k >> 1);  // use number of TMEM buffer b
+                if (use) mbarWait(&s.bufFree[b], (use - 1u) & 1u);
                 fenceAfter();
-                const unsigned long long descA = umDesc(warpUniform(smemAddr(s.A)), kLbo, kSbo);
-                const unsigned long long descB = umDesc(warpUniform(smemAddr(s.D16) + static_cast<uint32_t>(half) * 256u * 128u), kLbo, kSbo);
-                const uint32_t tm = warpUniform(tmem);
+                const unsigned long long descB = umDesc(dAddr + k * 128u * 128u, kLbo, kSbo);
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks)
-                    ummaF16Elect(tm, descA + ((ks * kKStep) >> 4), descB + ((ks * kKStep) >> 4), idescF16(128, 256), ks ? 1u : 0u);
-                ummaCommitElect(&s.mbarMma);
+                    ummaF16Elect(tm + b * 128u, descA + ((ks * kKStep) >> 4), descB + ((ks * kKStep) >> 4), idescF16(128, 128), ks ? 1u : 0u);
+                ummaCommitElect(&s.bufFull[b]);
             }
-            mbarWait(&s.mbarMma, mmaPhase);
-            mmaPhase ^= 1u;
-            fenceAfter();
-            // pass 1: this thread's maximum over its 128 columns (warps 0-3: columns 0-127, warps 4-7: 128-255)
-            float m = 0.0f;
-#pragma unroll 1
-            for (int cc = 0; cc < 4; ++cc) {
-                uint32_t raw[32];
-                tmemLoad32(tmem + laneBase + static_cast<uint32_t>(h * 128 + cc * 32), raw);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) m = fmaxf(m, fabsf(__uint_as_float(raw[i])));
+        }
+    } else {
+        // ================= scanning groups =================
+        const int g = warp >> 2, q = warp & 3;     // group (TMEM buffer), lane quarter
+        const int slot = q * 32 + lane;
+        const int tg = tid & 127;                  // thread within the group
+        const uint32_t laneBase = static_cast<uint32_t>(q * 32) << 16;
+        const int myRow = 64 * g + (tg & 63), myPair = tg >> 6;  // operand rows this thread fetches: pairs myPair and myPair + 2
+        unsigned nCandStat = 0;
+        uint32_t bcN = kWaveNone;
+        uint4 v[4];
+        float epsN = 0.0f;
+        auto loadIndex = [&](uint32_t tile) {
+            const uint32_t e = tile * kWaveTile + static_cast<uint32_t>(myRow);
+            bcN = e < nA ? __ldg(act + e) : kWaveNone;
+        };
+        auto loadRows = [&]() {
+            v[0] = v[1] = v[2] = v[3] = make_uint4(0u, 0u, 0u, 0u);
+            epsN = 0.0f;
+            if (bcN != kWaveNone) {
+                const uint4* src = reinterpret_cast<const uint4*>(p.res16 + static_cast<size_t>(bcN) * kN);
+                v[0] = __ldg(src + 2 * myPair), v[1] = __ldg(src + 2 * myPair + 1);
+                v[2] = __ldg(src + 2 * myPair + 4), v[3] = __ldg(src + 2 * myPair + 5);
+                epsN = __uint_as_float(p.state[bcN].z);
             }
-            s.halfMax[h][slot] = m;
-            __syncthreads();
-            mrun = fmaxf(mrun, fmaxf(s.halfMax[0][slot], s.halfMax[1][slot]));
-            const float thr = myBc != kWaveNone ? mrun - s.eps[slot] : __int_as_float(0x7F800000);
-            // pass 2: rows that can still be the exact maximum
+        };
+        auto storeRows = [&](uint32_t ab) {
+            unsigned char* d = reinterpret_cast<unsigned char*>(s.A[ab]) + (myRow >> 3) * kSbo + (2 * myPair) * kLbo + (myRow & 7) * 16;
+            *reinterpret_cast<uint4*>(d) = v[0];
+            *reinterpret_cast<uint4*>(d + kLbo) = v[1];
+            *reinterpret_cast<uint4*>(d + 4 * kLbo) = v[2];
+            *reinterpret_cast<uint4*>(d + 5 * kLbo) = v[3];
+            if (myPair == 0) s.bc[ab][myRow] = bcN, s.eps[ab][myRow] = epsN;
+            fenceProxyAsync();
+            __syncwarp();
+            if (lane == 0) mbarArrive(&s.aFull[ab]);
+        };
+        loadIndex(blockIdx.x);
+        loadRows();
+        storeRows(0);
+        for (uint32_t i = 0; i < nMine; ++i) {
+            const uint32_t ab = i & 1u;
+            const bool more = i + 1 < nMine;
+            mbarWait(&s.aFull[ab], (i >> 1) & 1u);  // also makes the other warps' bc / eps entries visible
+            const uint32_t myBc = s.bc[ab][slot];
+            const float eps = s.eps[ab][slot];
+            if (more) loadIndex(blockIdx.x + (i + 1) * gridDim.x);
+            float mrun = 0.0f;
 #pragma unroll 1
-            for (int cc = 0; cc < 4; ++cc) {
-                uint32_t raw[32];
-                tmemLoad32(tmem + laneBase + static_cast<uint32_t>(h * 128 + cc * 32), raw);
-                const int atom0 = half * 256 + h * 128 + cc * 32;
+            for (uint32_t kk = 0; kk < 2; ++kk) {
+                const uint32_t k = static_cast<uint32_t>(g) + 2u * kk;  // quarter of the dictionary: atoms 128 k .. 128 k + 127
+                mbarWait(&s.bufFull[g], (2u * i + kk) & 1u);
+                fenceAfter();
+                const uint32_t tcol = tmem + laneBase + static_cast<uint32_t>(g) * 128u;
+                float m = 0.0f;
+#pragma unroll 1
+                for (int cc = 0; cc < 4; ++cc) {
+                    uint32_t raw[32];
+                    tmemLoad32(tcol + static_cast<uint32_t>(cc * 32), raw);
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    bool any = false;
+                    for (int j = 0; j < 32; j += 2) m = fmaxf(m, fmaxf(fabsf(__uint_as_float(raw[j])), fabsf(__uint_as_float(raw[j + 1]))));
+                }
+                mrun = fmaxf(mrun, m);
+                const float thr = myBc != kWaveNone ? mrun - eps : __int_as_float(0x7F800000);
+                CandLocal cl;
+#pragma unroll 1
+                for (int cc = 0; cc < 4; ++cc) {
+                    uint32_t raw[32];
+                    tmemLoad32(tcol + static_cast<uint32_t>(cc * 32), raw);
+                    const int atom0 = static_cast<int>(k) * 128 + cc * 32;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) any |= fabsf(__uint_as_float(raw[8 * g + i])) >= thr;
-                    if (any) {
+                    for (int gq = 0; gq < 4; ++gq) {
+                        bool any = false;
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int atom = atom0 + 8 * g + i;
-                            if (fabsf(__uint_as_float(raw[8 * g + i])) >= thr && atom < p.nBase)
-                                pushCandidate(p, myBc, static_cast<uint32_t>(atom), static_cast<uint32_t>(atom));
+                        for (int j = 0; j < 8; ++j) any |= fabsf(__uint_as_float(raw[8 * gq + j])) >= thr;
+                        if (any) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                const int atom = atom0 + 8 * gq + j;
+                                if (fabsf(__uint_as_float(raw[8 * gq + j])) >= thr && atom < p.nBase)
+                                    cl.add(p, myBc, static_cast<uint32_t>(atom), static_cast<uint32_t>(atom));
+                            }
                         }
                     }
                 }
+                fenceBefore();
+                __syncwarp();
+                if (lane == 0) mbarArrive(&s.bufFree[g]);  // the tensor core may refill this buffer
+                if (myBc != kWaveNone) {  // sub-list k of the block-channel: plain stores, nobody else writes these slots
+                    uint32_t* slots = p.cand + static_cast<size_t>(myBc) * kCandSlots + kCandPerQuarter * k;
+#pragma unroll
+                    for (int j = 0; j < kCandPerQuarter; ++j)
+                        if (cl.n > j) slots[j] = cl.c[j];
+                    reinterpret_cast<uint8_t*>(p.ncand)[static_cast<size_t>(myBc) * 4 + k] = static_cast<uint8_t>(min(cl.n, kCandPerQuarter));
+                    nCandStat += static_cast<unsigned>(cl.n);
+                }
+                if (kk == 0 && more) loadRows();  // next tile's operand rows: in flight during the second quarter
             }
-            fenceBefore();
-            __syncthreads();  // TMEM columns and halfMax are reused by the next pass
+            if (more) storeRows(ab ^ 1u);  // every MMA that read that buffer (tile i - 1) completed before this tile's first quarter did
+            if (myBc != kWaveNone) atomicMax(&p.amax[myBc], __float_as_uint(mrun));
         }
-        if (h == 0 && myBc != kWaveNone) p.amax[myBc] = __float_as_uint(mrun);
+        nCandStat = __reduce_add_sync(kFullMask, nCandStat);
+        if (lane == 0 && nCandStat) atomicAdd(&p.stats[2], static_cast<unsigned long long>(nCandStat));
     }
     fenceBefore();
     __syncthreads();
@@ -279,38 +341,46 @@ __global__ void __launch_bounds__(256, 2) waveBaseKernel(const __grid_constant__
 }
 
 // ------------------------------------------------------------------------------------------------
-// (channel, atom) bins of the appended groups: count / fill, one thread per active block-channel.
+// (channel, atom) bins of the appended groups (counted by the decide pass, offsets by the scan): member lists, one thread per
+// active block-channel. A member record carries everything the scoring pass needs about it - block-channel, group position,
+// dictionary index of the group's first row, 2 eps, and the threshold the base scores imply - so that pass reads its members
+// with one coalesced load.
 // ------------------------------------------------------------------------------------------------
-template <bool kFill>
-__global__ void __launch_bounds__(256) waveBinKernel(const __grid_constant__ WaveParams p, const int iter) {
+__global__ void __launch_bounds__(256) waveBinFillKernel(const __grid_constant__ WaveParams p, const int iter) {
     const uint32_t nA = p.nAct[iter];
     const uint32_t* act = p.act[iter & 1];
     const int lane = threadIdx.x & 31;
     for (uint32_t e0 = blockIdx.x * blockDim.x; e0 < nA; e0 += gridDim.x * blockDim.x) {
         const uint32_t e = e0 + threadIdx.x;
-        uint32_t bc = 0, ng = 0;
+        uint32_t bc = 0, ng = 0, epsHalf = 0, thrBase = 0;
         if (e < nA) {
             bc = act[e];
-            ng = (p.state[bc].y >> 8) & 0xFFu;
+            const uint4 st = p.state[bc];
+            ng = (st.y >> 8) & 0xFFu;
+            const float twoEps = __uint_as_float(st.z);
+            epsHalf = static_cast<uint32_t>(__half_as_ushort(__float2half_ru(twoEps)));  // rounded UP: never a tighter filter
+            thrBase = __float_as_uint(__uint_as_float(p.amax[bc]) - twoEps);
         }
         uint32_t maxNg = ng;
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) maxNg = max(maxNg, __shfl_xor_sync(kFullMask, maxNg, off));
         const uint32_t ch = bc % 3u;
+        uint32_t first = static_cast<uint32_t>(p.nBase);
         for (uint32_t gi = 0; gi < maxNg; ++gi) {
             const bool has = gi < ng;
             const unsigned active = __ballot_sync(kFullMask, has);
             if (has) {
-                const uint32_t bin = ch * static_cast<uint32_t>(p.nBase) + p.groups[static_cast<size_t>(bc) * kMaxK + gi];
+                const uint32_t atom = p.groups[static_cast<size_t>(bc) * kMaxK + gi];
+                const uint32_t bin = ch * static_cast<uint32_t>(p.nBase) + atom;
                 const unsigned peers = __match_any_sync(active, bin);
                 const int leader = __ffs(peers) - 1;
                 uint32_t base = 0;
-                if (lane == leader) base = atomicAdd(kFill ? &p.binCursor[bin] : &p.binCount[bin], static_cast<uint32_t>(__popc(peers)));
-                if (kFill) {
-                    base = __shfl_sync(peers, base, leader);
-                    const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
-                    p.members[p.binOffset[bin] + base + rank] = bc | (gi << 27);
-                }
+                if (lane == leader) base = atomicAdd(&p.binCursor[bin], static_cast<uint32_t>(__popc(peers)));
+                base = __shfl_sync(peers, base, leader);
+                const uint32_t at = p.binOffset[bin] + base + __popc(peers & ((1u << lane) - 1u));
+                p.members[at] = bc | (gi << 27);
+                p.memberInfo[at] = make_uint2(first | (epsHalf << 16), thrBase);
+                first += p.detRows[atom];
             }
         }
     }
@@ -369,22 +439,41 @@ __global__ void __launch_bounds__(1024) waveScanKernel(const __grid_constant__ W
 struct __align__(1024) DetailSmem {
     __half A[kWaveTile * kN];                  // 16 KB residual rows of the tile's members
     alignas(1024) unsigned char B[kImgBytes];  // 8 KB group image
-    uint32_t member[kWaveTile];
     uint32_t bc[kWaveTile];
     uint32_t tileStart[3 * kRowsPad + 1];
+    uint32_t binOffset[3 * kRowsPad + 1];
     unsigned long long mbarB, mbarMma;
     uint32_t tmemBase;
 };
+
+// rows of res16 (128 B each) -> canonical K-major operand image; item = (row, pair of 16-byte chunks)
+__device__ __forceinline__ void gatherRows(const uint16_t* res16, const uint32_t* sBc, __half* A, int tid, int nthreads) {
+    unsigned char* dst = reinterpret_cast<unsigned char*>(A);
+#pragma unroll 4
+    for (int it = tid; it < kWaveTile * 4; it += nthreads) {
+        const int row = it & (kWaveTile - 1), pair = it >> 7;
+        const uint32_t bc = sBc[row];
+        uint4 v0 = make_uint4(0u, 0u, 0u, 0u), v1 = v0;
+        if (bc != kWaveNone) {
+            const uint4* src = reinterpret_cast<const uint4*>(res16 + static_cast<size_t>(bc) * kN) + 2 * pair;
+            v0 = __ldg(src);
+            v1 = __ldg(src + 1);
+        }
+        unsigned char* d = dst + (row >> 3) * kSbo + (2 * pair) * kLbo + (row & 7) * 16;
+        *reinterpret_cast<uint4*>(d) = v0;
+        *reinterpret_cast<uint4*>(d + kLbo) = v1;
+    }
+}
 
 __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant__ WaveParams p, const int iter) {
     extern __shared__ __align__(1024) unsigned char smemRaw[];
     DetailSmem& s = *reinterpret_cast<DetailSmem*>(smemRaw);
     if (p.nAct[iter] == 0) return;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5;
     const int nbins = 3 * p.nBase;
     const uint32_t nT = p.binTileStart[nbins];
     if (blockIdx.x >= nT) return;
-    for (int i = tid; i <= nbins; i += 128) s.tileStart[i] = p.binTileStart[i];
+    for (int i = tid; i <= nbins; i += 128) s.tileStart[i] = p.binTileStart[i], s.binOffset[i] = p.binOffset[i];
     if (tid == 0) {
         mbarInit(&s.mbarB, 1);
         mbarInit(&s.mbarMma, 1);
@@ -413,7 +502,7 @@ __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant
         }
         const int bin = lo;
         const uint32_t chunk = tile - s.tileStart[bin];
-        const uint32_t off = p.binOffset[bin], cnt = p.binOffset[bin + 1] - off;
+        const uint32_t off = s.binOffset[bin], cnt = s.binOffset[bin + 1] - off;
         const uint32_t n = min(static_cast<uint32_t>(kWaveTile), cnt - chunk * kWaveTile);
         const int ch = bin / p.nBase, atom = bin - ch * p.nBase;
         if (bin != curBin) {  // the previous tile's MMAs have completed (mbarMma was waited for), B may be overwritten
@@ -424,11 +513,11 @@ __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant
                 bulkCopy(s.B, reinterpret_cast<const unsigned char*>(p.detUm16) + static_cast<size_t>(bin) * kImgBytes, kImgBytes, &s.mbarB);
             }
         }
-        {
-            const uint32_t mem = static_cast<uint32_t>(tid) < n ? p.members[off + chunk * kWaveTile + tid] : kWaveNone;
-            s.member[tid] = mem;
-            s.bc[tid] = mem != kWaveNone ? (mem & kBcMask) : kWaveNone;
-        }
+        const bool valid = static_cast<uint32_t>(tid) < n;
+        const uint32_t mem = valid ? __ldg(p.members + off + chunk * kWaveTile + tid) : kWaveNone;
+        const uint2 info = valid ? __ldg(p.memberInfo + off + chunk * kWaveTile + tid) : make_uint2(0u, 0u);
+        const uint32_t bc = mem & kBcMask;
+        s.bc[tid] = valid ? bc : kWaveNone;
         __syncthreads();
         gatherRows(p.res16, s.bc, s.A, tid, 128);
         fenceProxyAsync();
@@ -448,17 +537,10 @@ __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant
         mbarWait(&s.mbarMma, mmaPhase);
         mmaPhase ^= 1u;
         fenceAfter();
-        const uint32_t mem = s.member[tid];
         const int rowsValid = p.detRows[atom];
-        float m = 0.0f, thr = __int_as_float(0x7F800000);
-        uint32_t bc = 0, first = 0;
-        if (mem != kWaveNone) {
-            bc = mem & kBcMask;
-            const uint32_t gi = mem >> 27;
-            first = static_cast<uint32_t>(p.nBase);
-            const uint16_t* g = p.groups + static_cast<size_t>(bc) * kMaxK;
-            for (uint32_t k = 0; k < gi; ++k) first += p.detRows[g[k]];
-        }
+        const uint32_t first = info.x & 0xFFFFu;
+        const float twoEps = __half2float(__ushort_as_half(static_cast<unsigned short>(info.x >> 16)));
+        float m = 0.0f;
 #pragma unroll 1
         for (int cc = 0; cc < 2; ++cc) {
             uint32_t raw[32];
@@ -467,25 +549,38 @@ __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant
             for (int i = 0; i < 32; ++i)
                 if (cc * 32 + i < rowsValid) m = fmaxf(m, fabsf(__uint_as_float(raw[i])));
         }
-        if (mem != kWaveNone) thr = fmaxf(m, __uint_as_float(p.amax[bc])) - __uint_as_float(p.state[bc].z);
+        // within 2 eps of the larger of this group's maximum and the base atoms' maximum
+        const float thr = valid ? fmaxf(m - twoEps, __uint_as_float(info.y)) : __int_as_float(0x7F800000);
+        CandLocal cl;
+        if (__any_sync(kFullMask, m >= thr)) {  // most groups stay below the base atoms' maximum: no second pass over them
 #pragma unroll 1
-        for (int cc = 0; cc < 2; ++cc) {
-            uint32_t raw[32];
-            tmemLoad32(tmem + laneBase + static_cast<uint32_t>(cc * 32), raw);
+            for (int cc = 0; cc < 2; ++cc) {
+                uint32_t raw[32];
+                tmemLoad32(tmem + laneBase + static_cast<uint32_t>(cc * 32), raw);
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                bool any = false;
+                for (int g = 0; g < 4; ++g) {
+                    bool any = false;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) any |= fabsf(__uint_as_float(raw[8 * g + i])) >= thr;
-                if (any) {
+                    for (int i = 0; i < 8; ++i) any |= fabsf(__uint_as_float(raw[8 * g + i])) >= thr;
+                    if (any) {
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int row = cc * 32 + 8 * g + i;
-                        if (fabsf(__uint_as_float(raw[8 * g + i])) >= thr && row < rowsValid)
-                            pushCandidate(p, bc, first + static_cast<uint32_t>(row),
-                                          static_cast<uint32_t>(kRowsPad + (ch * p.nBase + atom) * 64 + row));
+                        for (int i = 0; i < 8; ++i) {
+                            const int row = cc * 32 + 8 * g + i;
+                            if (fabsf(__uint_as_float(raw[8 * g + i])) >= thr && row < rowsValid)
+                                cl.add(p, bc, first + static_cast<uint32_t>(row), static_cast<uint32_t>(kRowsPad + (ch * p.nBase + atom) * 64 + row));
+                        }
                     }
                 }
+            }
+        }
+        if (cl.n) {  // one atomic per thread with candidates, after the scan
+            atomicAdd(&p.stats[4], static_cast<unsigned long long>(cl.n));  // diagnostics
+            const uint32_t take = static_cast<uint32_t>(min(cl.n, kCandPerQuarter));
+            const uint32_t pos = atomicAdd(&p.ncandDetail[bc], take);
+            uint32_t* slots = p.candDetail + static_cast<size_t>(bc) * kCandSlotsDetail;
+            for (uint32_t j = 0; j < take; ++j) {
+                if (pos + j < static_cast<uint32_t>(kCandSlotsDetail)) slots[pos + j] = cl.c[j];
+                else queueOverflow(p, bc, cl.c[j]);
             }
         }
         fenceBefore();
@@ -496,12 +591,33 @@ __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(64u) : "memory");
 }
 
+// candidates that found no slot: exact re-score, one per thread
+__global__ void __launch_bounds__(256) waveOverflowKernel(const __grid_constant__ WaveParams p) {
+    const uint32_t n = min(*p.ovfCount, p.ovfCap);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint2 e = p.ovf[i];
+        const float a = exactDot(p.rows32 + static_cast<size_t>(e.y >> 12) * kN, p.res32 + static_cast<size_t>(e.x) * kN);
+        atomicMax(&p.best[e.x], makeKey(a, static_cast<int>(e.y & 0xFFFu)));
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(&p.stats[3], static_cast<unsigned long long>(n));  // diagnostics
+}
+
 // ------------------------------------------------------------------------------------------------
 // Exact decision + step C (MatchingPursuit.cpp:86-104), 8 threads per block-channel, 32 block-channels per CTA pass.
+// The candidate rows of a block-channel are fetched together, 32 bytes per thread and row (one L2 round trip for all of
+// them), then re-scored from shared memory in the oracle's operation order, one candidate per thread.
+// Survivors go to the next iteration's list (batched in shared memory, one reservation per CTA and flush) and are counted
+// into the (channel, atom) bins of their groups.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) waveDecideKernel(const __grid_constant__ WaveParams p, const int iter) {
-    __shared__ __align__(16) float sR[32 * kRStr];
-    __shared__ uint32_t sSurv, sBase;
+constexpr int kRowsPerRound = 4;   // candidate rows of a block-channel staged per round (2.9 candidates on average)
+constexpr int kFlushEvery = 8;     // passes between two flushes of the survivor list
+__global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant__ WaveParams p, const int iter) {
+    __shared__ __align__(16) float sR[32 * kRStr];                       // residuals
+    __shared__ __align__(16) float sRow[32 * kRowsPerRound * kRStr];     // candidate rows
+    __shared__ uint32_t sCand[32][kCandSlots + kCandSlotsDetail];
+    __shared__ uint32_t sList[2][32 * kFlushEvery];
+    __shared__ uint32_t sCount[2], sBase, sN;
+    __shared__ uint32_t sDc[6];  // bins of the groups of atoms 0 and nBase-1: most members, counted per CTA
     const uint32_t nA = p.nAct[iter];
     if (nA == 0) return;
     const uint32_t* act = p.act[iter & 1];
@@ -510,38 +626,91 @@ __global__ void __launch_bounds__(256) waveDecideKernel(const __grid_constant__ 
     const unsigned groupMask = 0xFFu << (lane & 24);
     const int leaderLane = lane & 24;
     float* const myR = sR + grp * kRStr;
+    float* const myRows = sRow + grp * kRowsPerRound * kRStr;
     unsigned long long statRows = 0, statPicks = 0;
-    if (tid == 0) sSurv = 0;
+    if (tid < 2) sCount[tid] = 0;
+    if (tid < 6) sDc[tid] = 0;
+    if (blockIdx.x == 0 && tid == 0) *p.ovfCount = 0u;  // the overflow queue of this iteration has been consumed
     __syncthreads();
 
-    for (uint32_t base = blockIdx.x * 32u; base < nA; base += gridDim.x * 32u) {
-        const uint32_t e = base + static_cast<uint32_t>(grp);
+    auto flush = [&](uint32_t f) {  // survivor list f -> next iteration's active list
+        __syncthreads();
+        if (tid == 0) {
+            sN = sCount[f];
+            sBase = sN ? atomicAdd(&p.nAct[iter + 1], sN) : 0u;
+            sCount[f] = 0;  // list f is appended to again only after the NEXT flush's first barrier
+        }
+        __syncthreads();
+        for (uint32_t i = tid; i < sN; i += 256) actNext[sBase + i] = sList[f][i];
+    };
+
+    const uint32_t stride = gridDim.x * 32u;
+    uint32_t e = blockIdx.x * 32u + static_cast<uint32_t>(grp);
+    uint32_t bcNext = e < nA ? act[e] : 0u;
+    uint32_t pass = 0, f = 0;
+    for (uint32_t base = blockIdx.x * 32u; base < nA; base += stride, e += stride, ++pass) {
         const bool valid = e < nA;
-        uint32_t survRank = kWaveNone, bc = 0;
+        const uint32_t bc = bcNext;
+        if (e + stride < nA) bcNext = act[e + stride];  // next pass's block-channel: its loads start without this round trip
         if (valid) {
-            bc = act[e];
             const int ch = static_cast<int>(bc % 3u);
             const uint4 st = p.state[bc];
+            const uint32_t nBaseCand = p.ncand[bc];
+            const uint32_t nDet = min(p.ncandDetail[bc], static_cast<uint32_t>(kCandSlotsDetail));
+            const uint32_t c0 = p.cand[static_cast<size_t>(bc) * kCandSlots + l8], c1 = p.cand[static_cast<size_t>(bc) * kCandSlots + 8 + l8];
+            const uint32_t cd = l8 < kCandSlotsDetail ? p.candDetail[static_cast<size_t>(bc) * kCandSlotsDetail + l8] : 0u;
+            unsigned long long key = l8 == 0 ? p.best[bc] : 0ULL;
             const int prev = static_cast<int>(st.x & 0xFFFFu), height = static_cast<int>(st.x >> 16);
             const int reps = static_cast<int>(st.y & 0xFFu), ng = static_cast<int>((st.y >> 8) & 0xFFu);
             const float4* src = reinterpret_cast<const float4*>(p.res32 + static_cast<size_t>(bc) * kN + 8 * l8);
             const float4 r0 = src[0], r1 = src[1];
             reinterpret_cast<float4*>(myR + 8 * l8)[0] = r0;
             reinterpret_cast<float4*>(myR + 8 * l8)[1] = r1;
+            // compact list of the block-channel's candidates: base slot s is valid when (s % 4) < count of quarter s / 4
+            const bool v0 = static_cast<uint32_t>(l8 & 3) < ((nBaseCand >> (8 * (l8 >> 2))) & 0xFFu);
+            const bool v1 = static_cast<uint32_t>(l8 & 3) < ((nBaseCand >> (8 * (2 + (l8 >> 2)))) & 0xFFu);
+            const bool vd = static_cast<uint32_t>(l8) < nDet;
+            const unsigned m0 = (__ballot_sync(groupMask, v0) >> leaderLane) & 0xFFu, m1 = (__ballot_sync(groupMask, v1) >> leaderLane) & 0xFFu;
+            const unsigned md = (__ballot_sync(groupMask, vd) >> leaderLane) & 0xFFu;
+            const unsigned below = (1u << l8) - 1u;
+            const int n0 = __popc(m0), n1 = __popc(m1), nCand = n0 + n1 + __popc(md);
+            if (v0) sCand[grp][__popc(m0 & below)] = c0;
+            if (v1) sCand[grp][n0 + __popc(m1 & below)] = c1;
+            if (vd) sCand[grp][n0 + n1 + __popc(md & below)] = cd;
             __syncwarp(groupMask);
-            // exact re-score of the listed candidates, one per thread
-            const uint32_t nc = min(p.ncand[bc], static_cast<uint32_t>(kCandSlots));
-            unsigned long long key = 0ULL;
-            if (static_cast<uint32_t>(l8) < nc) {
-                const uint32_t c = p.cand[static_cast<size_t>(bc) * kCandSlots + l8];
-                const float a = exactDot(p.rows32 + static_cast<size_t>(c >> 12) * kN, myR);
-                key = makeKey(a, static_cast<int>(c & 0xFFFu));
+            for (int r = 0; r < nCand; r += kRowsPerRound) {
+                const int nr = min(kRowsPerRound, nCand - r);
+                // 32 bytes per thread and row straight into shared memory (cp.async: no staging registers, all rows in flight at once)
+#pragma unroll
+                for (int j = 0; j < kRowsPerRound; ++j)
+                    if (j < nr) {
+                        const float* rowp = p.rows32 + static_cast<size_t>(sCand[grp][r + j] >> 12) * kN + 8 * l8;
+                        const uint32_t dst = smemAddr(myRows + j * kRStr + 8 * l8);
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(rowp) : "memory");
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst + 16u), "l"(rowp + 4) : "memory");
+                    }
+                asm volatile("cp.async.wait_all;" ::: "memory");
+                __syncwarp(groupMask);
+                if (l8 < nr) {  // acc = fl(acc + fl(d * r)), j ascending, never fused (tc::exactDot)
+                    const float4* dp = reinterpret_cast<const float4*>(myRows + l8 * kRStr);
+                    const float4* rp = reinterpret_cast<const float4*>(myR);
+                    float acc = 0.0f;
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) {
+                        const float4 d4 = dp[c], r4 = rp[c];
+                        acc = __fadd_rn(acc, __fmul_rn(d4.x, r4.x));
+                        acc = __fadd_rn(acc, __fmul_rn(d4.y, r4.y));
+                        acc = __fadd_rn(acc, __fmul_rn(d4.z, r4.z));
+                        acc = __fadd_rn(acc, __fmul_rn(d4.w, r4.w));
+                    }
+                    key = max(key, makeKey(acc, static_cast<int>(sCand[grp][r + l8] & 0xFFFu)));
+                }
+                __syncwarp(groupMask);
             }
-            if (l8 == 0) key = max(key, p.best[bc]);
 #pragma unroll
             for (int off = 4; off > 0; off >>= 1) key = max(key, __shfl_xor_sync(groupMask, key, off));
-            const int idx = keyIndex(key);
-            const float proj = keyValue(key);
+            const int idx = key ? keyIndex(key) : 0;
+            const float proj = key ? keyValue(key) : 0.0f;
             const float qf = p.quant[ch * kMaxK + reps];
             const int qi = static_cast<int>(roundf(__fdiv_rn(proj, qf)));
             const uint32_t deltaId = (reps ? zigzag(idx - prev) : static_cast<uint32_t>(idx)) & 0xFFFFu;
@@ -552,7 +721,7 @@ __global__ void __launch_bounds__(256) waveDecideKernel(const __grid_constant__ 
             } else {
                 const float c = __fmul_rn(qf, static_cast<float>(qi));
                 uint32_t rowId = static_cast<uint32_t>(idx);
-                const uint16_t* g = p.groups + static_cast<size_t>(bc) * kMaxK;
+                uint16_t* g = p.groups + static_cast<size_t>(bc) * kMaxK;
                 if (idx >= p.nBase) {
                     int hh = p.nBase;
                     for (int k = 0; k < ng; ++k) {
@@ -566,7 +735,7 @@ __global__ void __launch_bounds__(256) waveDecideKernel(const __grid_constant__ 
                     }
                 }
                 const float4* rowp = reinterpret_cast<const float4*>(p.rows32 + static_cast<size_t>(rowId) * kN) + 2 * l8;
-                const float4 d0 = __ldg(rowp), d1 = __ldg(rowp + 1);
+                const float4 d0 = __ldg(rowp), d1 = __ldg(rowp + 1);  // fetched a moment ago as a candidate row: L1 / L2 hit
                 float r[8];
                 r[0] = __fsub_rn(r0.x, __fmul_rn(c, d0.x));
                 r[1] = __fsub_rn(r0.y, __fmul_rn(c, d0.y));
@@ -603,32 +772,40 @@ __global__ void __launch_bounds__(256) waveDecideKernel(const __grid_constant__ 
                         hw[i] = static_cast<uint32_t>(__half_as_ushort(__float2half_rn(r[2 * i]))) |
                                 (static_cast<uint32_t>(__half_as_ushort(__float2half_rn(r[2 * i + 1]))) << 16);
                     *reinterpret_cast<uint4*>(p.res16 + static_cast<size_t>(bc) * kN + 8 * l8) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+                    // the survivor's groups (those it had + the one just appended) count into next iteration's bins
+                    for (int k = l8; k < ngNew; k += 8) {
+                        const int atom = (k == ng) ? idx : static_cast<int>(g[k]);
+                        if (atom == 0) atomicAdd(&sDc[2 * ch], 1u);
+                        else if (atom == p.nBase - 1) atomicAdd(&sDc[2 * ch + 1], 1u);
+                        else atomicAdd(&p.binCount[ch * p.nBase + atom], 1u);
+                    }
                     if (l8 == 0) {
-                        if (isBase) p.groups[static_cast<size_t>(bc) * kMaxK + ng] = static_cast<uint16_t>(idx);
+                        if (isBase) g[ng] = static_cast<uint16_t>(idx);
                         p.state[bc] = make_uint4(static_cast<uint32_t>(idx) | (static_cast<uint32_t>(heightNew) << 16),
                                                  static_cast<uint32_t>(reps + 1) | (static_cast<uint32_t>(ngNew) << 8),
                                                  __float_as_uint(twoEpsOf(p, ss)), 0u);
-                        survRank = atomicAdd(&sSurv, 1u);
+                        p.amax[bc] = 0u;
+                        sList[f][atomicAdd(&sCount[f], 1u)] = bc;
                     }
                 }
             }
             if (l8 == 0) {
                 p.best[bc] = 0ULL;
-                p.ncand[bc] = 0u;
+                p.ncandDetail[bc] = 0u;
                 if (count >= 0) {
                     p.counts[bc] = static_cast<uint16_t>(count);
                     statPicks += static_cast<unsigned long long>(count);
                 }
             }
         }
-        __syncthreads();
-        if (tid == 0) {
-            sBase = sSurv ? atomicAdd(&p.nAct[iter + 1], sSurv) : 0u;
-            sSurv = 0;
+        if ((pass % kFlushEvery) == kFlushEvery - 1) {
+            flush(f);
+            f ^= 1u;
         }
-        __syncthreads();
-        if (survRank != kWaveNone) actNext[sBase + survRank] = bc;
     }
+    flush(f);
+    __syncthreads();
+    if (tid < 6 && sDc[tid]) atomicAdd(&p.binCount[(tid >> 1) * p.nBase + ((tid & 1) ? p.nBase - 1 : 0)], sDc[tid]);
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
         statRows += __shfl_xor_sync(kFullMask, statRows, off);
@@ -664,21 +841,21 @@ cudaError_t launchWaveIteration(const WaveParams& p, int iter, uint32_t nActHint
     if (nActHint == 0) return cudaSuccess;
     const unsigned sms = static_cast<unsigned>(numSMs);
     const unsigned tiles = (nActHint + kWaveTile - 1) / kWaveTile;
-    waveBaseKernel<<<std::min(tiles, 2u * sms), 256, smemBase, st>>>(p, iter);
+    waveBaseKernel<<<std::min(tiles, 2u * sms), kBaseThreads, smemBase, st>>>(p, iter);
     int n = 1;
     if (iter > 0) {
         const unsigned binGrid = std::min((nActHint + 255u) / 256u, 8u * sms);
-        waveBinKernel<false><<<binGrid, 256, 0, st>>>(p, iter);
         waveScanKernel<<<1, 1024, 0, st>>>(p, iter);
-        waveBinKernel<true><<<binGrid, 256, 0, st>>>(p, iter);
+        waveBinFillKernel<<<binGrid, 256, 0, st>>>(p, iter);
         // at most one partial tile per bin on top of the full ones
         const unsigned long long items = static_cast<unsigned long long>(nActHint) * static_cast<unsigned long long>(std::min(iter, kMaxK - 1));
         const unsigned long long maxTiles = items / kWaveTile + static_cast<unsigned long long>(3 * p.nBase);
         waveDetailKernel<<<static_cast<unsigned>(std::min<unsigned long long>(maxTiles, 6ull * sms)), 128, smemDetail, st>>>(p, iter);
-        n += 4;
+        n += 3;
     }
+    waveOverflowKernel<<<std::min((nActHint + 1023u) / 1024u + 1u, 2u * sms), 256, 0, st>>>(p);
     waveDecideKernel<<<std::min((nActHint + 31u) / 32u, 16u * sms), 256, 0, st>>>(p, iter);
-    n += 1;
+    n += 2;
     if (launches) *launches += n;
     return cudaGetLastError();
 }

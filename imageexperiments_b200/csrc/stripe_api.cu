@@ -62,6 +62,12 @@ int needPhase(mnenc_ctx* c, int phase) {
 }
 
 }  // namespace
+
+int stripeExchangeHistogram(mnenc_ctx* c) {
+    if (int rc = needPhase(c, 3)) return rc;
+    return exchangeHistogramSparse(c, c->stripe->b, 6 * c->K + 1);
+}
+
 }  // namespace mnenc
 
 using namespace mnenc;
@@ -337,7 +343,9 @@ int mnenc_stripe_plan(mnenc_t* c, uint64_t* seq_bits) try {
         s->entryOf[ent[e].seq].push_back(e);
     }
     s->plans.assign(nSeq, SequencePlan{});
-    {
+    if (stripeRanks(c) > 1) {  // in-library exchanges: the table builds are dealt over the ranks and all-gathered
+        if (int rc = planSharded(c, stats, s->plans)) return rc;
+    } else {
         std::vector<int> byLoad(nSeq);
         std::iota(byLoad.begin(), byLoad.end(), 0);
         std::sort(byLoad.begin(), byLoad.end(), [&](int a, int b2) { return stats[a].size() > stats[b2].size(); });

@@ -1,0 +1,393 @@
+// ONE image sharded by block columns over the GPUs of one box, exchanges INSIDE the library (BASELINE.json
+// configs[3]): the six phases of the stripe protocol (stripe_api.cu) driven in C++ with NCCL over NVLink / NVSwitch between
+// them, so that the reference-side callers — the C++ shim and the `Compression` front end (Compression.cpp:117-123) — get
+// stripes from a plain encode call. Two ways to get a communicator:
+//   * one process per GPU (torchrun, MPI, ...): mnenc_comm_unique_id on one rank, the 128 bytes handed to the others by any
+//     means, mnenc_comm_init_rank on every rank, then mnenc_encode_striped_rgb8 collectively;
+//   * one process, several GPUs: mnenc_create_multi (ncclCommInitAll); mnenc_encode_rgb8 on that context runs one host thread
+//     per GPU through the same code.
+// Exchanges (north_star: "NCCL ... only for the global symbol-histogram allreduce and the offset scan and gather of per-GPU
+// bitstream segments"):
+//   all-gather  stream sizes + last raw DC value; boundary run records                      (two small host-staged gathers)
+//   histogram   each rank compacts its local histogram into (sequence, symbol, count, first position) entries; the entry
+//               lists are all-gathered and merged on every GPU (sum / min / max) - ~1 MB instead of three dense
+//               [193][65536] all-reduces (150 MB)
+//   code tables the 193 table builds are dealt over the ranks (largest alphabets first), every rank builds its share on
+//               its host threads, the tables are all-gathered
+//   offset scan all-gather of the payload bits per (rank, sequence)
+//   segments    reduce(SUM) of the packed words to rank 0: every rank packs its slices at their FINAL bit positions, the bits
+//               are disjoint, so the sum is the concatenation of the per-GPU bitstream segments
+#include <algorithm>
+#include <cstring>
+#include <numeric>
+#include <thread>
+
+#include "mnenc_ctx.cuh"
+#include "nccl_dyn.h"
+
+namespace mnenc {
+
+struct StripeComm {
+    ncclComm_t comm = nullptr;
+    int rank = 0, nranks = 1;
+    DevBuf stage, gathered;   // host-staged all-gathers; all-gathered histogram entries
+    PinBuf hStage;
+    float ms[16] = {};         // host clock per phase / exchange of the last striped encode
+};
+
+void destroyStripeComm(StripeComm* sc) {
+    if (!sc) return;
+    if (sc->comm) {
+        std::string err;
+        if (const NcclApi* n = ncclApi(&err)) n->commDestroy(sc->comm);
+    }
+    delete sc;
+}
+
+int stripeRanks(const mnenc_ctx* c) { return c->comm ? c->comm->nranks : 1; }
+
+namespace {
+
+#define NC(expr)                                                                                                       \
+    do {                                                                                                               \
+        ncclResult_t r_ = (expr);                                                                                      \
+        if (r_ != ncclSuccess) return ::mnenc::fail(MNENC_ERR_CUDA, std::string(#expr) + ": " + nccl->getErrorString(r_)); \
+    } while (0)
+
+// all-gather of `bytes` host bytes per rank (small records): H2D, ncclAllGather, D2H on the context's stream
+int allGatherHost(mnenc_ctx* c, const NcclApi* nccl, const void* src, void* dst, size_t bytes) {
+    StripeComm* sc = c->comm.get();
+    if (sc->nranks == 1) {
+        std::memcpy(dst, src, bytes);
+        return MNENC_OK;
+    }
+    const size_t padded = (bytes + 15) / 16 * 16;
+    CU(sc->stage.ensure(padded * (sc->nranks + 1)));
+    CU(sc->hStage.ensure(padded * (sc->nranks + 1)));
+    unsigned char* h = sc->hStage.as<unsigned char>();
+    unsigned char* d = sc->stage.as<unsigned char>();
+    std::memcpy(h, src, bytes);
+    CU(cudaMemcpyAsync(d, h, padded, cudaMemcpyHostToDevice, c->stream));
+    NC(nccl->allGather(d, d + padded, padded, ncclUint8, sc->comm, c->stream));
+    CU(cudaMemcpyAsync(h + padded, d + padded, padded * sc->nranks, cudaMemcpyDeviceToHost, c->stream));
+    CU(waitStream(c));
+    for (int r = 0; r < sc->nranks; ++r) std::memcpy(static_cast<unsigned char*>(dst) + r * bytes, h + padded * (r + 1), bytes);
+    return MNENC_OK;
+}
+
+}  // namespace
+
+// Sparse exchange of the symbol histogram: local dense tables -> compact entries -> all-gather -> merge into the dense
+// tables of every rank (identical everywhere afterwards, like the three dense all-reduces it replaces).
+int exchangeHistogramSparse(mnenc_ctx* c, BackendBuffers& b, int nSeq) {
+    StripeComm* sc = c->comm.get();
+    std::string err;
+    const NcclApi* nccl = ncclApi(&err);
+    if (!nccl) return fail(MNENC_ERR_CUDA, err);
+    cudaStream_t st = c->stream;
+    const int nr = sc->nranks;
+    c->launches += launchCompact(b, nSeq, st);  // hist bins -> entries (bins cleared, firstPos = entry index)
+    // counts of every rank
+    CU(sc->stage.ensure(16 * (nr + 1)));
+    CU(sc->hStage.ensure(16 * (nr + 1)));
+    uint32_t* dCounts = sc->stage.as<uint32_t>();
+    NC(nccl->allGather(b.nEntries, dCounts, 1, ncclUint32, sc->comm, st));
+    CU(cudaMemcpyAsync(sc->hStage.p, dCounts, 4 * nr, cudaMemcpyDeviceToHost, st));
+    CU(waitStream(c));
+    const uint32_t* counts = sc->hStage.as<uint32_t>();
+    uint32_t nMax = 0;
+    for (int r = 0; r < nr; ++r) nMax = std::max(nMax, counts[r]);
+    if (nMax > c->entryCap) return fail(MNENC_ERR_INTERNAL, "more than 2^20 distinct (sequence, symbol) pairs on one rank");
+    const uint32_t mine = counts[sc->rank];
+    c->launches += launchResetHistogram(b, mine, st);  // firstPos back to "not seen", maxSym and nEntries to 0; the entry list stays
+    if (nMax) {
+        CU(sc->gathered.ensure(static_cast<size_t>(nMax) * nr * sizeof(HistEntry)));
+        NC(nccl->allGather(b.entries, sc->gathered.p, static_cast<size_t>(nMax) * sizeof(HistEntry), ncclUint8, sc->comm, st));
+        c->launches += launchMergeEntries(b, sc->gathered.as<HistEntry>(), dCounts, nr, nMax, st);
+    }
+    return MNENC_OK;
+}
+
+namespace {
+
+// Serialised code table of one sequence, as exchanged between the ranks.
+struct PlanWire {
+    uint32_t seq, golombM;  // golombM: 0 = Huffman
+    uint32_t eofCode, eofLen, maxCodeLen, nSym;
+    uint64_t payloadBits, headerBits;
+    uint32_t headerBytes, pad;
+};
+
+}  // namespace
+
+// Code tables of all sequences with the builds dealt over the ranks. stats[q] are this rank's entries of sequence q (same SET
+// on every rank after the histogram merge, order may differ); on return plans[q].code/len follow this rank's order.
+int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats, std::vector<SequencePlan>& plans) {
+    StripeComm* sc = c->comm.get();
+    std::string err;
+    const NcclApi* nccl = ncclApi(&err);
+    if (!nccl) return fail(MNENC_ERR_CUDA, err);
+    const int nSeq = static_cast<int>(stats.size()), nr = sc->nranks, me = sc->rank;
+    std::vector<int> byLoad(nSeq);
+    std::iota(byLoad.begin(), byLoad.end(), 0);
+    std::stable_sort(byLoad.begin(), byLoad.end(), [&](int a, int b2) { return stats[a].size() > stats[b2].size(); });  // identical on every rank
+    std::vector<int> mineSeqs;
+    for (int i = me; i < nSeq; i += nr) mineSeqs.push_back(byLoad[i]);
+    c->pool->parallelFor(static_cast<int>(mineSeqs.size()), [&](int i) { planSequence(stats[mineSeqs[i]], plans[mineSeqs[i]]); });
+    // serialise
+    std::vector<unsigned char> wire;
+    for (int q : mineSeqs) {
+        const SequencePlan& p = plans[q];
+        PlanWire w{};
+        w.seq = static_cast<uint32_t>(q);
+        w.golombM = p.golomb ? p.golombM : 0u;
+        w.eofCode = p.eofCode, w.eofLen = p.eofLen, w.maxCodeLen = p.maxCodeLen;
+        w.nSym = p.golomb ? 0u : static_cast<uint32_t>(stats[q].size());
+        w.payloadBits = p.payloadBits, w.headerBits = p.header.nbits;
+        w.headerBytes = static_cast<uint32_t>(p.header.bytes.size());
+        const size_t at = wire.size(), hb = (w.headerBytes + 7) / 8 * 8;
+        wire.resize(at + sizeof(PlanWire) + hb + static_cast<size_t>(w.nSym) * 8);
+        std::memcpy(wire.data() + at, &w, sizeof(w));
+        std::memcpy(wire.data() + at + sizeof(w), p.header.bytes.data(), w.headerBytes);
+        uint32_t* sym = reinterpret_cast<uint32_t*>(wire.data() + at + sizeof(w) + hb);
+        for (uint32_t k = 0; k < w.nSym; ++k) {
+            sym[2 * k] = stats[q][k].symbol | (static_cast<uint32_t>(p.len[k]) << 16);
+            sym[2 * k + 1] = p.code[k];
+        }
+    }
+    // sizes, then the tables
+    std::vector<uint64_t> sizes(nr);
+    const uint64_t mySize = wire.size();
+    if (int rc = allGatherHost(c, nccl, &mySize, sizes.data(), 8)) return rc;
+    const size_t maxSize = static_cast<size_t>(*std::max_element(sizes.begin(), sizes.end()));
+    wire.resize(maxSize);
+    std::vector<unsigned char> all(maxSize * nr);
+    if (int rc = allGatherHost(c, nccl, wire.data(), all.data(), maxSize)) return rc;
+    std::vector<uint32_t> slot(65536);
+    for (int r = 0; r < nr; ++r) {
+        if (r == me) continue;
+        const unsigned char* p0 = all.data() + maxSize * r;
+        size_t at = 0;
+        while (at + sizeof(PlanWire) <= sizes[r]) {
+            PlanWire w;
+            std::memcpy(&w, p0 + at, sizeof(w));
+            if (w.seq >= static_cast<uint32_t>(nSeq)) return fail(MNENC_ERR_INTERNAL, "bad code table from a peer");
+            const size_t hb = (w.headerBytes + 7) / 8 * 8;
+            SequencePlan& p = plans[w.seq];
+            const std::vector<SymbolStat>& mineStats = stats[w.seq];
+            p = SequencePlan{};
+            p.golomb = w.golombM != 0;
+            p.golombM = w.golombM;
+            p.eofCode = w.eofCode, p.eofLen = static_cast<uint8_t>(w.eofLen), p.maxCodeLen = w.maxCodeLen;
+            p.payloadBits = w.payloadBits;
+            p.header.nbits = w.headerBits;
+            p.header.bytes.assign(p0 + at + sizeof(w), p0 + at + sizeof(w) + w.headerBytes);
+            p.code.assign(mineStats.size(), 0u);
+            p.len.assign(mineStats.size(), 0);
+            if (w.nSym) {
+                if (w.nSym != mineStats.size()) return fail(MNENC_ERR_INTERNAL, "code table of a peer does not match the merged histogram");
+                for (uint32_t k = 0; k < w.nSym; ++k) slot[mineStats[k].symbol & 0xFFFFu] = k;
+                const uint32_t* sym = reinterpret_cast<const uint32_t*>(p0 + at + sizeof(w) + hb);
+                for (uint32_t k = 0; k < w.nSym; ++k) {
+                    const uint32_t s = sym[2 * k] & 0xFFFFu, mk = slot[s];
+                    if (mk >= w.nSym || mineStats[mk].symbol != s) return fail(MNENC_ERR_INTERNAL, "code table of a peer names an unknown symbol");
+                    p.code[mk] = sym[2 * k + 1];
+                    p.len[mk] = static_cast<uint8_t>(sym[2 * k] >> 16);
+                }
+            }
+            at += sizeof(PlanWire) + hb + static_cast<size_t>(w.nSym) * 8;
+        }
+    }
+    return MNENC_OK;
+}
+
+// reduce(SUM) of the packed words to rank 0
+int reduceSegments(mnenc_ctx* c, void* words, size_t nWords) {
+    StripeComm* sc = c->comm.get();
+    std::string err;
+    const NcclApi* nccl = ncclApi(&err);
+    if (!nccl) return fail(MNENC_ERR_CUDA, err);
+    NC(nccl->reduce(words, words, nWords, ncclUint32, ncclSum, 0, sc->comm, c->stream));
+    CU(waitStream(c));
+    return MNENC_OK;
+}
+
+int encodeStriped(mnenc_ctx* c, const uint8_t* rgb, int onDevice, size_t width, size_t height, size_t stride, uint32_t bx0, uint32_t bx1,
+                  uint8_t** out, size_t* outBytes) {
+    StripeComm* sc = c->comm.get();
+    if (!sc) return fail(MNENC_ERR_STATE, "no communicator on this context (mnenc_comm_init_rank / mnenc_create_multi)");
+    std::string err;
+    const NcclApi* nccl = ncclApi(&err);
+    if (!nccl) return fail(MNENC_ERR_CUDA, err);
+    const int K = c->K, nr = sc->nranks, nSeq = 6 * K + 1;
+    std::memset(sc->ms, 0, sizeof(sc->ms));
+    double t = nowMs();
+    auto lap = [&](int i) {
+        const double now = nowMs();
+        sc->ms[i] += static_cast<float>(now - t);
+        t = now;
+    };
+    std::vector<uint32_t> rec1(3 * K + 3), all1(static_cast<size_t>(nr) * (3 * K + 3));
+    if (int rc = mnenc_stripe_begin(c, rgb, onDevice, width, height, stride, sc->rank, nr, bx0, bx1, rec1.data())) return rc;
+    lap(0);
+    if (int rc = allGatherHost(c, nccl, rec1.data(), all1.data(), rec1.size() * 4)) return rc;
+    lap(1);
+    std::vector<uint32_t> rec2(static_cast<size_t>(6) * K * 6), all2(rec2.size() * nr);
+    if (int rc = mnenc_stripe_rle(c, all1.data(), rec2.data())) return rc;
+    lap(2);
+    if (int rc = allGatherHost(c, nccl, rec2.data(), all2.data(), rec2.size() * 4)) return rc;
+    lap(3);
+    void *hist = nullptr, *first = nullptr, *msym = nullptr;
+    size_t nh = 0, nm = 0;
+    if (int rc = mnenc_stripe_histogram(c, all2.data(), &hist, &first, &nh, &msym, &nm)) return rc;
+    lap(4);
+    if (nr > 1)
+        if (int rc = stripeExchangeHistogram(c)) return rc;
+    lap(5);
+    std::vector<uint64_t> bits(nSeq), allBits(static_cast<size_t>(nSeq) * nr);
+    if (int rc = mnenc_stripe_plan(c, bits.data())) return rc;  // code tables dealt over the ranks when a communicator is set
+    lap(6);
+    if (int rc = allGatherHost(c, nccl, bits.data(), allBits.data(), bits.size() * 8)) return rc;
+    lap(7);
+    void* words = nullptr;
+    size_t nWords = 0, nBytes = 0;
+    if (int rc = mnenc_stripe_pack(c, allBits.data(), &words, &nWords, &nBytes)) return rc;
+    lap(8);
+    if (nr > 1)
+        if (int rc = reduceSegments(c, words, nWords)) return rc;
+    lap(9);
+    if (int rc = mnenc_stripe_finish(c, out, outBytes)) return rc;
+    lap(10);
+    return MNENC_OK;
+}
+
+}  // namespace mnenc
+
+using namespace mnenc;
+
+extern "C" {
+
+int mnenc_comm_unique_id(uint8_t* id128) try {
+    if (!id128) return fail(MNENC_ERR_ARG, "null argument");
+    std::string err;
+    const NcclApi* nccl = ncclApi(&err);
+    if (!nccl) return fail(MNENC_ERR_CUDA, err);
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    NC(nccl->getUniqueId(&id));
+    std::memcpy(id128, &id, 128);
+    return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
+}
+
+int mnenc_comm_init_rank(mnenc_t* c, int rank, int nranks, const uint8_t* id128) try {
+    if (!c || !id128 || nranks < 1 || rank < 0 || rank >= nranks) return fail(MNENC_ERR_ARG, "bad argument");
+    std::string err;
+    const NcclApi* nccl = ncclApi(&err);
+    if (!nccl) return fail(MNENC_ERR_CUDA, err);
+    CU(cudaSetDevice(c->device));
+    std::unique_ptr<StripeComm, void (*)(StripeComm*)> sc(new StripeComm, destroyStripeComm);
+    sc->rank = rank, sc->nranks = nranks;
+    ncclUniqueId id;
+    std::memcpy(&id, id128, 128);
+    NC(nccl->commInitRank(&sc->comm, nranks, id, rank));
+    c->comm = std::move(sc);
+    return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
+}
+
+int mnenc_comm_destroy(mnenc_t* c) try {
+    if (!c) return fail(MNENC_ERR_ARG, "null argument");
+    c->comm.reset();
+    return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
+}
+
+int mnenc_encode_striped_rgb8(mnenc_t* c, const uint8_t* rgb_stripe, int on_device, size_t width, size_t height, size_t row_stride_bytes,
+                              uint32_t bx0, uint32_t bx1, uint8_t** out, size_t* out_bytes) try {
+    if (!c || !out || !out_bytes) return fail(MNENC_ERR_ARG, "null argument");
+    *out = nullptr;
+    *out_bytes = 0;
+    return encodeStriped(c, rgb_stripe, on_device, width, height, row_stride_bytes, bx0, bx1, out, out_bytes);
+} catch (...) {
+    return mnenc::abiCaught();
+}
+
+int mnenc_last_stripe_timing(mnenc_t* c, float* ms16) try {
+    if (!c || !ms16) return fail(MNENC_ERR_ARG, "null argument");
+    if (!c->comm) return fail(MNENC_ERR_STATE, "no communicator on this context");
+    std::memcpy(ms16, c->comm->ms, sizeof(c->comm->ms));
+    return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
+}
+
+int mnenc_create_multi(mnenc_t** out, const int* devices, int n_devices, int K, int block_size, const float* base, int n_base,
+                       const int32_t* detail_rows, const float* detailY, const float* detailU, const float* detailV) try {
+    if (!out || !devices || n_devices < 1) return fail(MNENC_ERR_ARG, "bad argument");
+    std::string err;
+    const NcclApi* nccl = ncclApi(&err);
+    if (!nccl) return fail(MNENC_ERR_CUDA, err);
+    std::vector<mnenc_t*> ctxs;
+    auto bail = [&](int rc) {
+        for (mnenc_t* x : ctxs) mnenc_destroy(x);
+        return rc;
+    };
+    for (int i = 0; i < n_devices; ++i) {
+        mnenc_t* x = nullptr;
+        if (int rc = mnenc_create(&x, devices[i], K, block_size, base, n_base, detail_rows, detailY, detailU, detailV)) return bail(rc);
+        ctxs.push_back(x);
+    }
+    std::vector<ncclComm_t> comms(n_devices);
+    if (ncclResult_t r = nccl->commInitAll(comms.data(), n_devices, devices); r != ncclSuccess)
+        return bail(fail(MNENC_ERR_CUDA, std::string("ncclCommInitAll: ") + nccl->getErrorString(r)));
+    for (int i = 0; i < n_devices; ++i) {
+        std::unique_ptr<StripeComm, void (*)(StripeComm*)> sc(new StripeComm, destroyStripeComm);
+        sc->rank = i, sc->nranks = n_devices, sc->comm = comms[i];
+        ctxs[i]->comm = std::move(sc);
+        if (i) ctxs[0]->groupPeers.push_back(ctxs[i]);
+    }
+    *out = ctxs[0];
+    return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
+}
+
+}  // extern "C"
+
+namespace mnenc {
+
+// mnenc_encode_rgb8 on a context made by mnenc_create_multi: one host thread per GPU, each takes its block columns of the
+// host image through the striped encode; the stream comes back from the first GPU.
+int encodeGroup(mnenc_ctx* c, const uint8_t* rgb, size_t width, size_t height, size_t stride, uint8_t** out, size_t* outBytes) {
+    std::vector<mnenc_ctx*> ranks{c};
+    ranks.insert(ranks.end(), c->groupPeers.begin(), c->groupPeers.end());
+    const int nr = static_cast<int>(ranks.size());
+    const uint32_t nbx = static_cast<uint32_t>((width + 7) / 8);
+    std::vector<int> rcs(nr, MNENC_OK);
+    std::vector<std::string> errs(nr);
+    std::vector<uint8_t*> outs(nr, nullptr);
+    std::vector<size_t> sizes(nr, 0);
+    auto work = [&](int r) {
+        const uint32_t bx0 = static_cast<uint32_t>(static_cast<uint64_t>(nbx) * r / nr), bx1 = static_cast<uint32_t>(static_cast<uint64_t>(nbx) * (r + 1) / nr);
+        rcs[r] = mnenc_encode_striped_rgb8(ranks[r], rgb + 3 * 8 * static_cast<size_t>(bx0), 0, width, height, stride, bx0, bx1, &outs[r], &sizes[r]);
+        if (rcs[r]) errs[r] = mnenc_last_error();
+    };
+    std::vector<std::thread> threads;
+    for (int r = 1; r < nr; ++r) threads.emplace_back(work, r);
+    work(0);
+    for (auto& th : threads) th.join();
+    for (int r = 0; r < nr; ++r)
+        if (rcs[r]) {
+            for (uint8_t* p : outs) resultRelease(p);
+            return fail(rcs[r], "GPU " + std::to_string(ranks[r]->device) + ": " + errs[r]);
+        }
+    *out = outs[0];
+    *outBytes = sizes[0];
+    return MNENC_OK;
+}
+
+}  // namespace mnenc

@@ -216,3 +216,68 @@ def encodeImageStripes(imgIn, context: CompressionContextFast, comm, width: Opti
     if rank != 0:
         return None
     return MnBuffer(out, n.value) if zero_copy else _take(out, n.value)
+
+
+# ---- exchanges inside the library (NCCL, csrc/stripe_comm.cu) ----------------------------------------------------------
+STRIPE_PHASES = ("begin", "x_sizes", "rle", "x_runs", "histogram", "x_histogram", "tables", "x_offsets", "pack", "x_segments", "finish")
+
+
+def initStripeComm(context: CompressionContextFast, group=None) -> Tuple[int, int]:
+    """Gives ``context`` an NCCL communicator of its own (mnenc_comm_init_rank) over the ranks of a torch.distributed group:
+    the 128-byte NCCL id is made on rank 0 and broadcast through the group - the only use of torch here. Returns (rank, world)."""
+    import torch
+    import torch.distributed as dist
+    L = _lib.load()
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    ident = np.zeros(128, np.uint8)
+    if rank == 0:
+        _lib.check(L.mnenc_comm_unique_id(ident.ctypes.data_as(_vp)))
+    t = torch.from_numpy(ident)
+    if dist.get_backend(group) == "nccl":
+        t = t.cuda(context.device)
+    dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    ident = t.cpu().numpy()
+    _lib.check(L.mnenc_comm_init_rank(context._h, rank, world, ident.ctypes.data_as(_vp)))
+    context._stripe_rank, context._stripe_world = rank, world
+    return rank, world
+
+
+def encodeImageStriped(imgIn, context: CompressionContextFast, width: Optional[int] = None, timings: Optional[dict] = None,
+                       zero_copy: bool = False):
+    """compressed::encodeImageFast (CompressedImage.cpp:578-633) of ONE image over all ranks of the context's communicator
+    (initStripeComm), every exchange done by the library itself over NCCL (mnenc_encode_striped_rgb8). Arguments as
+    encodeImageStripes. Returns the `.mn` bytes on rank 0, None elsewhere."""
+    L = _lib.load()
+    rank, world = context._stripe_rank, context._stripe_world
+    is_np = isinstance(imgIn, np.ndarray)
+    on_device = (not is_np) and imgIn.is_cuda
+    if is_np:
+        if imgIn.dtype != np.uint8 or imgIn.ndim != 3 or imgIn.shape[2] != 3:
+            raise ValueError("expected HxWx3 uint8")
+        if imgIn.strides[2] != 1 or imgIn.strides[1] != 3:
+            imgIn = np.ascontiguousarray(imgIn)
+        h, w_in = imgIn.shape[:2]
+        base, stride = imgIn.ctypes.data, imgIn.strides[0]
+    else:
+        if str(imgIn.dtype) != "torch.uint8" or imgIn.dim() != 3 or imgIn.shape[2] != 3 or not imgIn.is_contiguous():
+            raise ValueError("expected contiguous HxWx3 uint8")
+        h, w_in = int(imgIn.shape[0]), int(imgIn.shape[1])
+        base, stride = imgIn.data_ptr(), 3 * w_in
+    if on_device and width is None:
+        raise ValueError("a device stripe needs the full image width")
+    w = int(width) if width is not None else w_in
+    bx0, bx1 = stripeColumns((w + 7) // 8, world)[rank]
+    stripe_only = width is not None  # the tensor holds just this rank's block columns
+    if stripe_only and w_in != min(8 * bx1, w) - 8 * bx0:
+        raise ValueError("tensor is not this rank's stripe")
+    ptr = base if stripe_only else base + 3 * 8 * bx0
+    out, n = _vp(), C.c_size_t()
+    _lib.check(L.mnenc_encode_striped_rgb8(context._h, _vp(ptr), int(on_device), w, h, stride, bx0, bx1, C.byref(out), C.byref(n)))
+    if timings is not None:
+        ms = np.zeros(16, np.float32)
+        _lib.check(L.mnenc_last_stripe_timing(context._h, ms.ctypes.data_as(_vp)))
+        for name, v in zip(STRIPE_PHASES, ms):
+            timings[name] = timings.get(name, 0.0) + float(v) / 1e3
+    if rank != 0:
+        return None
+    return MnBuffer(out, n.value) if zero_copy else _take(out, n.value)

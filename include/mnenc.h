@@ -85,7 +85,7 @@ int mnenc_encode_batch_rgb8(mnenc_t* ctx, size_t n_images, const uint8_t* const*
  *   std::unique_ptr<image<rgb>> compressed::decodeImageFast(const uint8_t bytes[], size_t byteSize)
  *       CompressionLib/inc/CompressedImage.h:75, CompressionLib/src/CompressedImage.cpp:837-889
  * (readCompressedFast :709-782, huffmanDecode Huffman.cpp:173-244, runLengthDecode :281-307, readGolombCode
- * BitBuffer.cpp:243-258, FromCoeffsDynamicFast MatchingPursuit.cpp:152-169, RGBFromYUV misc.cpp:28-36).
+ * BitBuffer.cpp:243-258, FromCoeffsDynamicFast MatchingPursuit.cpp:130-147, RGBFromYUV misc.cpp:28-36).
  *   mn, mn_bytes: the stream, host memory. The quantisation tables are the stream's; the dictionary is the context's
  *                 (the reference rebuilds it in readCompressedFast :726 — same floats by construction);
  *                 K of the stream may differ from the context's.
@@ -145,6 +145,10 @@ int mnenc_pack_symbols(mnenc_t* ctx, size_t width, size_t height, const uint16_t
 int mnenc_last_timing(mnenc_t* ctx, float* ms8);
 /* Algorithmic work of the last encode: flops of the matching pursuit, symbols, payload bits. */
 int mnenc_last_work(mnenc_t* ctx, double* mp_flops, uint64_t* n_symbols, uint64_t* n_bits);
+/* Choices of compressed::writeHuffmanOrGolomb (CompressedImage.cpp:359-390) and of the run-length test (:508-516) in the last
+ * single-image encode: coded sequences (`lengths` + 6K streams) written with a Huffman table / as Golomb codes, and symbol
+ * streams that were run-length coded first. */
+int mnenc_last_plan(mnenc_t* ctx, int* n_huffman, int* n_golomb, int* n_rle);
 
 /*
  * Host-logic test hook (used by the CPU-only tests; never called by the encode entry points): runs the host
@@ -187,6 +191,34 @@ int mnenc_stripe_histogram(mnenc_t* ctx, const uint32_t* all_rec2, void** hist_d
 int mnenc_stripe_plan(mnenc_t* ctx, uint64_t* seq_bits);
 int mnenc_stripe_pack(mnenc_t* ctx, const uint64_t* all_seq_bits, void** out_dev, size_t* out_words, size_t* out_bytes);
 int mnenc_stripe_finish(mnenc_t* ctx, uint8_t** out, size_t* out_bytes);
+
+/*
+ * Stripes with the exchanges INSIDE the library (NCCL over NVLink / NVSwitch, loaded at run time from libnccl.so.2; SURVEY.md
+ * §8b "multi-GPU handled inside the context"). Replaces compressed::encodeImageFast (CompressedImage.cpp:578-633) for the
+ * reference-side callers (Compression.cpp:117-123) when one image is to be spread over the GPUs of a box.
+ *
+ * One process per GPU: one rank calls mnenc_comm_unique_id and hands the 128 bytes to the others (any transport), every rank
+ * calls mnenc_comm_init_rank on its context, then all ranks call mnenc_encode_striped_rgb8 collectively with their block
+ * columns [bx0, bx1) (arguments as mnenc_stripe_begin). Rank 0 receives the complete `.mn` stream (mnenc_free it), the others
+ * *out = NULL. The result is byte-identical to mnenc_encode_rgb8 of the whole image on one GPU.
+ * mnenc_last_stripe_timing: host milliseconds of the last striped encode on this rank — ms[0] begin (H2D, matching pursuit,
+ * scatter), [1] gather of sizes, [2] DC + runs, [3] gather of run records, [4] stitched RLE + local histogram, [5] histogram
+ * exchange (sparse all-gather + merge), [6] code tables (dealt over the ranks) + payload bits, [7] offset scan gather,
+ * [8] pack, [9] reduce of the segments to rank 0, [10] D2H + headers on rank 0.
+ */
+int mnenc_comm_unique_id(uint8_t* id128);
+int mnenc_comm_init_rank(mnenc_t* ctx, int rank, int nranks, const uint8_t* id128);
+int mnenc_comm_destroy(mnenc_t* ctx);
+int mnenc_encode_striped_rgb8(mnenc_t* ctx, const uint8_t* rgb_stripe, int on_device, size_t width, size_t height,
+                              size_t row_stride_bytes, uint32_t bx0, uint32_t bx1, uint8_t** out, size_t* out_bytes);
+int mnenc_last_stripe_timing(mnenc_t* ctx, float* ms16);
+/*
+ * One process, several GPUs: a context over n_devices GPUs (ncclCommInitAll), dictionary arguments as mnenc_create.
+ * mnenc_set_quant reaches every GPU; mnenc_encode_rgb8 on such a context shards the host image by block columns over the GPUs
+ * (one host thread per GPU) and returns the same bytes as a single-GPU context. mnenc_destroy releases all of it.
+ */
+int mnenc_create_multi(mnenc_t** out, const int* devices, int n_devices, int K, int block_size, const float* base_rowmajor, int n_base,
+                       const int32_t* detail_rows, const float* detailY, const float* detailU, const float* detailV);
 
 /*
  * Host-logic test hooks of the stripe path (used by the CPU-only world_size-2/3 gloo tests): run stitching of

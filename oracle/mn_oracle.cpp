@@ -511,7 +511,7 @@ uint8_t* mno_encode(void* h, const uint8_t* rgb, size_t w, size_t hgt, size_t st
 
 // ---------------------------------------------------------------------------------------------------
 // Decoder: restates readCompressedFast (CompressedImage.cpp:709-782), decodeImageFast (:837-889),
-// FromCoeffsDynamicFast (MatchingPursuit.cpp:152-169), huffmanDecode (Huffman.cpp:173-244), runLengthDecode (:281-307),
+// FromCoeffsDynamicFast (MatchingPursuit.cpp:130-147), huffmanDecode (Huffman.cpp:173-244), runLengthDecode (:281-307),
 // readGolombCode / readEliasFanoSequenceCode (BitBuffer.cpp:243-258, 319-343), RGBFromYUV (ImageHelper/src/misc.cpp:28-36).
 // Pinned against the reference's own reader/decoder in tests/test_oracle.py (symbols and pixels, bit-exact).
 // ---------------------------------------------------------------------------------------------------
@@ -748,7 +748,7 @@ int mno_decode(void* h, const uint8_t* bytes, size_t n, uint8_t** rgbOut, size_t
                     const int count = P.lengths.at(lengthOffset++);
                     float* r = dec.data() + ch * N;
                     std::fill(r, r + N, 0.0f);
-                    // FromCoeffsDynamicFast (MatchingPursuit.cpp:152-169) on the dictionary dynamicBasisFast builds from ALL `count`
+                    // FromCoeffsDynamicFast (MatchingPursuit.cpp:130-147) on the dictionary dynamicBasisFast builds from ALL `count`
                     // picks (CompressedImage.cpp:252-289): base atoms, then the detail group of every pick < nBase, in pick order.
                     int choice = 0;
                     std::vector<int> groups;

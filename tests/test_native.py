@@ -1,5 +1,5 @@
 """Host builds of header-only pieces of the library, run as small native programs (tests/native/*.cpp):
-  * csrc/word_acc.h — the per-thread bit accumulator and sequence walk of the MNENC_PACK=2/3 pack kernels — against a bit-by-bit
+  * csrc/word_acc.h — the per-thread bit accumulator and sequence walk of the pack kernels — against a bit-by-bit
     MSB-first writer (BitBuffer::WriteBits, BitBuffer.cpp:78-110; writeGolombCode, :228-241) and the slow definition of the walk;
   * csrc/host_pool.h — exceptions thrown by jobs reach the caller, never std::terminate, the pool stays usable;
   * csrc/spin_team.h — the decoder's spinning helper team under oversubscription: no index of a job is ever lost."""

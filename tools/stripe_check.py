@@ -1,4 +1,5 @@
-"""torchrun script: the stripe protocol over NCCL, one process per GPU, checked against the single-GPU encode of rank 0.
+"""torchrun script: the stripe protocol over NCCL, one process per GPU, checked against the single-GPU encode of rank 0 - both with
+the exchanges inside the library (mnenc_encode_striped_rgb8, csrc/stripe_comm.cu) and with the caller's transport (TorchComm).
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/stripe_check.py [W H]
 """
@@ -25,26 +26,35 @@ def main():
     rank, world = dist.get_rank(), dist.get_world_size()
     ctx = mn.createCompressionContextFast(32, 8, 3.5, device=local)
     comm = mn.TorchComm()
+    mn.initStripeComm(ctx)
     sizes = [(512, 512), (1023, 77), (8, 8), (4928, 3264)]
     if len(sys.argv) >= 3:
         sizes = [(int(sys.argv[1]), int(sys.argv[2]))]
     for (w, h) in sizes:
         img = synthetic_rgb(w, h, 12345) if w * h <= 4928 * 3264 else np.tile(synthetic_rgb(2048, 2048, 12345), ((h + 2047) // 2048, (w + 2047) // 2048, 1))[:h, :w]
         got = mn.encodeImageStripes(img, ctx, comm)
+        lib = mn.encodeImageStriped(img, ctx)
         dist.barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         got = mn.encodeImageStripes(img, ctx, comm)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
+        dist.barrier()
+        tm = {}
+        t0 = time.perf_counter()
+        lib = mn.encodeImageStriped(img, ctx, timings=tm)
+        dl = time.perf_counter() - t0
         if rank == 0:
             t1 = time.perf_counter()
             want = mn.encodeImageFast(img, ctx)
             d1 = time.perf_counter() - t1
-            assert got == want, f"{w}x{h}: stripe-sharded stream differs from the single-GPU stream"
-            print(f"{w}x{h}: {len(got)} bytes identical over {world} ranks; striped {dt * 1e3:.2f} ms, single GPU {d1 * 1e3:.2f} ms", flush=True)
+            assert got == want, f"{w}x{h}: stripe-sharded stream (caller's transport) differs from the single-GPU stream"
+            assert lib == want, f"{w}x{h}: stripe-sharded stream (exchanges inside the library) differs from the single-GPU stream"
+            print(f"{w}x{h}: {len(got)} bytes identical over {world} ranks; in-library {dl * 1e3:.2f} ms, caller's transport {dt * 1e3:.2f} ms, "
+                  f"single GPU {d1 * 1e3:.2f} ms; phases {({k: round(v * 1e3, 3) for k, v in tm.items()})}", flush=True)
         else:
-            assert got is None
+            assert got is None and lib is None
         dist.barrier()
     if rank == 0:
         print("stripe_check OK", flush=True)
