@@ -58,8 +58,7 @@ cudaError_t launchMatchingPursuitTeams(const MpParams& p, int numSMs, cudaStream
 // round of kernels, so that dictionary tiles are shared by whole tiles of block-channels instead of being streamed
 // once per block-channel.
 // ------------------------------------------------------------------------------------------------
-constexpr int kCandPerQuarter = 4;       // base-atom candidate slots per 128-atom quarter of the base scan
-constexpr int kCandSlots = 4 * kCandPerQuarter;
+constexpr int kCandSlots = 8;            // base-atom candidate slots per block-channel (more candidates: overflow queue)
 constexpr int kCandSlotsDetail = 4;      // candidate slots for rows of the appended KLT groups
 constexpr uint32_t kWaveNone = 0xFFFFFFFFu;
 constexpr int kWaveTile = 128;           // block-channels per MMA tile (M of tcgen05.mma)

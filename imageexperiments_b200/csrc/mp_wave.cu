@@ -55,7 +55,7 @@ __device__ __noinline__ void queueOverflow(const WaveParams& p, uint32_t bc, uin
 // Thread-local candidate collector: the scan loops only fill registers (no memory round trip, no divergent atomics); the
 // candidates leave the thread in one convergent step after the loop.
 struct CandLocal {
-    uint32_t c[kCandPerQuarter];
+    uint32_t c[kCandSlotsDetail];
     int n = 0;
     __device__ __forceinline__ void add(const WaveParams& p, uint32_t bc, uint32_t idx, uint32_t rowId) {
         const uint32_t code = idx | (rowId << 12);
@@ -158,43 +158,80 @@ __global__ void __launch_bounds__(256) waveInitKernel(const __grid_constant__ Wa
 }
 
 // ------------------------------------------------------------------------------------------------
-// Base scores. 288 threads: two groups of four scanning warps + one MMA-issuing warp; 2 CTAs per SM (256 TMEM columns each).
-// The 512 dictionary rows are scored in four quarters of 128 atoms (N = 128 per tcgen05.mma) that ping-pong between two
-// 128-column TMEM buffers: while group A (warps 0-3) scans quarter 0 in buffer 0, the tensor core fills buffer 1 with quarter
-// 1 for group B (warps 4-7), and so on. A thread owns ONE block-channel (TMEM lane) for a whole quarter: maximum, threshold
-// and candidate filter are thread-local, and nothing in the tile loop is a CTA-wide barrier - only mbarriers between the MMA
-// warp and a scanning group. The residual rows of the NEXT tile are fetched into registers between the two quarters of a
-// group and stored to the other operand buffer after the second, so their latency hides behind the scans.
+// Base scores. 256 threads = two independent groups of four warps, 2 CTAs per SM (256 TMEM columns each, 128 per group).
+// A group owns a tile of 128 active block-channels: thread t of the group stages residual row t (cp.async straight into the
+// canonical operand image), and later scans TMEM lane t, i.e. the scores of ITS block-channel, so block-channel index and
+// eps never leave the thread's registers. The 512 dictionary rows are scored in eight parts of 64 atoms (N = 64 per
+// tcgen05.mma) that ping-pong between the group's two 64-column TMEM buffers: while the group scans part e, the tensor core
+// fills the other buffer with part e + 1. One thread sees the eight parts of its block-channel in ascending atom order, so
+// its threshold (running maximum - 2 eps) is that of a sequential scan, and nothing in the loop is a CTA-wide barrier:
+// mbarriers between the group's issuing warp and its four warps, one 128-thread named barrier per tile. The next tile's rows
+// are fetched during the scan of the last part.
+// Candidates go straight to the block-channel's slots (plain stores, the thread is their only writer). A part whose maximum
+// exceeds the running maximum by more than 2 eps makes every earlier candidate stale (their scores are below the new
+// threshold): the slot counter restarts at 0, which keeps the list at the candidates of the final threshold plus near-ties.
 // ------------------------------------------------------------------------------------------------
-constexpr int kBaseThreads = 288;
+constexpr int kBaseThreads = 256;
+constexpr uint32_t kPartAtoms = 64, kParts = 8;
 struct __align__(1024) BaseSmem {
     __half D16[kRowsPad * kN];                    // 64 KB base dictionary image (B operand)
-    alignas(1024) __half A[2][kWaveTile * kN];    // 2 x 16 KB residual tiles (A operand), canonical K-major images
-    uint32_t bc[2][kWaveTile];
-    float eps[2][kWaveTile];
-    unsigned long long mbarDict, aFull[2], bufFull[2], bufFree[2];
+    alignas(1024) __half A[2][kWaveTile * kN];    // one 16 KB residual tile (A operand) per group, canonical K-major image
+    unsigned long long mbarDict, full[2][2], free_[2][2];
     uint32_t tmemBase;
 };
+
+__device__ __forceinline__ void groupBarrier(int g) {  // immediate barrier ids: a register id makes ptxas reserve all 16
+    if (g == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+    else asm volatile("bar.sync 2, 128;" ::: "memory");
+}
+
+// candidates of one 32-column chunk held in registers
+__device__ __forceinline__ void filterChunk(const WaveParams& p, const uint32_t (&raw)[32], float thr, int atom0, uint32_t bc, uint32_t* slots, int& n) {
+#pragma unroll
+    for (int gq = 0; gq < 4; ++gq) {
+        bool any = false;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) any |= fabsf(__uint_as_float(raw[8 * gq + j])) >= thr;
+        if (any) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int atom = atom0 + 8 * gq + j;
+                if (fabsf(__uint_as_float(raw[8 * gq + j])) >= thr && atom < p.nBase) {
+                    const uint32_t code = static_cast<uint32_t>(atom) | (static_cast<uint32_t>(atom) << 12);
+                    if (n < kCandSlots) slots[n] = code;
+                    else queueOverflow(p, bc, code);
+                    ++n;
+                }
+            }
+        }
+    }
+}
 
 __global__ void __launch_bounds__(kBaseThreads, 2) waveBaseKernel(const __grid_constant__ WaveParams p, const int iter) {
     extern __shared__ __align__(1024) unsigned char smemRaw[];
     BaseSmem& s = *reinterpret_cast<BaseSmem*>(smemRaw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = warp >> 2, wq = warp & 3, tg = tid & 127;
     const uint32_t nA = p.nAct[iter];
     const uint32_t ntiles = (nA + kWaveTile - 1) / kWaveTile;
-    if (blockIdx.x >= ntiles) return;
+    if (blockIdx.x * 2u >= ntiles) return;
     const uint32_t* act = p.act[iter & 1];
-    const uint32_t nMine = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;  // tiles blockIdx.x, + gridDim.x, ...
+    const uint32_t firstTile = blockIdx.x * 2u + static_cast<uint32_t>(g), tileStride = gridDim.x * 2u;
 
     if (tid == 0) {
         mbarInit(&s.mbarDict, 1);
-        for (int i = 0; i < 2; ++i) {
-            mbarInit(&s.aFull[i], 8);     // one arrival per scanning warp
-            mbarInit(&s.bufFull[i], 1);   // tcgen05.commit
-            mbarInit(&s.bufFree[i], 4);   // one arrival per warp of the group that read the buffer
-        }
+        for (int i = 0; i < 2; ++i)
+            for (int b = 0; b < 2; ++b) {
+                mbarInit(&s.full[i][b], 1);   // tcgen05.commit
+                mbarInit(&s.free_[i][b], 4);  // one arrival per warp of the group
+            }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        constexpr uint32_t total = kRowsPad * kN * sizeof(__half);
+        mbarExpectTx(&s.mbarDict, total);
+        for (uint32_t o = 0; o < total; o += 32768)
+            bulkCopy(reinterpret_cast<unsigned char*>(s.D16) + o, reinterpret_cast<const unsigned char*>(p.baseUm16) + o, 32768, &s.mbarDict);
     }
+    __syncwarp();
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smemAddr(&s.tmemBase)), "r"(256u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -203,134 +240,106 @@ __global__ void __launch_bounds__(kBaseThreads, 2) waveBaseKernel(const __grid_c
     __syncthreads();
     fenceAfter();
     const uint32_t tmem = s.tmemBase;
+    const uint32_t tcolBase = tmem + (static_cast<uint32_t>(wq * 32) << 16) + static_cast<uint32_t>(g) * 128u;
+    const uint32_t aAddr = smemAddr(s.A[g]);
+    const uint32_t myDst = aAddr + static_cast<uint32_t>(tg >> 3) * kSbo + static_cast<uint32_t>(tg & 7) * 16u;
+    const uint32_t dAddr = smemAddr(s.D16);
 
-    if (warp == 8) {
-        // ================= MMA issuer: the whole warp runs the issue path with warp-uniform operands, one elected lane issues =====
-        if (lane == 0) {
-            constexpr uint32_t total = kRowsPad * kN * sizeof(__half);
-            mbarExpectTx(&s.mbarDict, total);
-            for (uint32_t o = 0; o < total; o += 32768)
-                bulkCopy(reinterpret_cast<unsigned char*>(s.D16) + o, reinterpret_cast<const unsigned char*>(p.baseUm16) + o, 32768, &s.mbarDict);
-        }
-        __syncwarp();
-        mbarWait(&s.mbarDict, 0);
-        const uint32_t dAddr = warpUniform(smemAddr(s.D16));
-        const uint32_t tm = warpUniform(tmem);
-        for (uint32_t i = 0; i < nMine; ++i) {
-            const uint32_t ab = i & 1u;
-            mbarWait(&s.aFull[ab], (i >> 1) & 1u);
-            const unsigned long long descA = umDesc(warpUniform(smemAddr(s.A[ab])), kLbo, kSbo);
-#pragma unroll 1
-            for (uint32_t k = 0; k < 4; ++k) {
-                const uint32_t b = k & 1u, use = 2u * i + (k >> 1);  // use number of TMEM buffer b
-                if (use) mbarWait(&s.bufFree[b], (use - 1u) & 1u);
-                fenceAfter();
-                const unsigned long long descB = umDesc(dAddr + k * 128u * 128u, kLbo, kSbo);
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks)
-                    ummaF16Elect(tm + b * 128u, descA + ((ks * kKStep) >> 4), descB + ((ks * kKStep) >> 4), idescF16(128, 128), ks ? 1u : 0u);
-                ummaCommitElect(&s.bufFull[b]);
-            }
-        }
-    } else {
-        // ================= scanning groups =================
-        const int g = warp >> 2, q = warp & 3;     // group (TMEM buffer), lane quarter
-        const int slot = q * 32 + lane;
-        const int tg = tid & 127;                  // thread within the group
-        const uint32_t laneBase = static_cast<uint32_t>(q * 32) << 16;
-        const int myRow = 64 * g + (tg & 63), myPair = tg >> 6;  // operand rows this thread fetches: pairs myPair and myPair + 2
-        unsigned nCandStat = 0;
+    if (firstTile < ntiles) {
         uint32_t bcN = kWaveNone;
-        uint4 v[4];
         float epsN = 0.0f;
         auto loadIndex = [&](uint32_t tile) {
-            const uint32_t e = tile * kWaveTile + static_cast<uint32_t>(myRow);
+            const uint32_t e = tile * kWaveTile + static_cast<uint32_t>(tg);
             bcN = e < nA ? __ldg(act + e) : kWaveNone;
         };
-        auto loadRows = [&]() {
-            v[0] = v[1] = v[2] = v[3] = make_uint4(0u, 0u, 0u, 0u);
-            epsN = 0.0f;
-            if (bcN != kWaveNone) {
-                const uint4* src = reinterpret_cast<const uint4*>(p.res16 + static_cast<size_t>(bcN) * kN);
-                v[0] = __ldg(src + 2 * myPair), v[1] = __ldg(src + 2 * myPair + 1);
-                v[2] = __ldg(src + 2 * myPair + 4), v[3] = __ldg(src + 2 * myPair + 5);
-                epsN = __uint_as_float(p.state[bcN].z);
+        auto fetchRow = [&]() {  // residual row -> canonical image: chunk c of row r at (r / 8) * SBO + c * LBO + (r % 8) * 16
+            const bool has = bcN != kWaveNone;
+            const unsigned char* src = reinterpret_cast<const unsigned char*>(p.res16 + static_cast<size_t>(has ? bcN : 0u) * kN);
+            const uint32_t bytes = has ? 16u : 0u;  // src-size 0: the 16 bytes are zero-filled
+#pragma unroll
+            for (uint32_t c = 0; c < 8; ++c)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(myDst + c * kLbo), "l"(src + 16u * c), "r"(bytes) : "memory");
+            epsN = has ? __uint_as_float(p.state[bcN].z) : 0.0f;
+        };
+        // issue number j of buffer b (j = 0, 1, ...): waits for the group's j-th release of b, commits to full[g][b]
+        uint32_t issued0 = 0u, issued1 = 0u;
+        auto issuePart = [&](uint32_t e) {  // warp wq == 0 only, converged
+            const uint32_t b = e & 1u;
+            const uint32_t issued = b ? issued1 : issued0;
+            if (issued) mbarWait(&s.free_[g][b], (issued - 1u) & 1u);
+            if (b) ++issued1;
+            else ++issued0;
+            fenceAfter();
+            const unsigned long long descA = umDesc(warpUniform(aAddr), kLbo, kSbo);
+            const unsigned long long descB = umDesc(warpUniform(dAddr + e * kPartAtoms * 128u), kLbo, kSbo);
+            const uint32_t tm = warpUniform(tmem + static_cast<uint32_t>(g) * 128u + b * kPartAtoms);
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks)
+                ummaF16Elect(tm, descA + ((ks * kKStep) >> 4), descB + ((ks * kKStep) >> 4), idescF16(128, kPartAtoms), ks ? 1u : 0u);
+            ummaCommitElect(&s.full[g][b]);
+        };
+        auto publishTile = [&]() {  // rows landed -> visible to the tensor core -> first two parts in flight
+            asm volatile("cp.async.wait_all;" ::: "memory");
+            fenceProxyAsync();
+            groupBarrier(g);
+            if (wq == 0) {
+                issuePart(0);
+                issuePart(1);
             }
         };
-        auto storeRows = [&](uint32_t ab) {
-            unsigned char* d = reinterpret_cast<unsigned char*>(s.A[ab]) + (myRow >> 3) * kSbo + (2 * myPair) * kLbo + (myRow & 7) * 16;
-            *reinterpret_cast<uint4*>(d) = v[0];
-            *reinterpret_cast<uint4*>(d + kLbo) = v[1];
-            *reinterpret_cast<uint4*>(d + 4 * kLbo) = v[2];
-            *reinterpret_cast<uint4*>(d + 5 * kLbo) = v[3];
-            if (myPair == 0) s.bc[ab][myRow] = bcN, s.eps[ab][myRow] = epsN;
-            fenceProxyAsync();
-            __syncwarp();
-            if (lane == 0) mbarArrive(&s.aFull[ab]);
-        };
-        loadIndex(blockIdx.x);
-        loadRows();
-        storeRows(0);
-        for (uint32_t i = 0; i < nMine; ++i) {
-            const uint32_t ab = i & 1u;
-            const bool more = i + 1 < nMine;
-            mbarWait(&s.aFull[ab], (i >> 1) & 1u);  // also makes the other warps' bc / eps entries visible
-            const uint32_t myBc = s.bc[ab][slot];
-            const float eps = s.eps[ab][slot];
-            if (more) loadIndex(blockIdx.x + (i + 1) * gridDim.x);
+        loadIndex(firstTile);
+        fetchRow();
+        if (wq == 0) mbarWait(&s.mbarDict, 0);
+        publishTile();
+        uint32_t scanned0 = 0u, scanned1 = 0u;
+        unsigned nCandStat = 0;
+        for (uint32_t tile = firstTile; tile < ntiles; tile += tileStride) {
+            const uint32_t myBc = bcN;
+            const float eps = epsN;
+            const bool more = tile + tileStride < ntiles;
+            uint32_t* const slots = p.cand + static_cast<size_t>(myBc != kWaveNone ? myBc : 0u) * kCandSlots;
             float mrun = 0.0f;
+            int n = 0;
 #pragma unroll 1
-            for (uint32_t kk = 0; kk < 2; ++kk) {
-                const uint32_t k = static_cast<uint32_t>(g) + 2u * kk;  // quarter of the dictionary: atoms 128 k .. 128 k + 127
-                mbarWait(&s.bufFull[g], (2u * i + kk) & 1u);
+            for (uint32_t e = 0; e < kParts; ++e) {
+                const uint32_t b = e & 1u;
+                mbarWait(&s.full[g][b], (b ? scanned1 : scanned0) & 1u);
+                if (b) ++scanned1;
+                else ++scanned0;
                 fenceAfter();
-                const uint32_t tcol = tmem + laneBase + static_cast<uint32_t>(g) * 128u;
-                float m = 0.0f;
-#pragma unroll 1
-                for (int cc = 0; cc < 4; ++cc) {
-                    uint32_t raw[32];
-                    tmemLoad32(tcol + static_cast<uint32_t>(cc * 32), raw);
+                if (e == kParts - 2 && more) loadIndex(tile + tileStride);
+                if (e == kParts - 1 && more) fetchRow();  // every MMA that reads A[g] has completed: refill it behind this scan
+                const uint32_t tcol = tcolBase + b * kPartAtoms;
+                uint32_t raw[32];
+                tmemLoad32(tcol, raw);
+                float m0 = 0.0f, m1 = 0.0f;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 2) m = fmaxf(m, fmaxf(fabsf(__uint_as_float(raw[j])), fabsf(__uint_as_float(raw[j + 1]))));
-                }
-                mrun = fmaxf(mrun, m);
+                for (int j = 0; j < 32; j += 2) m0 = fmaxf(m0, fmaxf(fabsf(__uint_as_float(raw[j])), fabsf(__uint_as_float(raw[j + 1]))));
+                tmemLoad32(tcol + 32u, raw);
+#pragma unroll
+                for (int j = 0; j < 32; j += 2) m1 = fmaxf(m1, fmaxf(fabsf(__uint_as_float(raw[j])), fabsf(__uint_as_float(raw[j + 1]))));
+                const float mPart = fmaxf(m0, m1);
+                if (mPart - eps > mrun) n = 0;  // every earlier candidate scored <= mrun < the new threshold: stale
+                mrun = fmaxf(mrun, mPart);
                 const float thr = myBc != kWaveNone ? mrun - eps : __int_as_float(0x7F800000);
-                CandLocal cl;
-#pragma unroll 1
-                for (int cc = 0; cc < 4; ++cc) {
-                    uint32_t raw[32];
-                    tmemLoad32(tcol + static_cast<uint32_t>(cc * 32), raw);
-                    const int atom0 = static_cast<int>(k) * 128 + cc * 32;
-#pragma unroll
-                    for (int gq = 0; gq < 4; ++gq) {
-                        bool any = false;
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) any |= fabsf(__uint_as_float(raw[8 * gq + j])) >= thr;
-                        if (any) {
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                const int atom = atom0 + 8 * gq + j;
-                                if (fabsf(__uint_as_float(raw[8 * gq + j])) >= thr && atom < p.nBase)
-                                    cl.add(p, myBc, static_cast<uint32_t>(atom), static_cast<uint32_t>(atom));
-                            }
-                        }
-                    }
+                const int atom0 = static_cast<int>(e * kPartAtoms);
+                if (m1 >= thr) filterChunk(p, raw, thr, atom0 + 32, myBc, slots, n);  // the second chunk is still in registers
+                if (__any_sync(kFullMask, m0 >= thr)) {  // tcgen05.ld is warp-collective: the reload is decided per warp
+                    tmemLoad32(tcol, raw);
+                    if (m0 >= thr) filterChunk(p, raw, thr, atom0, myBc, slots, n);
                 }
                 fenceBefore();
                 __syncwarp();
-                if (lane == 0) mbarArrive(&s.bufFree[g]);  // the tensor core may refill this buffer
-                if (myBc != kWaveNone) {  // sub-list k of the block-channel: plain stores, nobody else writes these slots
-                    uint32_t* slots = p.cand + static_cast<size_t>(myBc) * kCandSlots + kCandPerQuarter * k;
-#pragma unroll
-                    for (int j = 0; j < kCandPerQuarter; ++j)
-                        if (cl.n > j) slots[j] = cl.c[j];
-                    reinterpret_cast<uint8_t*>(p.ncand)[static_cast<size_t>(myBc) * 4 + k] = static_cast<uint8_t>(min(cl.n, kCandPerQuarter));
-                    nCandStat += static_cast<unsigned>(cl.n);
-                }
-                if (kk == 0 && more) loadRows();  // next tile's operand rows: in flight during the second quarter
+                if (lane == 0) mbarArrive(&s.free_[g][b]);
+                __syncwarp();
+                if (wq == 0 && e + 2 < kParts) issuePart(e + 2);
             }
-            if (more) storeRows(ab ^ 1u);  // every MMA that read that buffer (tile i - 1) completed before this tile's first quarter did
-            if (myBc != kWaveNone) atomicMax(&p.amax[myBc], __float_as_uint(mrun));
+            if (more) publishTile();
+            if (myBc != kWaveNone) {
+                p.ncand[myBc] = static_cast<uint32_t>(min(n, kCandSlots));
+                p.amax[myBc] = __float_as_uint(mrun);
+                nCandStat += static_cast<unsigned>(n);
+            }
         }
         nCandStat = __reduce_add_sync(kFullMask, nCandStat);
         if (lane == 0 && nCandStat) atomicAdd(&p.stats[2], static_cast<unsigned long long>(nCandStat));
@@ -491,6 +500,7 @@ __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant
     uint32_t mmaPhase = 0, bPhase = 0;
     int curBin = -1;
     bool bPending = false;
+    unsigned nDetStat = 0;
 
     for (uint32_t tile = blockIdx.x; tile < nT; tile += gridDim.x) {
         // bin of this tile: the last bin whose first tile is <= tile (empty bins have equal starts and are skipped)
@@ -574,8 +584,8 @@ __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant
             }
         }
         if (cl.n) {  // one atomic per thread with candidates, after the scan
-            atomicAdd(&p.stats[4], static_cast<unsigned long long>(cl.n));  // diagnostics
-            const uint32_t take = static_cast<uint32_t>(min(cl.n, kCandPerQuarter));
+            nDetStat += static_cast<unsigned>(cl.n);
+            const uint32_t take = static_cast<uint32_t>(min(cl.n, kCandSlotsDetail));
             const uint32_t pos = atomicAdd(&p.ncandDetail[bc], take);
             uint32_t* slots = p.candDetail + static_cast<size_t>(bc) * kCandSlotsDetail;
             for (uint32_t j = 0; j < take; ++j) {
@@ -586,6 +596,8 @@ __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant
         fenceBefore();
         __syncthreads();
     }
+    nDetStat = __reduce_add_sync(kFullMask, nDetStat);
+    if ((tid & 31) == 0 && nDetStat) atomicAdd(&p.stats[4], static_cast<unsigned long long>(nDetStat));  // diagnostics
     fenceBefore();
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(64u) : "memory");
@@ -655,9 +667,9 @@ __global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant
         if (valid) {
             const int ch = static_cast<int>(bc % 3u);
             const uint4 st = p.state[bc];
-            const uint32_t nBaseCand = p.ncand[bc];
+            const uint32_t nBaseCand = min(p.ncand[bc], static_cast<uint32_t>(kCandSlots));
             const uint32_t nDet = min(p.ncandDetail[bc], static_cast<uint32_t>(kCandSlotsDetail));
-            const uint32_t c0 = p.cand[static_cast<size_t>(bc) * kCandSlots + l8], c1 = p.cand[static_cast<size_t>(bc) * kCandSlots + 8 + l8];
+            const uint32_t c0 = p.cand[static_cast<size_t>(bc) * kCandSlots + l8];
             const uint32_t cd = l8 < kCandSlotsDetail ? p.candDetail[static_cast<size_t>(bc) * kCandSlotsDetail + l8] : 0u;
             unsigned long long key = l8 == 0 ? p.best[bc] : 0ULL;
             const int prev = static_cast<int>(st.x & 0xFFFFu), height = static_cast<int>(st.x >> 16);
@@ -666,17 +678,10 @@ __global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant
             const float4 r0 = src[0], r1 = src[1];
             reinterpret_cast<float4*>(myR + 8 * l8)[0] = r0;
             reinterpret_cast<float4*>(myR + 8 * l8)[1] = r1;
-            // compact list of the block-channel's candidates: base slot s is valid when (s % 4) < count of quarter s / 4
-            const bool v0 = static_cast<uint32_t>(l8 & 3) < ((nBaseCand >> (8 * (l8 >> 2))) & 0xFFu);
-            const bool v1 = static_cast<uint32_t>(l8 & 3) < ((nBaseCand >> (8 * (2 + (l8 >> 2)))) & 0xFFu);
-            const bool vd = static_cast<uint32_t>(l8) < nDet;
-            const unsigned m0 = (__ballot_sync(groupMask, v0) >> leaderLane) & 0xFFu, m1 = (__ballot_sync(groupMask, v1) >> leaderLane) & 0xFFu;
-            const unsigned md = (__ballot_sync(groupMask, vd) >> leaderLane) & 0xFFu;
-            const unsigned below = (1u << l8) - 1u;
-            const int n0 = __popc(m0), n1 = __popc(m1), nCand = n0 + n1 + __popc(md);
-            if (v0) sCand[grp][__popc(m0 & below)] = c0;
-            if (v1) sCand[grp][n0 + __popc(m1 & below)] = c1;
-            if (vd) sCand[grp][n0 + n1 + __popc(md & below)] = cd;
+            // the block-channel's candidates: base atoms first, then rows of its appended groups
+            const int nCand = static_cast<int>(nBaseCand + nDet);
+            if (static_cast<uint32_t>(l8) < nBaseCand) sCand[grp][l8] = c0;
+            if (static_cast<uint32_t>(l8) < nDet) sCand[grp][nBaseCand + l8] = cd;
             __syncwarp(groupMask);
             for (int r = 0; r < nCand; r += kRowsPerRound) {
                 const int nr = min(kRowsPerRound, nCand - r);
