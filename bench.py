@@ -190,7 +190,7 @@ def stripes_record(ctx, rank, world, local, steps, barrier, max_over_ranks):
 
     import imageexperiments_b200 as mn
     try:
-        mn.initStripeComm(ctx) if world > 1 else _single_rank_comm(ctx)
+        mn.initStripeComm(ctx)
         bx0, bx1 = mn.stripeColumns((SW + 7) // 8, world)[rank]
         stripe = stripe_image_columns(8 * bx0, min(8 * bx1, SW))
         dev = torch.from_numpy(stripe).cuda()
@@ -254,18 +254,6 @@ def stripes_record(ctx, rank, world, local, steps, barrier, max_over_ranks):
         return rec
     except Exception as e:  # noqa: BLE001
         return {"error": repr(e)} if rank == 0 else None
-
-
-def _single_rank_comm(ctx):
-    """N = 1: the same in-library path over a one-rank communicator."""
-    import ctypes as C
-
-    from imageexperiments_b200 import _lib
-    L = _lib.load()
-    ident = np.zeros(128, np.uint8)
-    _lib.check(L.mnenc_comm_unique_id(ident.ctypes.data_as(C.c_void_p)))
-    _lib.check(L.mnenc_comm_init_rank(ctx._h, 0, 1, ident.ctypes.data_as(C.c_void_p)))
-    ctx._stripe_rank, ctx._stripe_world = 0, 1
 
 
 def quality_sweep_record(ctx, tensor_peak):

@@ -68,8 +68,16 @@ Image loadPpm(const std::string& path) {
     };
     if (field() != "P6") die(path + ": not a binary PPM (P6)");
     Image im;
-    const long w = std::atol(field().c_str()), h = std::atol(field().c_str()), maxv = std::atol(field().c_str());
-    if (w <= 0 || h <= 0 || maxv != 255) die(path + ": unsupported PPM header (need 8-bit RGB)");
+    auto number = [&](long limit) {  // a decimal field with nothing after the digits, 1 .. limit
+        const std::string tok = field();
+        if (tok.empty() || tok.size() > 7 || tok.find_first_not_of("0123456789") != std::string::npos) die(path + ": malformed PPM header");
+        const long v = std::atol(tok.c_str());
+        if (v <= 0 || v > limit) die(path + ": unsupported PPM header (need 8-bit RGB, sides up to 2^20)");
+        return v;
+    };
+    const long w = number(1L << 20), h = number(1L << 20), maxv = number(255);
+    if (maxv != 255) die(path + ": unsupported PPM header (need 8-bit RGB)");
+    if (static_cast<unsigned long long>(w) * static_cast<unsigned long long>(h) > (1ULL << 32)) die(path + ": image too large");
     f.get();  // the single whitespace after maxval
     im.w = static_cast<size_t>(w), im.h = static_cast<size_t>(h);
     im.px.resize(im.w * im.h * 3);
@@ -83,6 +91,8 @@ void savePpm(const std::string& path, const uint8_t* px, size_t w, size_t h) {
     if (!f) die("cannot write " + path);
     f << "P6\n" << w << " " << h << "\n255\n";
     f.write(reinterpret_cast<const char*>(px), static_cast<std::streamsize>(w * h * 3));
+    f.flush();
+    if (!f) die("write failed: " + path);
 }
 
 std::vector<uint8_t> loadFile(const std::string& path) {
@@ -202,6 +212,8 @@ int main(int argc, char* argv[]) {
         std::ofstream out(argv[4], std::ios::out | std::ios::trunc | std::ios::binary);
         if (!out) die(std::string("cannot write ") + argv[4]);
         out.write(reinterpret_cast<const char*>(bytes), static_cast<std::streamsize>(n));
+        out.flush();
+        if (!out) die(std::string("write failed: ") + argv[4]);
         mnenc_free(bytes);
         mnenc_destroy(ctx);
     } else if (mode == "-d") {

@@ -7,9 +7,9 @@ process group).
 from .compressed import (calculatePSNR, CompressionContextFast, MnBuffer, createCompressionContextFast, createQuantizationTables, encodeImageBatch, encodeImageFast,
                          decodeImageBatch, decodeImageFast, parseStream, streamInfo, lastSymbols, packSymbols, planSequenceHost)
 from .dictionary import Dictionary
-from .stripes import TorchComm, ThreadComm, encodeImageStripes, encodeImageStriped, initStripeComm, stripeColumns
+from .stripes import STRIPE_PHASES, TorchComm, ThreadComm, encodeImageStripes, encodeImageStriped, initStripeComm, stripeColumns
 from ._lib import MnencError
 
 __all__ = ["calculatePSNR", "CompressionContextFast", "MnBuffer", "createCompressionContextFast", "createQuantizationTables", "encodeImageFast", "encodeImageBatch", "decodeImageBatch", "decodeImageFast", "parseStream", "streamInfo", "lastSymbols",
-           "packSymbols", "planSequenceHost", "Dictionary", "MnencError", "TorchComm", "ThreadComm", "encodeImageStripes", "encodeImageStriped", "initStripeComm",
+           "packSymbols", "planSequenceHost", "Dictionary", "MnencError", "TorchComm", "ThreadComm", "encodeImageStripes", "encodeImageStriped", "initStripeComm", "STRIPE_PHASES",
            "stripeColumns"]

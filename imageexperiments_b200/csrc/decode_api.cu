@@ -15,14 +15,29 @@ using namespace mnenc;
 
 namespace {
 
+constexpr size_t kMaxDecodePairsBytes = size_t(8) << 30;
+
 struct DecodeMisc {  // pinned: uploaded tables, downloaded error flag
     float quant[3 * kMaxK];
     unsigned int error;
 };
 
+int decodeImageBody(mnenc_ctx* c, const uint8_t* mn, size_t mnBytes, uint8_t* rgbDev, size_t capacity, size_t stride, uint8_t** hostOut,
+                    size_t* widthOut, size_t* heightOut);
+
+// Every failure leaves through here: copies from the context's pinned buffers may still be queued on the stream, and the next
+// call on the context rewrites (or reallocates) those buffers - so a failed call drains the stream before it returns.
 int decodeImage(mnenc_ctx* c, const uint8_t* mn, size_t mnBytes, uint8_t* rgbDev, size_t capacity, size_t stride, uint8_t** hostOut,
                 size_t* widthOut, size_t* heightOut) {
     if (!c || !mn || !widthOut || !heightOut) return fail(MNENC_ERR_ARG, "null argument");
+    const int rc = decodeImageBody(c, mn, mnBytes, rgbDev, capacity, stride, hostOut, widthOut, heightOut);
+    if (rc != MNENC_OK && c->stream) cudaStreamSynchronize(c->stream);
+    return rc;
+}
+
+int decodeImageBody(mnenc_ctx* c, const uint8_t* mn, size_t mnBytes, uint8_t* rgbDev, size_t capacity, size_t stride, uint8_t** hostOut,
+                    size_t* widthOut, size_t* heightOut) {
+    NvtxRange nvtxRange("mnenc:decode");
     static const bool envParallel = [] {
         const char* e = std::getenv("MNENC_DECODE_THREADS");
         return e && std::atoi(e) > 1;
@@ -55,12 +70,15 @@ int decodeImage(mnenc_ctx* c, const uint8_t* mn, size_t mnBytes, uint8_t* rgbDev
     size_t N = 0;
     BackendBuffers b{};
     const int rcParse = P.withTeam([&]() -> int {
-        CU(c->hDecCounts.ensure(nbc * 2));
+        CU(c->hDecCounts.ensure(nbc * 2 + 16));  // + 16: the `lengths` reader stores 8 bytes at a time
         CU(c->hDecMisc.ensure(sizeof(DecodeMisc)));
         if (P.readLengths(c->hDecCounts.as<uint16_t>(), err)) return fail(MNENC_ERR_STREAM, err);
         t1 = nowMs();
         b.K = K, b.nblocks = static_cast<uint32_t>(nblocks), b.ntiles = static_cast<uint32_t>((nblocks + kTileBlocks - 1) / kTileBlocks);
         CU(c->counts.ensure(nbc * 2));
+        // [block-channel][K] symbol slots: up to 256 bytes of device memory per block-channel for a stream that may spend one bit
+        // on it; the cap keeps a crafted header from demanding more than any real image needs (16384^2 at K = 64 is 3.2 GB)
+        if (nbc * static_cast<size_t>(K) * 4 > kMaxDecodePairsBytes) return fail(MNENC_ERR_ARG, "decoded image too large for this build (symbol slots > 8 GiB)");
         CU(c->pairs.ensure(nbc * static_cast<size_t>(K) * 4));
         CU(c->tileCounts.ensure(static_cast<size_t>(b.ntiles) * 3 * K * 4));
         CU(c->totals.ensure(3 * kMaxK * 4));

@@ -163,6 +163,7 @@ int ensureHistogram(mnenc_ctx* c) {
 
 // Everything after the matching pursuit: counts/pairs (device) -> .mn bytes.
 int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t* outBytes) {
+    NvtxRange nvtxRange("mnenc:backend (RLE, Huffman/Golomb plan, bit packing)");
     const int K = c->K;
     const int nStreams = 6 * K, nSeq = nStreams + 1;
     const uint32_t nbx = static_cast<uint32_t>((width + 7) / 8), nby = static_cast<uint32_t>((height + 7) / 8);
@@ -494,6 +495,7 @@ static int runWavePursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, siz
 }
 
 int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride) {
+    NvtxRange nvtxRange("mnenc:matching_pursuit");
     const uint32_t nbx = static_cast<uint32_t>((width + 7) / 8), nby = static_cast<uint32_t>((height + 7) / 8);
     const uint64_t nbc64 = 3ull * nbx * nby;
     if (nbc64 >= 0x7FFFFFFFull) return fail(MNENC_ERR_ARG, "image too large");

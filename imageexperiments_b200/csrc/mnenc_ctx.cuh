@@ -5,6 +5,7 @@
 
 #include <cuda_runtime.h>
 #include <sched.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include <algorithm>
 #include <chrono>
@@ -30,6 +31,14 @@ int abiCaught() noexcept;                    // inside a catch (...) of a C-ABI 
         cudaError_t e_ = (expr);                                                                                          \
         if (e_ != cudaSuccess) return ::mnenc::fail(MNENC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
     } while (0)
+
+// NVTX range for the timeline tools (Nsight Systems; header-only NVTX 3: a no-op unless a tool is attached)
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 inline double nowMs() {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();

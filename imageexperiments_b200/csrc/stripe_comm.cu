@@ -214,6 +214,7 @@ int reduceSegments(mnenc_ctx* c, void* words, size_t nWords) {
 
 int encodeStriped(mnenc_ctx* c, const uint8_t* rgb, int onDevice, size_t width, size_t height, size_t stride, uint32_t bx0, uint32_t bx1,
                   uint8_t** out, size_t* outBytes) {
+    NvtxRange nvtxRange("mnenc:encode_striped");
     StripeComm* sc = c->comm.get();
     if (!sc) return fail(MNENC_ERR_STATE, "no communicator on this context (mnenc_comm_init_rank / mnenc_create_multi)");
     std::string err;
@@ -363,6 +364,7 @@ namespace mnenc {
 // mnenc_encode_rgb8 on a context made by mnenc_create_multi: one host thread per GPU, each takes its block columns of the
 // host image through the striped encode; the stream comes back from the first GPU.
 int encodeGroup(mnenc_ctx* c, const uint8_t* rgb, size_t width, size_t height, size_t stride, uint8_t** out, size_t* outBytes) {
+    NvtxRange nvtxRange("mnenc:encode_group");
     std::vector<mnenc_ctx*> ranks{c};
     ranks.insert(ranks.end(), c->groupPeers.begin(), c->groupPeers.end());
     const int nr = static_cast<int>(ranks.size());

@@ -224,19 +224,24 @@ STRIPE_PHASES = ("begin", "x_sizes", "rle", "x_runs", "histogram", "x_histogram"
 
 def initStripeComm(context: CompressionContextFast, group=None) -> Tuple[int, int]:
     """Gives ``context`` an NCCL communicator of its own (mnenc_comm_init_rank) over the ranks of a torch.distributed group:
-    the 128-byte NCCL id is made on rank 0 and broadcast through the group - the only use of torch here. Returns (rank, world)."""
+    the 128-byte NCCL id is made on rank 0 and broadcast through the group - the only use of torch here. Without an
+    initialised process group the communicator has this one rank (the same code path, N = 1). Returns (rank, world)."""
     import torch
     import torch.distributed as dist
     L = _lib.load()
-    rank, world = dist.get_rank(group), dist.get_world_size(group)
     ident = np.zeros(128, np.uint8)
-    if rank == 0:
+    if not (dist.is_available() and dist.is_initialized()):
+        rank, world = 0, 1
         _lib.check(L.mnenc_comm_unique_id(ident.ctypes.data_as(_vp)))
-    t = torch.from_numpy(ident)
-    if dist.get_backend(group) == "nccl":
-        t = t.cuda(context.device)
-    dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
-    ident = t.cpu().numpy()
+    else:
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        if rank == 0:
+            _lib.check(L.mnenc_comm_unique_id(ident.ctypes.data_as(_vp)))
+        t = torch.from_numpy(ident)
+        if dist.get_backend(group) == "nccl":
+            t = t.cuda(context.device)
+        dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        ident = t.cpu().numpy()
     _lib.check(L.mnenc_comm_init_rank(context._h, rank, world, ident.ctypes.data_as(_vp)))
     context._stripe_rank, context._stripe_world = rank, world
     return rank, world

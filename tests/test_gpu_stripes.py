@@ -158,3 +158,42 @@ def test_stripes_other_iteration_budget(dictionary, oracle_ctx_factory):
     finally:
         for c in cs:
             c.close()
+
+
+def test_in_library_exchange_single_rank(dictionary, oracle_ctx_factory):
+    """mnenc_encode_striped_rgb8 over a one-rank NCCL communicator: the in-library exchanges (sparse histogram gather + merge,
+    dealt code tables, segment reduce) must reproduce the plain encode byte for byte - host, device and stripe-only inputs."""
+    import torch
+    ctx = mn.createCompressionContextFast(32, 8, 3.5, dictionary=dictionary, device=0)
+    try:
+        assert mn.initStripeComm(ctx) == (0, 1)
+        oc = oracle_ctx_factory(ctx.Quant)
+        for (w, h, seed) in ((512, 512, 1), (1023, 77, 2), (8, 8, 3), (5, 3, 4)):
+            img = synthetic_rgb(w, h, seed)
+            want = oc.encode(img)
+            tm = {}
+            assert mn.encodeImageStriped(img, ctx, timings=tm) == want, (w, h)
+            assert set(tm) == set(mn.STRIPE_PHASES)
+            assert mn.encodeImageStriped(torch.from_numpy(img).cuda(), ctx, width=w) == want, (w, h)
+            assert mn.encodeImageFast(img, ctx) == want  # the context still serves plain encodes in between
+        oc.close()
+    finally:
+        ctx.close()
+
+
+def test_multi_gpu_context(dictionary, oracle_ctx_factory):
+    """mnenc_create_multi: ONE handle over several GPUs of this process (what the shim and the CLI use); plain
+    mnenc_encode_rgb8 calls on it shard the image by block columns. Needs >= 2 GPUs."""
+    import torch
+    n = min(torch.cuda.device_count(), 4)
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    ctx = mn.createCompressionContextFast(32, 8, 3.5, dictionary=dictionary, device=list(range(n)))
+    try:
+        oc = oracle_ctx_factory(ctx.Quant)
+        for (w, h, seed) in ((512, 512, 1), (1023, 77, 2), (8, 8, 3)):
+            img = synthetic_rgb(w, h, seed)
+            assert mn.encodeImageFast(img, ctx) == oc.encode(img), (w, h)
+        oc.close()
+    finally:
+        ctx.close()
