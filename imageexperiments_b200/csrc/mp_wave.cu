@@ -185,23 +185,33 @@ __device__ __forceinline__ void groupBarrier(int g) {  // immediate barrier ids:
     else asm volatile("bar.sync 2, 128;" ::: "memory");
 }
 
-// candidates of one 32-column chunk held in registers
-__device__ __forceinline__ void filterChunk(const WaveParams& p, const uint32_t (&raw)[32], float thr, int atom0, uint32_t bc, uint32_t* slots, int& n) {
+// One 32-column chunk held in registers: running maximum, stale-list reset, and - only if the chunk reaches the threshold - its
+// candidates. The hit mask is built branch-free (the lanes of a warp hit different columns: predicated per-column blocks would
+// all be issued), then the few set bits are walked.
+__device__ __forceinline__ void scanChunk(const WaveParams& p, const uint32_t (&raw)[32], float eps, bool valid, int atom0, uint32_t bc,
+                                          uint32_t* slots, float& mrun, int& n) {
+    float m[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
-    for (int gq = 0; gq < 4; ++gq) {
-        bool any = false;
+    for (int j = 0; j < 32; j += 8)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) any |= fabsf(__uint_as_float(raw[8 * gq + j])) >= thr;
-        if (any) {
+        for (int q = 0; q < 4; ++q) m[q] = fmaxf(m[q], fmaxf(fabsf(__uint_as_float(raw[j + 2 * q])), fabsf(__uint_as_float(raw[j + 2 * q + 1]))));
+    const float mc = fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3]));
+    if (mc - eps > mrun) n = 0;  // every earlier candidate scored <= mrun < the new threshold: stale
+    mrun = fmaxf(mrun, mc);
+    const float thr = mrun - eps;
+    if (valid && mc >= thr) {
+        uint32_t mask = 0u;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int atom = atom0 + 8 * gq + j;
-                if (fabsf(__uint_as_float(raw[8 * gq + j])) >= thr && atom < p.nBase) {
-                    const uint32_t code = static_cast<uint32_t>(atom) | (static_cast<uint32_t>(atom) << 12);
-                    if (n < kCandSlots) slots[n] = code;
-                    else queueOverflow(p, bc, code);
-                    ++n;
-                }
+        for (int j = 0; j < 32; ++j)
+            if (fabsf(__uint_as_float(raw[j])) >= thr) mask |= 1u << j;
+        while (mask) {
+            const int atom = atom0 + __ffs(mask) - 1;
+            mask &= mask - 1u;
+            if (atom < p.nBase) {
+                const uint32_t code = static_cast<uint32_t>(atom) | (static_cast<uint32_t>(atom) << 12);
+                if (n < kCandSlots) slots[n] = code;
+                else queueOverflow(p, bc, code);
+                ++n;
             }
         }
     }
@@ -310,24 +320,13 @@ __global__ void __launch_bounds__(kBaseThreads, 2) waveBaseKernel(const __grid_c
                 if (e == kParts - 2 && more) loadIndex(tile + tileStride);
                 if (e == kParts - 1 && more) fetchRow();  // every MMA that reads A[g] has completed: refill it behind this scan
                 const uint32_t tcol = tcolBase + b * kPartAtoms;
-                uint32_t raw[32];
-                tmemLoad32(tcol, raw);
-                float m0 = 0.0f, m1 = 0.0f;
-#pragma unroll
-                for (int j = 0; j < 32; j += 2) m0 = fmaxf(m0, fmaxf(fabsf(__uint_as_float(raw[j])), fabsf(__uint_as_float(raw[j + 1]))));
-                tmemLoad32(tcol + 32u, raw);
-#pragma unroll
-                for (int j = 0; j < 32; j += 2) m1 = fmaxf(m1, fmaxf(fabsf(__uint_as_float(raw[j])), fabsf(__uint_as_float(raw[j + 1]))));
-                const float mPart = fmaxf(m0, m1);
-                if (mPart - eps > mrun) n = 0;  // every earlier candidate scored <= mrun < the new threshold: stale
-                mrun = fmaxf(mrun, mPart);
-                const float thr = myBc != kWaveNone ? mrun - eps : __int_as_float(0x7F800000);
+                uint32_t raw0[32], raw1[32];
+                tmemLoad32NoWait(tcol, raw0);
+                tmemLoad32NoWait(tcol + 32u, raw1);
+                tmemWaitLd();
                 const int atom0 = static_cast<int>(e * kPartAtoms);
-                if (m1 >= thr) filterChunk(p, raw, thr, atom0 + 32, myBc, slots, n);  // the second chunk is still in registers
-                if (__any_sync(kFullMask, m0 >= thr)) {  // tcgen05.ld is warp-collective: the reload is decided per warp
-                    tmemLoad32(tcol, raw);
-                    if (m0 >= thr) filterChunk(p, raw, thr, atom0, myBc, slots, n);
-                }
+                scanChunk(p, raw0, eps, myBc != kWaveNone, atom0, myBc, slots, mrun, n);
+                scanChunk(p, raw1, eps, myBc != kWaveNone, atom0 + 32, myBc, slots, mrun, n);
                 fenceBefore();
                 __syncwarp();
                 if (lane == 0) mbarArrive(&s.free_[g][b]);
@@ -356,11 +355,19 @@ __global__ void __launch_bounds__(kBaseThreads, 2) waveBaseKernel(const __grid_c
 // with one coalesced load.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) waveBinFillKernel(const __grid_constant__ WaveParams p, const int iter) {
+    // The groups of atoms 0 and nBase-1 have most members (nearly every block-channel picks them): their positions are drawn from
+    // per-CTA counters in shared memory and one global reservation per CTA; all other bins straight from the global cursors, four
+    // independent atomics in flight per thread.
+    __shared__ uint32_t sCnt[6], sBase[6];
+    __shared__ uint8_t sDetRows[kRowsPad];
     const uint32_t nA = p.nAct[iter];
     const uint32_t* act = p.act[iter & 1];
-    const int lane = threadIdx.x & 31;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < kRowsPad; i += 256) sDetRows[i] = p.detRows[i];
     for (uint32_t e0 = blockIdx.x * blockDim.x; e0 < nA; e0 += gridDim.x * blockDim.x) {
-        const uint32_t e = e0 + threadIdx.x;
+        if (tid < 6) sCnt[tid] = 0u;
+        __syncthreads();
+        const uint32_t e = e0 + tid;
         uint32_t bc = 0, ng = 0, epsHalf = 0, thrBase = 0;
         if (e < nA) {
             bc = act[e];
@@ -370,28 +377,54 @@ __global__ void __launch_bounds__(256) waveBinFillKernel(const __grid_constant__
             epsHalf = static_cast<uint32_t>(__half_as_ushort(__float2half_ru(twoEps)));  // rounded UP: never a tighter filter
             thrBase = __float_as_uint(__uint_as_float(p.amax[bc]) - twoEps);
         }
-        uint32_t maxNg = ng;
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) maxNg = max(maxNg, __shfl_xor_sync(kFullMask, maxNg, off));
         const uint32_t ch = bc % 3u;
+        const uint32_t lastAtom = static_cast<uint32_t>(p.nBase - 1);
+        const uint16_t* g = p.groups + static_cast<size_t>(bc) * kMaxK;
         uint32_t first = static_cast<uint32_t>(p.nBase);
-        for (uint32_t gi = 0; gi < maxNg; ++gi) {
-            const bool has = gi < ng;
-            const unsigned active = __ballot_sync(kFullMask, has);
-            if (has) {
-                const uint32_t atom = p.groups[static_cast<size_t>(bc) * kMaxK + gi];
-                const uint32_t bin = ch * static_cast<uint32_t>(p.nBase) + atom;
-                const unsigned peers = __match_any_sync(active, bin);
-                const int leader = __ffs(peers) - 1;
-                uint32_t base = 0;
-                if (lane == leader) base = atomicAdd(&p.binCursor[bin], static_cast<uint32_t>(__popc(peers)));
-                base = __shfl_sync(peers, base, leader);
-                const uint32_t at = p.binOffset[bin] + base + __popc(peers & ((1u << lane) - 1u));
-                p.members[at] = bc | (gi << 27);
-                p.memberInfo[at] = make_uint2(first | (epsHalf << 16), thrBase);
-                first += p.detRows[atom];
+        uint32_t hotRank[2] = {kWaveNone, kWaveNone}, hotRec[2] = {0u, 0u}, hotFirst[2] = {0u, 0u};
+        for (uint32_t g0 = 0; g0 < ng; g0 += 4) {
+            const uint2 gw = *reinterpret_cast<const uint2*>(g + g0);
+            uint32_t pos[4], bin[4], fst[4];
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j) {
+                pos[j] = kWaveNone;
+                if (g0 + j < ng) {
+                    const uint32_t atom = ((j < 2 ? gw.x : gw.y) >> (16 * (j & 1))) & 0xFFFFu;
+                    bin[j] = ch * static_cast<uint32_t>(p.nBase) + atom;
+                    fst[j] = first;
+                    first += sDetRows[atom];
+                    const int hot = atom == 0u ? 0 : (atom == lastAtom ? 1 : -1);
+                    if (hot >= 0 && hotRank[hot] == kWaveNone) {
+                        hotRank[hot] = atomicAdd(&sCnt[2 * ch + hot], 1u);
+                        hotRec[hot] = bc | ((g0 + j) << 27);
+                        hotFirst[hot] = fst[j];
+                    } else {
+                        pos[j] = atomicAdd(&p.binCursor[bin[j]], 1u);
+                    }
+                }
             }
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j)
+                if (pos[j] != kWaveNone) {
+                    const uint32_t at = p.binOffset[bin[j]] + pos[j];
+                    p.members[at] = bc | ((g0 + j) << 27);
+                    p.memberInfo[at] = make_uint2(fst[j] | (epsHalf << 16), thrBase);
+                }
         }
+        __syncthreads();
+        if (tid < 6) {
+            const uint32_t hb = static_cast<uint32_t>(tid >> 1) * static_cast<uint32_t>(p.nBase) + ((tid & 1) ? lastAtom : 0u);
+            sBase[tid] = p.binOffset[hb] + (sCnt[tid] ? atomicAdd(&p.binCursor[hb], sCnt[tid]) : 0u);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int hot = 0; hot < 2; ++hot)
+            if (hotRank[hot] != kWaveNone) {
+                const uint32_t at = sBase[2 * ch + hot] + hotRank[hot];
+                p.members[at] = hotRec[hot];
+                p.memberInfo[at] = make_uint2(hotFirst[hot] | (epsHalf << 16), thrBase);
+            }
+        __syncthreads();
     }
 }
 
@@ -448,33 +481,16 @@ __global__ void __launch_bounds__(1024) waveScanKernel(const __grid_constant__ W
 struct __align__(1024) DetailSmem {
     __half A[kWaveTile * kN];                  // 16 KB residual rows of the tile's members
     alignas(1024) unsigned char B[kImgBytes];  // 8 KB group image
-    uint32_t bc[kWaveTile];
     uint32_t tileStart[3 * kRowsPad + 1];
     uint32_t binOffset[3 * kRowsPad + 1];
     unsigned long long mbarB, mbarMma;
     uint32_t tmemBase;
 };
 
-// rows of res16 (128 B each) -> canonical K-major operand image; item = (row, pair of 16-byte chunks)
-__device__ __forceinline__ void gatherRows(const uint16_t* res16, const uint32_t* sBc, __half* A, int tid, int nthreads) {
-    unsigned char* dst = reinterpret_cast<unsigned char*>(A);
-#pragma unroll 4
-    for (int it = tid; it < kWaveTile * 4; it += nthreads) {
-        const int row = it & (kWaveTile - 1), pair = it >> 7;
-        const uint32_t bc = sBc[row];
-        uint4 v0 = make_uint4(0u, 0u, 0u, 0u), v1 = v0;
-        if (bc != kWaveNone) {
-            const uint4* src = reinterpret_cast<const uint4*>(res16 + static_cast<size_t>(bc) * kN) + 2 * pair;
-            v0 = __ldg(src);
-            v1 = __ldg(src + 1);
-        }
-        unsigned char* d = dst + (row >> 3) * kSbo + (2 * pair) * kLbo + (row & 7) * 16;
-        *reinterpret_cast<uint4*>(d) = v0;
-        *reinterpret_cast<uint4*>(d + kLbo) = v1;
-    }
-}
-
-__global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant__ WaveParams p, const int iter) {
+// Thread t stages the residual row of member t and later scans TMEM lane t, the scores of that member: the member record stays
+// in registers. The next tile's records are fetched while the tensor core works on this one, and its rows (cp.async) and group
+// image (TMA) start as soon as this tile's MMAs have completed, i.e. behind the scan; one CTA-wide barrier per tile.
+__global__ void __launch_bounds__(128, 5) waveDetailKernel(const __grid_constant__ WaveParams p, const int iter) {
     extern __shared__ __align__(1024) unsigned char smemRaw[];
     DetailSmem& s = *reinterpret_cast<DetailSmem*>(smemRaw);
     if (p.nAct[iter] == 0) return;
@@ -497,40 +513,56 @@ __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant
     fenceAfter();
     const uint32_t tmem = s.tmemBase;
     const uint32_t laneBase = static_cast<uint32_t>(warp * 32) << 16;
+    const uint32_t myDst = smemAddr(s.A) + static_cast<uint32_t>(tid >> 3) * kSbo + static_cast<uint32_t>(tid & 7) * 16u;
     uint32_t mmaPhase = 0, bPhase = 0;
-    int curBin = -1;
-    bool bPending = false;
     unsigned nDetStat = 0;
 
-    for (uint32_t tile = blockIdx.x; tile < nT; tile += gridDim.x) {
-        // bin of this tile: the last bin whose first tile is <= tile (empty bins have equal starts and are skipped)
+    struct Tile {
+        int bin;
+        uint32_t mem;   // block-channel | group position << 27, kWaveNone beyond the bin's last member
+        uint2 info;     // first dictionary index of the group | fp16(2 eps) << 16, threshold implied by the base scores
+    };
+    auto describe = [&](uint32_t tile) {  // bin of the tile: the last bin whose first tile is <= tile (empty bins have equal starts)
         int lo = 0, hi = nbins;
         while (hi - lo > 1) {
             const int mid = (lo + hi) >> 1;
             if (s.tileStart[mid] <= tile) lo = mid;
             else hi = mid;
         }
-        const int bin = lo;
-        const uint32_t chunk = tile - s.tileStart[bin];
-        const uint32_t off = s.binOffset[bin], cnt = s.binOffset[bin + 1] - off;
+        Tile t;
+        t.bin = lo;
+        const uint32_t chunk = tile - s.tileStart[lo];
+        const uint32_t off = s.binOffset[lo], cnt = s.binOffset[lo + 1] - off;
         const uint32_t n = min(static_cast<uint32_t>(kWaveTile), cnt - chunk * kWaveTile);
-        const int ch = bin / p.nBase, atom = bin - ch * p.nBase;
-        if (bin != curBin) {  // the previous tile's MMAs have completed (mbarMma was waited for), B may be overwritten
-            curBin = bin;
-            bPending = true;
-            if (tid == 0) {
-                mbarExpectTx(&s.mbarB, kImgBytes);
-                bulkCopy(s.B, reinterpret_cast<const unsigned char*>(p.detUm16) + static_cast<size_t>(bin) * kImgBytes, kImgBytes, &s.mbarB);
-            }
-        }
         const bool valid = static_cast<uint32_t>(tid) < n;
-        const uint32_t mem = valid ? __ldg(p.members + off + chunk * kWaveTile + tid) : kWaveNone;
-        const uint2 info = valid ? __ldg(p.memberInfo + off + chunk * kWaveTile + tid) : make_uint2(0u, 0u);
-        const uint32_t bc = mem & kBcMask;
-        s.bc[tid] = valid ? bc : kWaveNone;
-        __syncthreads();
-        gatherRows(p.res16, s.bc, s.A, tid, 128);
+        t.mem = valid ? __ldg(p.members + off + chunk * kWaveTile + tid) : kWaveNone;
+        t.info = valid ? __ldg(p.memberInfo + off + chunk * kWaveTile + tid) : make_uint2(0u, 0u);
+        return t;
+    };
+    auto fetchRow = [&](uint32_t mem) {  // residual row -> canonical image: chunk c of row r at (r / 8) * SBO + c * LBO + (r % 8) * 16
+        const bool has = mem != kWaveNone;
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(p.res16 + static_cast<size_t>(has ? (mem & kBcMask) : 0u) * kN);
+        const uint32_t bytes = has ? 16u : 0u;  // src-size 0: the 16 bytes are zero-filled
+#pragma unroll
+        for (uint32_t c = 0; c < 8; ++c)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(myDst + c * kLbo), "l"(src + 16u * c), "r"(bytes) : "memory");
+    };
+    auto fetchGroup = [&](int bin) {
+        if (tid == 0) {
+            mbarExpectTx(&s.mbarB, kImgBytes);
+            bulkCopy(s.B, reinterpret_cast<const unsigned char*>(p.detUm16) + static_cast<size_t>(bin) * kImgBytes, kImgBytes, &s.mbarB);
+        }
+    };
+
+    Tile cur = describe(blockIdx.x);
+    fetchRow(cur.mem);
+    fetchGroup(cur.bin);
+    bool bPending = true;
+    for (uint32_t tile = blockIdx.x; tile < nT; tile += gridDim.x) {
+        const bool more = tile + gridDim.x < nT;
+        asm volatile("cp.async.wait_all;" ::: "memory");
         fenceProxyAsync();
+        fenceBefore();      // this thread's TMEM reads of the previous tile precede the barrier, the next MMAs follow it
         __syncthreads();
         if (warp == 0) {
             if (bPending) mbarWait(&s.mbarB, bPhase);
@@ -544,57 +576,72 @@ __global__ void __launch_bounds__(128, 6) waveDetailKernel(const __grid_constant
             ummaCommitElect(&s.mbarMma);
         }
         if (bPending) bPhase ^= 1u, bPending = false;
+        Tile nxt = cur;
+        if (more) nxt = describe(tile + gridDim.x);  // in flight while the tensor core works
         mbarWait(&s.mbarMma, mmaPhase);
         mmaPhase ^= 1u;
         fenceAfter();
-        const int rowsValid = p.detRows[atom];
-        const uint32_t first = info.x & 0xFFFFu;
-        const float twoEps = __half2float(__ushort_as_half(static_cast<unsigned short>(info.x >> 16)));
-        float m = 0.0f;
-#pragma unroll 1
-        for (int cc = 0; cc < 2; ++cc) {
-            uint32_t raw[32];
-            tmemLoad32(tmem + laneBase + static_cast<uint32_t>(cc * 32), raw);
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-                if (cc * 32 + i < rowsValid) m = fmaxf(m, fabsf(__uint_as_float(raw[i])));
+        if (more) {  // A and B have been consumed: refill them behind the scan
+            fetchRow(nxt.mem);
+            if (nxt.bin != cur.bin) {
+                fetchGroup(nxt.bin);
+                bPending = true;
+            }
         }
+        const bool valid = cur.mem != kWaveNone;
+        const uint32_t bc = cur.mem & kBcMask;
+        const int ch = cur.bin / p.nBase, atom = cur.bin - ch * p.nBase;
+        const int rowsValid = p.detRows[atom];
+        const uint32_t first = cur.info.x & 0xFFFFu;
+        const float twoEps = __half2float(__ushort_as_half(static_cast<unsigned short>(cur.info.x >> 16)));
+        uint32_t raw0[32], raw1[32];
+        tmemLoad32NoWait(tmem + laneBase, raw0);
+        tmemLoad32NoWait(tmem + laneBase + 32u, raw1);
+        tmemWaitLd();
+        // rows past the group's height are zero in the image: they score exactly 0 and cannot raise the maximum
+        float m[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                m[q] = fmaxf(m[q], fmaxf(fabsf(__uint_as_float(raw0[j + 2 * q])), fabsf(__uint_as_float(raw0[j + 2 * q + 1]))));
+                m[2 + q] = fmaxf(m[2 + q], fmaxf(fabsf(__uint_as_float(raw1[j + 2 * q])), fabsf(__uint_as_float(raw1[j + 2 * q + 1]))));
+            }
+        const float m0 = fmaxf(m[0], m[1]), m1 = fmaxf(m[2], m[3]), mAll = fmaxf(m0, m1);
         // within 2 eps of the larger of this group's maximum and the base atoms' maximum
-        const float thr = valid ? fmaxf(m - twoEps, __uint_as_float(info.y)) : __int_as_float(0x7F800000);
-        CandLocal cl;
-        if (__any_sync(kFullMask, m >= thr)) {  // most groups stay below the base atoms' maximum: no second pass over them
-#pragma unroll 1
-            for (int cc = 0; cc < 2; ++cc) {
-                uint32_t raw[32];
-                tmemLoad32(tmem + laneBase + static_cast<uint32_t>(cc * 32), raw);
+        const float thr = valid ? fmaxf(mAll - twoEps, __uint_as_float(cur.info.y)) : __int_as_float(0x7F800000);
+        if (mAll >= thr) {  // most groups stay below the base atoms' maximum
+            CandLocal cl;
+            uint32_t mask0 = 0u, mask1 = 0u;
+            if (m0 >= thr) {
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    bool any = false;
+                for (int j = 0; j < 32; ++j)
+                    if (fabsf(__uint_as_float(raw0[j])) >= thr) mask0 |= 1u << j;
+            }
+            if (m1 >= thr) {
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) any |= fabsf(__uint_as_float(raw[8 * g + i])) >= thr;
-                    if (any) {
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int row = cc * 32 + 8 * g + i;
-                            if (fabsf(__uint_as_float(raw[8 * g + i])) >= thr && row < rowsValid)
-                                cl.add(p, bc, first + static_cast<uint32_t>(row), static_cast<uint32_t>(kRowsPad + (ch * p.nBase + atom) * 64 + row));
-                        }
-                    }
+                for (int j = 0; j < 32; ++j)
+                    if (fabsf(__uint_as_float(raw1[j])) >= thr) mask1 |= 1u << j;
+            }
+            const uint32_t rowBase = static_cast<uint32_t>(kRowsPad + (ch * p.nBase + atom) * 64);
+            while (mask0 | mask1) {
+                int row;
+                if (mask0) row = __ffs(mask0) - 1, mask0 &= mask0 - 1u;
+                else row = 32 + __ffs(mask1) - 1, mask1 &= mask1 - 1u;
+                if (row < rowsValid) cl.add(p, bc, first + static_cast<uint32_t>(row), rowBase + static_cast<uint32_t>(row));
+            }
+            if (cl.n) {  // one atomic per thread with candidates
+                nDetStat += static_cast<unsigned>(cl.n);
+                const uint32_t take = static_cast<uint32_t>(min(cl.n, kCandSlotsDetail));
+                const uint32_t pos = atomicAdd(&p.ncandDetail[bc], take);
+                uint32_t* slots = p.candDetail + static_cast<size_t>(bc) * kCandSlotsDetail;
+                for (uint32_t j = 0; j < take; ++j) {
+                    if (pos + j < static_cast<uint32_t>(kCandSlotsDetail)) slots[pos + j] = cl.c[j];
+                    else queueOverflow(p, bc, cl.c[j]);
                 }
             }
         }
-        if (cl.n) {  // one atomic per thread with candidates, after the scan
-            nDetStat += static_cast<unsigned>(cl.n);
-            const uint32_t take = static_cast<uint32_t>(min(cl.n, kCandSlotsDetail));
-            const uint32_t pos = atomicAdd(&p.ncandDetail[bc], take);
-            uint32_t* slots = p.candDetail + static_cast<size_t>(bc) * kCandSlotsDetail;
-            for (uint32_t j = 0; j < take; ++j) {
-                if (pos + j < static_cast<uint32_t>(kCandSlotsDetail)) slots[pos + j] = cl.c[j];
-                else queueOverflow(p, bc, cl.c[j]);
-            }
-        }
-        fenceBefore();
-        __syncthreads();
+        cur = nxt;
     }
     nDetStat = __reduce_add_sync(kFullMask, nDetStat);
     if ((tid & 31) == 0 && nDetStat) atomicAdd(&p.stats[4], static_cast<unsigned long long>(nDetStat));  // diagnostics
@@ -621,49 +668,47 @@ __global__ void __launch_bounds__(256) waveOverflowKernel(const __grid_constant_
 // Survivors go to the next iteration's list (batched in shared memory, one reservation per CTA and flush) and are counted
 // into the (channel, atom) bins of their groups.
 // ------------------------------------------------------------------------------------------------
-constexpr int kRowsPerRound = 4;   // candidate rows of a block-channel staged per round (2.9 candidates on average)
-constexpr int kFlushEvery = 8;     // passes between two flushes of the survivor list
+constexpr int kRowsPerRound = 4;   // candidate rows of a block-channel staged per round (about 3 candidates on average)
 __global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant__ WaveParams p, const int iter) {
     __shared__ __align__(16) float sR[32 * kRStr];                       // residuals
     __shared__ __align__(16) float sRow[32 * kRowsPerRound * kRStr];     // candidate rows
     __shared__ uint32_t sCand[32][kCandSlots + kCandSlotsDetail];
-    __shared__ uint32_t sList[2][32 * kFlushEvery];
-    __shared__ uint32_t sCount[2], sBase, sN;
-    __shared__ uint32_t sDc[6];  // bins of the groups of atoms 0 and nBase-1: most members, counted per CTA
+    __shared__ uint32_t sList[8][32];  // survivors, one list per warp: flushed by the warp itself, no CTA barrier in the loop
+    __shared__ uint32_t sDc[6];        // bins of the groups of atoms 0 and nBase-1: most members, counted per CTA
+    __shared__ uint8_t sDetRows[kRowsPad];
     const uint32_t nA = p.nAct[iter];
     if (nA == 0) return;
     const uint32_t* act = p.act[iter & 1];
     uint32_t* actNext = p.act[(iter + 1) & 1];
-    const int tid = threadIdx.x, lane = tid & 31, l8 = tid & 7, grp = tid >> 3;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, l8 = tid & 7, grp = tid >> 3;
     const unsigned groupMask = 0xFFu << (lane & 24);
     const int leaderLane = lane & 24;
     float* const myR = sR + grp * kRStr;
     float* const myRows = sRow + grp * kRowsPerRound * kRStr;
     unsigned long long statRows = 0, statPicks = 0;
-    if (tid < 2) sCount[tid] = 0;
     if (tid < 6) sDc[tid] = 0;
+    for (int i = tid; i < kRowsPad; i += 256) sDetRows[i] = p.detRows[i];
     if (blockIdx.x == 0 && tid == 0) *p.ovfCount = 0u;  // the overflow queue of this iteration has been consumed
     __syncthreads();
 
-    auto flush = [&](uint32_t f) {  // survivor list f -> next iteration's active list
-        __syncthreads();
-        if (tid == 0) {
-            sN = sCount[f];
-            sBase = sN ? atomicAdd(&p.nAct[iter + 1], sN) : 0u;
-            sCount[f] = 0;  // list f is appended to again only after the NEXT flush's first barrier
-        }
-        __syncthreads();
-        for (uint32_t i = tid; i < sN; i += 256) actNext[sBase + i] = sList[f][i];
+    uint32_t nList = 0;  // warp-uniform
+    auto flushWarp = [&]() {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&p.nAct[iter + 1], nList);
+        base = __shfl_sync(kFullMask, base, 0);
+        if (static_cast<uint32_t>(lane) < nList) actNext[base + lane] = sList[warp][lane];
+        nList = 0;
+        __syncwarp();
     };
 
     const uint32_t stride = gridDim.x * 32u;
     uint32_t e = blockIdx.x * 32u + static_cast<uint32_t>(grp);
     uint32_t bcNext = e < nA ? act[e] : 0u;
-    uint32_t pass = 0, f = 0;
-    for (uint32_t base = blockIdx.x * 32u; base < nA; base += stride, e += stride, ++pass) {
+    for (uint32_t base = blockIdx.x * 32u; base < nA; base += stride, e += stride) {
         const bool valid = e < nA;
         const uint32_t bc = bcNext;
         if (e + stride < nA) bcNext = act[e + stride];  // next pass's block-channel: its loads start without this round trip
+        bool survivor = false;
         if (valid) {
             const int ch = static_cast<int>(bc % 3u);
             const uint4 st = p.state[bc];
@@ -671,7 +716,10 @@ __global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant
             const uint32_t nDet = min(p.ncandDetail[bc], static_cast<uint32_t>(kCandSlotsDetail));
             const uint32_t c0 = p.cand[static_cast<size_t>(bc) * kCandSlots + l8];
             const uint32_t cd = l8 < kCandSlotsDetail ? p.candDetail[static_cast<size_t>(bc) * kCandSlotsDetail + l8] : 0u;
-            unsigned long long key = l8 == 0 ? p.best[bc] : 0ULL;
+            uint16_t* const g = p.groups + static_cast<size_t>(bc) * kMaxK;
+            const uint2 gw = *reinterpret_cast<const uint2*>(g + 4 * l8);  // groups 4 l8 .. 4 l8 + 3 of the block-channel
+            unsigned long long key = l8 == 0 ? p.best[bc] : 0ULL;          // best of the overflow queue, if any
+            uint32_t keyCode = kWaveNone;
             const int prev = static_cast<int>(st.x & 0xFFFFu), height = static_cast<int>(st.x >> 16);
             const int reps = static_cast<int>(st.y & 0xFFu), ng = static_cast<int>((st.y >> 8) & 0xFFu);
             const float4* src = reinterpret_cast<const float4*>(p.res32 + static_cast<size_t>(bc) * kN + 8 * l8);
@@ -708,14 +756,20 @@ __global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant
                         acc = __fadd_rn(acc, __fmul_rn(d4.z, r4.z));
                         acc = __fadd_rn(acc, __fmul_rn(d4.w, r4.w));
                     }
-                    key = max(key, makeKey(acc, static_cast<int>(sCand[grp][r + l8] & 0xFFFu)));
+                    const uint32_t code = sCand[grp][r + l8];
+                    const unsigned long long k2 = makeKey(acc, static_cast<int>(code & 0xFFFu));
+                    if (k2 > key) key = k2, keyCode = code;
                 }
                 __syncwarp(groupMask);
             }
+            unsigned long long kmax = key;
 #pragma unroll
-            for (int off = 4; off > 0; off >>= 1) key = max(key, __shfl_xor_sync(groupMask, key, off));
-            const int idx = key ? keyIndex(key) : 0;
-            const float proj = key ? keyValue(key) : 0.0f;
+            for (int off = 4; off > 0; off >>= 1) kmax = max(kmax, __shfl_xor_sync(groupMask, kmax, off));
+            const int idx = kmax ? keyIndex(kmax) : 0;
+            const float proj = kmax ? keyValue(kmax) : 0.0f;
+            // row of the winner: the thread that scored it knows it (a winner from the overflow queue is looked up below)
+            const unsigned owners = (__ballot_sync(groupMask, kmax != 0ULL && key == kmax && keyCode != kWaveNone) >> leaderLane) & 0xFFu;
+            const uint32_t winCode = __shfl_sync(groupMask, keyCode, leaderLane + (owners ? __ffs(owners) - 1 : 0));
             const float qf = p.quant[ch * kMaxK + reps];
             const int qi = static_cast<int>(roundf(__fdiv_rn(proj, qf)));
             const uint32_t deltaId = (reps ? zigzag(idx - prev) : static_cast<uint32_t>(idx)) & 0xFFFFu;
@@ -726,12 +780,13 @@ __global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant
             } else {
                 const float c = __fmul_rn(qf, static_cast<float>(qi));
                 uint32_t rowId = static_cast<uint32_t>(idx);
-                uint16_t* g = p.groups + static_cast<size_t>(bc) * kMaxK;
-                if (idx >= p.nBase) {
+                if (owners) {
+                    rowId = winCode >> 12;
+                } else if (idx >= p.nBase) {
                     int hh = p.nBase;
                     for (int k = 0; k < ng; ++k) {
                         const int atom = g[k];
-                        const int rows = p.detRows[atom];
+                        const int rows = sDetRows[atom];
                         if (idx < hh + rows) {
                             rowId = static_cast<uint32_t>(kRowsPad + (ch * p.nBase + atom) * 64 + (idx - hh));
                             break;
@@ -760,7 +815,7 @@ __global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant
                 const bool nonZero = (__ballot_sync(groupMask, nz) & groupMask) != 0u;
                 const bool isBase = idx < p.nBase;
                 const int ngNew = ng + (isBase ? 1 : 0);
-                const int heightNew = height + (isBase ? static_cast<int>(p.detRows[idx]) : 0);
+                const int heightNew = height + (isBase ? static_cast<int>(sDetRows[idx]) : 0);
                 if (l8 == 0) p.pairs[static_cast<size_t>(bc) * p.K + reps] = deltaId | ((zigzag(qi) & 0xFFFFu) << 16);
                 if (reps + 1 == p.K) {
                     count = p.K;
@@ -778,19 +833,24 @@ __global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant
                                 (static_cast<uint32_t>(__half_as_ushort(__float2half_rn(r[2 * i + 1]))) << 16);
                     *reinterpret_cast<uint4*>(p.res16 + static_cast<size_t>(bc) * kN + 8 * l8) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
                     // the survivor's groups (those it had + the one just appended) count into next iteration's bins
-                    for (int k = l8; k < ngNew; k += 8) {
-                        const int atom = (k == ng) ? idx : static_cast<int>(g[k]);
+                    auto countBin = [&](int atom) {
                         if (atom == 0) atomicAdd(&sDc[2 * ch], 1u);
                         else if (atom == p.nBase - 1) atomicAdd(&sDc[2 * ch + 1], 1u);
                         else atomicAdd(&p.binCount[ch * p.nBase + atom], 1u);
-                    }
+                    };
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (4 * l8 + j < ng) countBin(static_cast<int>(((j < 2 ? gw.x : gw.y) >> (16 * (j & 1))) & 0xFFFFu));
                     if (l8 == 0) {
-                        if (isBase) g[ng] = static_cast<uint16_t>(idx);
+                        if (isBase) {
+                            countBin(idx);
+                            g[ng] = static_cast<uint16_t>(idx);
+                        }
                         p.state[bc] = make_uint4(static_cast<uint32_t>(idx) | (static_cast<uint32_t>(heightNew) << 16),
                                                  static_cast<uint32_t>(reps + 1) | (static_cast<uint32_t>(ngNew) << 8),
                                                  __float_as_uint(twoEpsOf(p, ss)), 0u);
                         p.amax[bc] = 0u;
-                        sList[f][atomicAdd(&sCount[f], 1u)] = bc;
+                        survivor = true;
                     }
                 }
             }
@@ -803,12 +863,17 @@ __global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant
                 }
             }
         }
-        if ((pass % kFlushEvery) == kFlushEvery - 1) {
-            flush(f);
-            f ^= 1u;
+        // survivors -> the warp's list -> next iteration's active list
+        __syncwarp();
+        const unsigned surv = __ballot_sync(kFullMask, survivor);
+        if (surv) {
+            if (survivor) sList[warp][nList + __popc(surv & ((1u << lane) - 1u))] = bc;
+            nList += static_cast<uint32_t>(__popc(surv));
+            __syncwarp();
+            if (nList > 28u) flushWarp();
         }
     }
-    flush(f);
+    if (nList) flushWarp();
     __syncthreads();
     if (tid < 6 && sDc[tid]) atomicAdd(&p.binCount[(tid >> 1) * p.nBase + ((tid & 1) ? p.nBase - 1 : 0)], sDc[tid]);
 #pragma unroll
@@ -855,7 +920,7 @@ cudaError_t launchWaveIteration(const WaveParams& p, int iter, uint32_t nActHint
         // at most one partial tile per bin on top of the full ones
         const unsigned long long items = static_cast<unsigned long long>(nActHint) * static_cast<unsigned long long>(std::min(iter, kMaxK - 1));
         const unsigned long long maxTiles = items / kWaveTile + static_cast<unsigned long long>(3 * p.nBase);
-        waveDetailKernel<<<static_cast<unsigned>(std::min<unsigned long long>(maxTiles, 6ull * sms)), 128, smemDetail, st>>>(p, iter);
+        waveDetailKernel<<<static_cast<unsigned>(std::min<unsigned long long>(maxTiles, 5ull * sms)), 128, smemDetail, st>>>(p, iter);
         n += 3;
     }
     waveOverflowKernel<<<std::min((nActHint + 1023u) / 1024u + 1u, 2u * sms), 256, 0, st>>>(p);

@@ -18,7 +18,9 @@
 //   segments    reduce(SUM) of the packed words to rank 0: every rank packs its slices at their FINAL bit positions, the bits
 //               are disjoint, so the sum is the concatenation of the per-GPU bitstream segments
 #include <algorithm>
+#include <condition_variable>
 #include <cstring>
+#include <mutex>
 #include <numeric>
 #include <thread>
 
@@ -27,7 +29,43 @@
 
 namespace mnenc {
 
+// One process, several GPUs: the host threads of the group meet here right before every NCCL launch, after the buffers of that
+// exchange have been allocated. Without it thread A's NCCL kernel (spinning until its peer's kernel starts) and thread B's
+// cudaHostAlloc / cudaMalloc on the way to that launch (which wait for every running kernel of the process) wait for each other.
+// A rank that fails aborts the meeting point, so its peers return an error instead of launching a collective nobody completes.
+struct GroupSync {
+    std::mutex m;
+    std::condition_variable cv;
+    int n = 1, waiting = 0;
+    uint64_t generation = 0;
+    bool aborted = false;
+    bool arrive() {
+        std::unique_lock<std::mutex> lk(m);
+        if (aborted) return false;
+        const uint64_t g0 = generation;
+        if (++waiting == n) {
+            waiting = 0;
+            ++generation;
+            cv.notify_all();
+            return true;
+        }
+        cv.wait(lk, [&] { return generation != g0 || aborted; });
+        return generation != g0;
+    }
+    void abort() {
+        std::lock_guard<std::mutex> lk(m);
+        aborted = true;
+        cv.notify_all();
+    }
+    void reset() {
+        std::lock_guard<std::mutex> lk(m);
+        aborted = false;
+        waiting = 0;
+    }
+};
+
 struct StripeComm {
+    std::shared_ptr<GroupSync> sync;  // mnenc_create_multi only
     ncclComm_t comm = nullptr;
     int rank = 0, nranks = 1;
     DevBuf stage, gathered;   // host-staged all-gathers; all-gathered histogram entries
@@ -54,6 +92,11 @@ namespace {
         if (r_ != ncclSuccess) return ::mnenc::fail(MNENC_ERR_CUDA, std::string(#expr) + ": " + nccl->getErrorString(r_)); \
     } while (0)
 
+#define MEET(sc)                                                                                                  \
+    do {                                                                                                          \
+        if ((sc)->sync && !(sc)->sync->arrive()) return ::mnenc::fail(MNENC_ERR_STATE, "another GPU of the group failed"); \
+    } while (0)
+
 // all-gather of `bytes` host bytes per rank (small records): H2D, ncclAllGather, D2H on the context's stream
 int allGatherHost(mnenc_ctx* c, const NcclApi* nccl, const void* src, void* dst, size_t bytes) {
     StripeComm* sc = c->comm.get();
@@ -67,6 +110,7 @@ int allGatherHost(mnenc_ctx* c, const NcclApi* nccl, const void* src, void* dst,
     unsigned char* h = sc->hStage.as<unsigned char>();
     unsigned char* d = sc->stage.as<unsigned char>();
     std::memcpy(h, src, bytes);
+    MEET(sc);
     CU(cudaMemcpyAsync(d, h, padded, cudaMemcpyHostToDevice, c->stream));
     NC(nccl->allGather(d, d + padded, padded, ncclUint8, sc->comm, c->stream));
     CU(cudaMemcpyAsync(h + padded, d + padded, padded * sc->nranks, cudaMemcpyDeviceToHost, c->stream));
@@ -91,6 +135,7 @@ int exchangeHistogramSparse(mnenc_ctx* c, BackendBuffers& b, int nSeq) {
     CU(sc->stage.ensure(16 * (nr + 1)));
     CU(sc->hStage.ensure(16 * (nr + 1)));
     uint32_t* dCounts = sc->stage.as<uint32_t>();
+    MEET(sc);
     NC(nccl->allGather(b.nEntries, dCounts, 1, ncclUint32, sc->comm, st));
     CU(cudaMemcpyAsync(sc->hStage.p, dCounts, 4 * nr, cudaMemcpyDeviceToHost, st));
     CU(waitStream(c));
@@ -102,6 +147,7 @@ int exchangeHistogramSparse(mnenc_ctx* c, BackendBuffers& b, int nSeq) {
     c->launches += launchResetHistogram(b, mine, st);  // firstPos back to "not seen", maxSym and nEntries to 0; the entry list stays
     if (nMax) {
         CU(sc->gathered.ensure(static_cast<size_t>(nMax) * nr * sizeof(HistEntry)));
+        MEET(sc);
         NC(nccl->allGather(b.entries, sc->gathered.p, static_cast<size_t>(nMax) * sizeof(HistEntry), ncclUint8, sc->comm, st));
         c->launches += launchMergeEntries(b, sc->gathered.as<HistEntry>(), dCounts, nr, nMax, st);
     }
@@ -207,6 +253,7 @@ int reduceSegments(mnenc_ctx* c, void* words, size_t nWords) {
     std::string err;
     const NcclApi* nccl = ncclApi(&err);
     if (!nccl) return fail(MNENC_ERR_CUDA, err);
+    MEET(sc);
     NC(nccl->reduce(words, words, nWords, ncclUint32, ncclSum, 0, sc->comm, c->stream));
     CU(waitStream(c));
     return MNENC_OK;
@@ -345,9 +392,11 @@ int mnenc_create_multi(mnenc_t** out, const int* devices, int n_devices, int K, 
     std::vector<ncclComm_t> comms(n_devices);
     if (ncclResult_t r = nccl->commInitAll(comms.data(), n_devices, devices); r != ncclSuccess)
         return bail(fail(MNENC_ERR_CUDA, std::string("ncclCommInitAll: ") + nccl->getErrorString(r)));
+    auto sync = std::make_shared<GroupSync>();
+    sync->n = n_devices;
     for (int i = 0; i < n_devices; ++i) {
         std::unique_ptr<StripeComm, void (*)(StripeComm*)> sc(new StripeComm, destroyStripeComm);
-        sc->rank = i, sc->nranks = n_devices, sc->comm = comms[i];
+        sc->rank = i, sc->nranks = n_devices, sc->comm = comms[i], sc->sync = sync;
         ctxs[i]->comm = std::move(sc);
         if (i) ctxs[0]->groupPeers.push_back(ctxs[i]);
     }
@@ -376,8 +425,12 @@ int encodeGroup(mnenc_ctx* c, const uint8_t* rgb, size_t width, size_t height, s
     auto work = [&](int r) {
         const uint32_t bx0 = static_cast<uint32_t>(static_cast<uint64_t>(nbx) * r / nr), bx1 = static_cast<uint32_t>(static_cast<uint64_t>(nbx) * (r + 1) / nr);
         rcs[r] = mnenc_encode_striped_rgb8(ranks[r], rgb + 3 * 8 * static_cast<size_t>(bx0), 0, width, height, stride, bx0, bx1, &outs[r], &sizes[r]);
-        if (rcs[r]) errs[r] = mnenc_last_error();
+        if (rcs[r]) {
+            errs[r] = mnenc_last_error();
+            if (c->comm->sync) c->comm->sync->abort();
+        }
     };
+    if (c->comm->sync) c->comm->sync->reset();
     std::vector<std::thread> threads;
     for (int r = 1; r < nr; ++r) threads.emplace_back(work, r);
     work(0);
