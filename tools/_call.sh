@@ -1,9 +1,11 @@
 mkdir -p gpurun_out
-L=gpurun_out/r02_call14.log
+L=gpurun_out/r02_call16.log
 : > $L
-echo "=== ncu full: decide iteration 1, bin fill iteration 2 (of the 2nd encode)" >> $L
-timeout 300 ncu --set full --import-source on --clock-control none -k regex:waveDecideKernel --launch-skip 15 --launch-count 1 -o gpurun_out/r02_wave_decide_v6 -f python tools/profile_encode.py 2 >> $L 2>&1; echo "rc=$?" >> $L
-timeout 300 ncu --set full --import-source on --clock-control none -k regex:waveBinFillKernel --launch-skip 14 --launch-count 1 -o gpurun_out/r02_wave_binfill_v6 -f python tools/profile_encode.py 2 >> $L 2>&1; echo "rc=$?" >> $L
-echo "=== pytest -m gpu" >> $L
-timeout 1500 python -m pytest tests/ -x -q -m gpu >> $L 2>&1; echo "rc=$?" >> $L
-grep -v "==WARNING\|==PROF" $L | tail -n 40
+echo "=== wave check (small first, short limits)" >> $L
+timeout 90 python tools/mp_check.py --sizes 64x64,200x136 --q 3.5 --time 0 >> $L 2>&1; rc=$?; echo "rc=$rc" >> $L
+if [ $rc -ne 0 ]; then tail -n 30 $L; exit 0; fi
+MNENC_WAVE_TRACE=1 timeout 200 python tools/mp_check.py 2>&1 | grep -v "wave round" >> $L; echo "rc=$?" >> $L
+echo "=== ncu launch list, wave 16MP q3.5 (2 encodes)" >> $L
+timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r02_wave_launches_16mp_g.csv python tools/profile_encode.py 2 >> $L 2>&1; echo "rc=$?" >> $L
+python tools/agg_launches.py gpurun_out/r02_wave_launches_16mp_g.csv | grep -i "wave\|matching" >> $L 2>&1
+grep -v "^wave candidates\|==WARNING\|==PROF" $L | tail -n 40
