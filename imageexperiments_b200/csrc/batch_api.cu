@@ -66,6 +66,24 @@ extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
         std::memcpy(lanes[i]->hQuant, c->hQuant, sizeof(c->hQuant));  // the device table is shared; the header needs the host copy
         lanes[i]->quantSet = true;
     }
+    // Frames of one geometry that are small enough to leave the per-iteration kernels of the matching pursuit launch-bound share
+    // one pursuit, `group` frames at a time (about the block-channel count of a 16 MP image).
+    size_t group = 1;
+    {
+        bool uniform = c->mpMode == 4 && n_images > 1;
+        for (size_t i = 1; i < n_images && uniform; ++i)
+            uniform = width[i] == width[0] && height[i] == height[0] && (!on_device || row_stride_bytes[i] == row_stride_bytes[0]);
+        if (uniform && width[0] && height[0] && row_stride_bytes[0] >= 3 * width[0]) {
+            for (size_t i = 0; i < n_images && uniform; ++i) uniform = rgb[i] != nullptr && row_stride_bytes[i] >= 3 * width[0];
+            const size_t nbcFrame = 3 * static_cast<size_t>(frameBlockSlots(width[0], height[0]));
+            if (uniform && nbcFrame < 400000) {
+                group = std::clamp<size_t>(786432 / nbcFrame, 1, 16);
+                if (const char* e = std::getenv("MNENC_FRAME_GROUP")) group = std::clamp<size_t>(static_cast<size_t>(std::atoi(e)), 1, 64);
+                // every lane gets work: no more frames per group than the batch spread over the lanes holds
+                group = std::min(group, std::max<size_t>(1, (n_images + lanes.size() - 1) / lanes.size()));
+            }
+        }
+    }
     std::atomic<size_t> next{0};
     std::atomic<int> firstError{MNENC_OK};
     int launches[kMaxLanes] = {};
@@ -75,10 +93,16 @@ extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
         mnenc_ctx* l = lanes[li];
         cudaSetDevice(l->device);
         while (firstError.load(std::memory_order_relaxed) == MNENC_OK) {
-            const size_t i = next.fetch_add(1);
+            const size_t i = next.fetch_add(group);
             if (i >= n_images) break;
-            const int rc = on_device ? mnenc_encode_rgb8_device(l, rgb[i], width[i], height[i], row_stride_bytes[i], &out[i], &out_bytes[i])
-                                     : mnenc_encode_rgb8(l, rgb[i], width[i], height[i], row_stride_bytes[i], &out[i], &out_bytes[i]);
+            const size_t g = std::min(group, n_images - i);
+            int rc;
+            if (g > 1) {
+                rc = encodeFrames(l, rgb + i, on_device, g, width[i], height[i], row_stride_bytes + i, out + i, out_bytes + i);
+            } else {
+                rc = on_device ? mnenc_encode_rgb8_device(l, rgb[i], width[i], height[i], row_stride_bytes[i], &out[i], &out_bytes[i])
+                               : mnenc_encode_rgb8(l, rgb[i], width[i], height[i], row_stride_bytes[i], &out[i], &out_bytes[i]);
+            }
             if (rc != MNENC_OK) {
                 int expected = MNENC_OK;
                 if (firstError.compare_exchange_strong(expected, rc)) c->laneError = "image " + std::to_string(i) + ": " + mnenc_last_error();

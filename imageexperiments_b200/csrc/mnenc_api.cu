@@ -172,8 +172,8 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     cudaStream_t st = c->stream;
 
     BackendBuffers b{};
-    b.counts = c->counts.as<uint16_t>();
-    b.pairs = c->pairs.as<uint32_t>();
+    b.counts = c->counts.as<uint16_t>() + c->frameBc;  // frameBc: this frame's slice when several frames shared one pursuit
+    b.pairs = c->pairs.as<uint32_t>() + static_cast<size_t>(c->frameBc) * K;
     b.K = K;
     b.nblocks = nblocks;
     b.ntiles = ntiles;
@@ -401,7 +401,7 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
 // Level-synchronous matching pursuit: one round of kernels per greedy iteration (mp_wave.cu). The host queues rounds
 // kWaveLookahead iterations ahead of the GPU and stops as soon as a finished round reports no active block-channel.
 static int runWavePursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride, uint32_t nbx, uint32_t nby,
-                          uint32_t nbc) {
+                          uint32_t nbc, const uint8_t* const* framesDev, uint32_t frameBlocks) {
     constexpr int kWaveLookahead = 3;
     if (nbc > 0x07FFFFFFu) return fail(MNENC_ERR_ARG, "image too large: more than 2^27 block-channels");
     const int K = c->K, nbins = 3 * c->nBase;
@@ -428,6 +428,8 @@ static int runWavePursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, siz
     CU(cudaMemsetAsync(c->wBins.p, 0, (headWords + binWords) * 4, c->stream));
     WaveParams p{};
     p.rgb = rgbDev;
+    p.frames = framesDev;
+    p.frameBlocks = frameBlocks;
     p.stride = stride;
     p.width = static_cast<int>(width);
     p.height = static_cast<int>(height);
@@ -494,10 +496,21 @@ static int runWavePursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, siz
     return MNENC_OK;
 }
 
-int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride) {
+// Block slots per frame when several frames share one pursuit: a multiple of 8, so that every frame's slice of counts / pairs
+// starts on a 16-byte boundary.
+uint32_t frameBlockSlots(size_t width, size_t height) {
+    const uint64_t nb = static_cast<uint64_t>((width + 7) / 8) * ((height + 7) / 8);
+    return static_cast<uint32_t>((nb + 7) / 8 * 8);
+}
+
+int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride, const uint8_t* const* framesDev,
+                       uint32_t nFrames) {
     NvtxRange nvtxRange("mnenc:matching_pursuit");
     const uint32_t nbx = static_cast<uint32_t>((width + 7) / 8), nby = static_cast<uint32_t>((height + 7) / 8);
-    const uint64_t nbc64 = 3ull * nbx * nby;
+    const uint32_t frameBlocks = framesDev ? frameBlockSlots(width, height) : 0u;
+    const uint64_t nbc64 = framesDev ? 3ull * frameBlocks * nFrames : 3ull * nbx * nby;
+    if (framesDev && c->mpMode != 4) return fail(MNENC_ERR_STATE, "frame groups need the level-synchronous pursuit");
+    c->frameBc = 0;
     if (nbc64 >= 0x7FFFFFFFull) return fail(MNENC_ERR_ARG, "image too large");
     const uint32_t nbc = static_cast<uint32_t>(nbc64);
     CU(c->counts.ensure(static_cast<size_t>(nbc) * 2 + 16));
@@ -507,7 +520,7 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     CU(cudaMemsetAsync(c->mpScratch.p, 0, 64, c->stream));
     CU(cudaEventRecord(c->ev[0], c->stream));
     if (c->mpMode == 4) {
-        if (int rc = runWavePursuit(c, rgbDev, width, height, stride, nbx, nby, nbc)) return rc;
+        if (int rc = runWavePursuit(c, rgbDev, width, height, stride, nbx, nby, nbc, framesDev, frameBlocks)) return rc;
     } else {
         MpParams p{};
         p.rgb = rgbDev;
@@ -539,7 +552,7 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     CU(cudaMemcpyAsync(c->hStats.p, c->mpScratch.as<unsigned char>() + 16, 48, cudaMemcpyDeviceToHost, c->stream));
     c->lastW = width;
     c->lastH = height;
-    c->haveSymbols = true;
+    c->haveSymbols = framesDev == nullptr;  // mnenc_get_symbols describes ONE image
     return MNENC_OK;
 }
 
@@ -704,6 +717,51 @@ static int encodeDevice(mnenc_t* c, const uint8_t* rgbDev, size_t w, size_t h, s
     c->ms[7] = static_cast<float>(nowMs() - t0);
     return MNENC_OK;
 }
+
+}  // extern "C"
+
+// n frames of one geometry (batch mode): ONE matching pursuit over all their block-channels - small frames alone leave the
+// per-iteration kernels launch-bound - then the back end frame by frame on the frames' slices of the symbol arrays. Every stream
+// is the one the single-image call writes.
+int mnenc::encodeFrames(mnenc_ctx* c, const uint8_t* const* rgb, int onDevice, size_t n, size_t w, size_t h, const size_t* strides,
+                        uint8_t** out, size_t* outBytes) {
+    if (n == 0) return MNENC_OK;
+    CU(cudaSetDevice(c->device));
+    const double t0 = nowMs();
+    c->launches = 0;
+    c->ms[0] = 0;
+    CU(c->hFrameTab.ensure(n * sizeof(void*)));
+    CU(c->frameTab.ensure(n * sizeof(void*)));
+    const uint8_t** tab = c->hFrameTab.as<const uint8_t*>();
+    size_t stride = 3 * w;
+    if (onDevice) {
+        stride = strides[0];
+        for (size_t i = 0; i < n; ++i) tab[i] = rgb[i];
+    } else {
+        const size_t frameBytes = (3 * w * h + 15) / 16 * 16;
+        CU(c->rgb.ensure(frameBytes * n + 16));
+        for (size_t i = 0; i < n; ++i) {
+            uint8_t* d = c->rgb.as<uint8_t>() + frameBytes * i;
+            CU(cudaMemcpy2DAsync(d, 3 * w, rgb[i], strides[i], 3 * w, h, cudaMemcpyHostToDevice, c->stream));
+            tab[i] = d;
+        }
+    }
+    CU(cudaMemcpyAsync(c->frameTab.p, tab, n * sizeof(void*), cudaMemcpyHostToDevice, c->stream));
+    if (int rc = runMatchingPursuit(c, nullptr, w, h, stride, c->frameTab.as<const uint8_t*>(), static_cast<uint32_t>(n))) return rc;
+    const uint32_t slots = frameBlockSlots(w, h);
+    int rcAll = MNENC_OK;
+    for (size_t i = 0; i < n && rcAll == MNENC_OK; ++i) {
+        c->frameBc = 3u * slots * static_cast<uint32_t>(i);
+        rcAll = runBackend(c, w, h, &out[i], &outBytes[i]);
+    }
+    c->frameBc = 0;
+    if (rcAll) return rcAll;
+    finishMpAccounting(c);
+    c->ms[7] = static_cast<float>(nowMs() - t0);
+    return MNENC_OK;
+}
+
+extern "C" {
 
 int mnenc_encode_rgb8_device(mnenc_t* c, const uint8_t* rgb_dev, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes) try {
     if (int rc = checkEncodeArgs(c, rgb_dev, w, h, stride, out, outBytes)) return rc;

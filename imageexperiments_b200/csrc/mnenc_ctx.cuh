@@ -156,6 +156,9 @@ struct mnenc_ctx {
     // stripe protocol
     std::unique_ptr<mnenc::StripeState, void (*)(mnenc::StripeState*)> stripe{nullptr, nullptr};
     std::unique_ptr<mnenc::StripeComm, void (*)(mnenc::StripeComm*)> comm{nullptr, mnenc::destroyStripeComm};
+    uint32_t frameBc = 0;      // block-channel offset of the frame the back end works on (frames that shared one pursuit)
+    mnenc::DevBuf frameTab;    // device pointers of the frames of a group
+    mnenc::PinBuf hFrameTab;
     std::vector<mnenc_ctx*> groupPeers;  // mnenc_create_multi: the contexts of the other GPUs (this one is rank 0)
     // batch mode (batch_api.cu): extra lanes = contexts with their own stream and buffers that alias this dictionary
     std::vector<mnenc_ctx*> lanes;
@@ -179,7 +182,11 @@ inline cudaError_t waitStream(mnenc_ctx* c) {
 
 // Pieces of the single-GPU encode that the other translation units reuse (mnenc_api.cu).
 int ensureHistogram(mnenc_ctx* c);
-int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride);
+int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t height, size_t stride,
+                       const uint8_t* const* framesDev = nullptr, uint32_t nFrames = 1);
+uint32_t frameBlockSlots(size_t width, size_t height);
+int encodeFrames(mnenc_ctx* c, const uint8_t* const* rgb, int onDevice, size_t n, size_t w, size_t h, const size_t* strides, uint8_t** out,
+                 size_t* outBytes);
 void finishMpAccounting(mnenc_ctx* c);
 int checkEncodeArgs(mnenc_ctx* c, const void* rgb, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes);
 // stripe_comm.cu / stripe_api.cu: exchanges of the stripe protocol inside the library

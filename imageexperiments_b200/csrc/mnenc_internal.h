@@ -69,6 +69,10 @@ struct WaveParams {
     size_t stride;
     int width, height, nbx, nby;
     int K, nBase;
+    // several frames of one geometry in one pursuit (batch mode): frame f owns blocks [f * frameBlocks, f * frameBlocks + nbx * nby)
+    // of the block numbering; frameBlocks >= nbx * nby, the blocks in between do not exist. frames == nullptr: one image (`rgb`).
+    const uint8_t* const* frames;
+    uint32_t frameBlocks;
     // dictionary (device)
     const uint16_t* baseUm16;  // [512][64] fp16, canonical K-major UMMA image
     const uint16_t* detUm16;   // [3][nBase] fp16 images of the KLT groups, 8 KB each
@@ -85,9 +89,8 @@ struct WaveParams {
     uint4* state;              // {prev | height << 16, reps | ngroups << 8, twoEps bits, 0}
     uint16_t* groups;          // [nbc][32] base atoms picked so far, pick order (dynamicBasisFast, CompressedImage.cpp:252-289)
     unsigned long long* best;  // [nbc] exact arg-max key of candidates that found no free slot
-    uint32_t* amax;            // [nbc] max |approximate base score| of the current iteration (float bits; atomicMax by the two
-                               // scanning threads of a block-channel, reset by the decide pass)
-    uint32_t* ncand;           // [nbc] four bytes: candidates in each quarter's sub-list (rewritten by every base pass)
+    uint32_t* amax;            // [nbc] max |approximate base score| of the current iteration (float bits; reset by the decide pass)
+    uint32_t* ncand;           // [nbc] candidates among the base atoms (rewritten by every base pass)
     uint32_t* cand;            // [nbc][kCandSlots] dictionary index | row id in rows32 << 12
     uint32_t* ncandDetail;     // [nbc] candidates among the rows of the appended groups (reset by the decide pass)
     uint32_t* candDetail;      // [nbc][kCandSlotsDetail]

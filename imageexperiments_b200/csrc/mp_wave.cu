@@ -76,19 +76,27 @@ __device__ __forceinline__ uint32_t rawByte(const uint32_t (&w)[6], int k) { ret
 
 __global__ void __launch_bounds__(256) waveInitKernel(const __grid_constant__ WaveParams p) {
     __shared__ uint32_t sCount, sBase;
-    const uint32_t nblocks = static_cast<uint32_t>(p.nbx) * static_cast<uint32_t>(p.nby);
+    const uint32_t frameBlocksReal = static_cast<uint32_t>(p.nbx) * static_cast<uint32_t>(p.nby);
     const int tid = threadIdx.x, lane = tid & 31, l8 = tid & 7;
     const unsigned groupMask = 0xFFu << (lane & 24);
     const uint32_t blk = blockIdx.x * 32u + static_cast<uint32_t>(tid >> 3);
     if (tid == 0) sCount = 0;
     __syncthreads();
     uint32_t w[6] = {0u, 0u, 0u, 0u, 0u, 0u};
-    const bool valid = blk < nblocks;
+    uint32_t local = blk;
+    const uint8_t* image = p.rgb;
+    bool valid = blk < p.nbc / 3u;
+    if (p.frames && valid) {
+        const uint32_t f = blk / p.frameBlocks;
+        local = blk - f * p.frameBlocks;
+        image = p.frames[f];
+    }
+    valid = valid && local < frameBlocksReal;
     if (valid) {
-        const int bx = static_cast<int>(blk / static_cast<uint32_t>(p.nby)), by = static_cast<int>(blk - static_cast<uint32_t>(bx) * p.nby);
+        const int bx = static_cast<int>(local / static_cast<uint32_t>(p.nby)), by = static_cast<int>(local - static_cast<uint32_t>(bx) * p.nby);
         const int x0 = bx * 8, y = by * 8 + l8;
         if (y < p.height) {
-            const uint8_t* row = p.rgb + static_cast<size_t>(y) * p.stride + 3 * static_cast<size_t>(x0);
+            const uint8_t* row = image + static_cast<size_t>(y) * p.stride + 3 * static_cast<size_t>(x0);
             if (x0 + 8 <= p.width && (reinterpret_cast<uintptr_t>(row) & 7u) == 0) {
                 const uint2* r2 = reinterpret_cast<const uint2*>(row);
                 const uint2 a = __ldg(r2), b = __ldg(r2 + 1), c = __ldg(r2 + 2);
@@ -669,23 +677,13 @@ __global__ void __launch_bounds__(256) waveOverflowKernel(const __grid_constant_
 // into the (channel, atom) bins of their groups.
 // ------------------------------------------------------------------------------------------------
 constexpr int kRowsPerRound = 4;   // candidate rows of a block-channel staged per round (about 3 candidates on average)
-struct DecideSmem {
-    alignas(16) float sR[2][32 * kRStr];                    // residuals: this pass / the next one (prefetched)
-    alignas(16) float sRow[32 * kRowsPerRound * kRStr];     // candidate rows
-    uint32_t sCand[32][kCandSlots + kCandSlotsDetail];
-    uint32_t sList[8][32];  // survivors, one list per warp: flushed by the warp itself, no CTA barrier in the loop
-    uint32_t sDc[6];        // bins of the groups of atoms 0 and nBase-1: most members, counted per CTA
-    uint8_t sDetRows[kRowsPad];
-};
-__global__ void __launch_bounds__(256, 3) waveDecideKernel(const __grid_constant__ WaveParams p, const int iter) {
-    extern __shared__ __align__(1024) unsigned char smemRaw[];
-    DecideSmem& sm = *reinterpret_cast<DecideSmem*>(smemRaw);
-    auto& sR = sm.sR;
-    auto& sRow = sm.sRow;
-    auto& sCand = sm.sCand;
-    auto& sList = sm.sList;
-    auto& sDc = sm.sDc;
-    auto& sDetRows = sm.sDetRows;
+__global__ void __launch_bounds__(256, 4) waveDecideKernel(const __grid_constant__ WaveParams p, const int iter) {
+    __shared__ __align__(16) float sR[32 * kRStr];                       // residuals
+    __shared__ __align__(16) float sRow[32 * kRowsPerRound * kRStr];     // candidate rows
+    __shared__ uint32_t sCand[32][kCandSlots + kCandSlotsDetail];
+    __shared__ uint32_t sList[8][32];  // survivors, one list per warp: flushed by the warp itself, no CTA barrier in the loop
+    __shared__ uint32_t sDc[6];        // bins of the groups of atoms 0 and nBase-1: most members, counted per CTA
+    __shared__ uint8_t sDetRows[kRowsPad];
     const uint32_t nA = p.nAct[iter];
     if (nA == 0) return;
     const uint32_t* act = p.act[iter & 1];
@@ -693,7 +691,8 @@ __global__ void __launch_bounds__(256, 3) waveDecideKernel(const __grid_constant
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, l8 = tid & 7, grp = tid >> 3;
     const unsigned groupMask = 0xFFu << (lane & 24);
     const int leaderLane = lane & 24;
-    float* const myRows = &sRow[0] + grp * kRowsPerRound * kRStr;
+    float* const myR = sR + grp * kRStr;
+    float* const myRows = sRow + grp * kRowsPerRound * kRStr;
     unsigned long long statRows = 0, statPicks = 0;
     if (tid < 6) sDc[tid] = 0;
     for (int i = tid; i < kRowsPad; i += 256) sDetRows[i] = p.detRows[i];
@@ -710,68 +709,38 @@ __global__ void __launch_bounds__(256, 3) waveDecideKernel(const __grid_constant
         __syncwarp();
     };
 
-    // Software pipeline over the passes: while a pass works, the NEXT pass's block-channel record is on its way into registers
-    // and its residual into the other shared-memory buffer (cp.async), and the index of the pass after that is being read.
-    struct Record {
-        uint4 st;
-        uint32_t nBaseCand, nDet, c0, cd;
-        uint2 gw;                 // groups 4 l8 .. 4 l8 + 3 of the block-channel
-        unsigned long long best;  // best of the overflow queue, if any
-    };
-    auto fetch = [&](uint32_t bc, int buf) {
-        Record rc;
-        rc.st = p.state[bc];
-        rc.nBaseCand = p.ncand[bc];
-        rc.nDet = p.ncandDetail[bc];
-        rc.c0 = p.cand[static_cast<size_t>(bc) * kCandSlots + l8];
-        rc.cd = l8 < kCandSlotsDetail ? p.candDetail[static_cast<size_t>(bc) * kCandSlotsDetail + l8] : 0u;
-        rc.gw = *reinterpret_cast<const uint2*>(p.groups + static_cast<size_t>(bc) * kMaxK + 4 * l8);
-        rc.best = l8 == 0 ? p.best[bc] : 0ULL;
-        const float* src = p.res32 + static_cast<size_t>(bc) * kN + 8 * l8;
-        const uint32_t dst = smemAddr(&sR[buf][0] + grp * kRStr + 8 * l8);
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u), "l"(src + 4) : "memory");
-        return rc;
-    };
     const uint32_t stride = gridDim.x * 32u;
     uint32_t e = blockIdx.x * 32u + static_cast<uint32_t>(grp);
-    uint32_t bcCur = e < nA ? act[e] : 0u;
-    uint32_t bcNext = e + stride < nA ? act[e + stride] : 0u;
-    Record cur{};
-    if (e < nA) cur = fetch(bcCur, 0);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    int buf = 0;
-    for (uint32_t base = blockIdx.x * 32u; base < nA; base += stride, e += stride, buf ^= 1) {
+    uint32_t bcNext = e < nA ? act[e] : 0u;
+    for (uint32_t base = blockIdx.x * 32u; base < nA; base += stride, e += stride) {
         const bool valid = e < nA;
-        const uint32_t bc = bcCur;
-        const bool validNext = e + stride < nA;
-        const uint32_t bcN = bcNext;
-        if (e + 2 * stride < nA) bcNext = act[e + 2 * stride];
-        float* const myR = &sR[buf][0] + grp * kRStr;
-        asm volatile("cp.async.wait_group 0;" ::: "memory");  // this pass's residual (prefetched during the previous pass)
-        __syncwarp();
+        const uint32_t bc = bcNext;
+        if (e + stride < nA) bcNext = act[e + stride];  // next pass's block-channel: its loads start without this round trip
         bool survivor = false;
-        Record nxt{};
         if (valid) {
             const int ch = static_cast<int>(bc % 3u);
-            const uint4 st = cur.st;
-            const uint32_t nBaseCand = min(cur.nBaseCand, static_cast<uint32_t>(kCandSlots));
-            const uint32_t nDet = min(cur.nDet, static_cast<uint32_t>(kCandSlotsDetail));
-            const uint32_t c0 = cur.c0, cd = cur.cd;
+            const uint4 st = p.state[bc];
+            const uint32_t nBaseCand = min(p.ncand[bc], static_cast<uint32_t>(kCandSlots));
+            const uint32_t nDet = min(p.ncandDetail[bc], static_cast<uint32_t>(kCandSlotsDetail));
+            const uint32_t c0 = p.cand[static_cast<size_t>(bc) * kCandSlots + l8];
+            const uint32_t cd = l8 < kCandSlotsDetail ? p.candDetail[static_cast<size_t>(bc) * kCandSlotsDetail + l8] : 0u;
             uint16_t* const g = p.groups + static_cast<size_t>(bc) * kMaxK;
-            const uint2 gw = cur.gw;
-            unsigned long long key = cur.best;
+            const uint2 gw = *reinterpret_cast<const uint2*>(g + 4 * l8);  // groups 4 l8 .. 4 l8 + 3 of the block-channel
+            unsigned long long key = l8 == 0 ? p.best[bc] : 0ULL;          // best of the overflow queue, if any
             uint32_t keyCode = kWaveNone;
             const int prev = static_cast<int>(st.x & 0xFFFFu), height = static_cast<int>(st.x >> 16);
             const int reps = static_cast<int>(st.y & 0xFFu), ng = static_cast<int>((st.y >> 8) & 0xFFu);
+            const float4* src = reinterpret_cast<const float4*>(p.res32 + static_cast<size_t>(bc) * kN + 8 * l8);
+            const float4 r0 = src[0], r1 = src[1];
+            reinterpret_cast<float4*>(myR + 8 * l8)[0] = r0;
+            reinterpret_cast<float4*>(myR + 8 * l8)[1] = r1;
             // the block-channel's candidates: base atoms first, then rows of its appended groups
             const int nCand = static_cast<int>(nBaseCand + nDet);
             if (static_cast<uint32_t>(l8) < nBaseCand) sCand[grp][l8] = c0;
             if (static_cast<uint32_t>(l8) < nDet) sCand[grp][nBaseCand + l8] = cd;
             __syncwarp(groupMask);
-            bool prefetched = false;
-            for (int r = 0; r < nCand || !prefetched; r += kRowsPerRound) {
-                const int nr = max(min(kRowsPerRound, nCand - r), 0);
+            for (int r = 0; r < nCand; r += kRowsPerRound) {
+                const int nr = min(kRowsPerRound, nCand - r);
                 // 32 bytes per thread and row straight into shared memory (cp.async: no staging registers, all rows in flight at once)
 #pragma unroll
                 for (int j = 0; j < kRowsPerRound; ++j)
@@ -781,15 +750,7 @@ __global__ void __launch_bounds__(256, 3) waveDecideKernel(const __grid_constant
                         asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(rowp) : "memory");
                         asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst + 16u), "l"(rowp + 4) : "memory");
                     }
-                asm volatile("cp.async.commit_group;" ::: "memory");
-                if (!prefetched) {  // the next pass's record and residual start behind this pass's first rows
-                    if (validNext) nxt = fetch(bcN, buf ^ 1);
-                    asm volatile("cp.async.commit_group;" ::: "memory");
-                    prefetched = true;
-                    asm volatile("cp.async.wait_group 1;" ::: "memory");  // the rows; the prefetch may still be in flight
-                } else {
-                    asm volatile("cp.async.wait_group 0;" ::: "memory");
-                }
+                asm volatile("cp.async.wait_all;" ::: "memory");
                 __syncwarp(groupMask);
                 if (l8 < nr) {  // acc = fl(acc + fl(d * r)), j ascending, never fused (tc::exactDot)
                     const float4* dp = reinterpret_cast<const float4*>(myRows + l8 * kRStr);
@@ -843,7 +804,6 @@ __global__ void __launch_bounds__(256, 3) waveDecideKernel(const __grid_constant
                 }
                 const float4* rowp = reinterpret_cast<const float4*>(p.rows32 + static_cast<size_t>(rowId) * kN) + 2 * l8;
                 const float4 d0 = __ldg(rowp), d1 = __ldg(rowp + 1);  // fetched a moment ago as a candidate row: L1 / L2 hit
-                const float4 r0 = reinterpret_cast<const float4*>(myR + 8 * l8)[0], r1 = reinterpret_cast<const float4*>(myR + 8 * l8)[1];
                 float r[8];
                 r[0] = __fsub_rn(r0.x, __fmul_rn(c, d0.x));
                 r[1] = __fsub_rn(r0.y, __fmul_rn(c, d0.y));
@@ -911,12 +871,6 @@ __global__ void __launch_bounds__(256, 3) waveDecideKernel(const __grid_constant
                 }
             }
         }
-        else if (validNext) {  // (no work in this pass for this group: still start the next pass's loads)
-            nxt = fetch(bcN, buf ^ 1);
-            asm volatile("cp.async.commit_group;" ::: "memory");
-        }
-        cur = nxt;
-        bcCur = bcN;
         // survivors -> the warp's list -> next iteration's active list
         __syncwarp();
         const unsigned surv = __ballot_sync(kFullMask, survivor);
@@ -954,13 +908,11 @@ cudaError_t launchWaveInit(const WaveParams& p, cudaStream_t st) {
 
 cudaError_t launchWaveIteration(const WaveParams& p, int iter, uint32_t nActHint, int numSMs, cudaStream_t st, int* launches) {
     static bool configured = false;
-    const size_t smemBase = sizeof(BaseSmem) + 1024, smemDetail = sizeof(DetailSmem) + 1024, smemDecide = sizeof(DecideSmem);
+    const size_t smemBase = sizeof(BaseSmem) + 1024, smemDetail = sizeof(DetailSmem) + 1024;
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(waveBaseKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBase));
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(waveDetailKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemDetail));
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(waveDecideKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemDecide));
         if (e != cudaSuccess) return e;
         configured = true;
     }
@@ -980,7 +932,7 @@ cudaError_t launchWaveIteration(const WaveParams& p, int iter, uint32_t nActHint
         n += 3;
     }
     waveOverflowKernel<<<std::min((nActHint + 1023u) / 1024u + 1u, 2u * sms), 256, 0, st>>>(p);
-    waveDecideKernel<<<std::min((nActHint + 31u) / 32u, 12u * sms), 256, smemDecide, st>>>(p, iter);
+    waveDecideKernel<<<std::min((nActHint + 31u) / 32u, 16u * sms), 256, 0, st>>>(p, iter);
     n += 2;
     if (launches) *launches += n;
     return cudaGetLastError();

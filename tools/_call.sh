@@ -1,11 +1,13 @@
 mkdir -p gpurun_out
-L=gpurun_out/r02_call16.log
+L=gpurun_out/r02_call17.log
 : > $L
-echo "=== wave check (small first, short limits)" >> $L
-timeout 90 python tools/mp_check.py --sizes 64x64,200x136 --q 3.5 --time 0 >> $L 2>&1; rc=$?; echo "rc=$rc" >> $L
-if [ $rc -ne 0 ]; then tail -n 30 $L; exit 0; fi
-MNENC_WAVE_TRACE=1 timeout 200 python tools/mp_check.py 2>&1 | grep -v "wave round" >> $L; echo "rc=$?" >> $L
-echo "=== ncu launch list, wave 16MP q3.5 (2 encodes)" >> $L
-timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r02_wave_launches_16mp_g.csv python tools/profile_encode.py 2 >> $L 2>&1; echo "rc=$?" >> $L
-python tools/agg_launches.py gpurun_out/r02_wave_launches_16mp_g.csv | grep -i "wave\|matching" >> $L 2>&1
-grep -v "^wave candidates\|==WARNING\|==PROF" $L | tail -n 40
+echo "=== batch check" >> $L
+timeout 300 python tools/batch_check.py >> $L 2>&1; echo "rc=$?" >> $L
+echo "=== per-frame path for comparison (MNENC_FRAME_GROUP=1)" >> $L
+MNENC_FRAME_GROUP=1 timeout 300 python tools/batch_check.py 2>&1 | tail -n 1 >> $L
+echo "=== groups of 4 / 16" >> $L
+MNENC_FRAME_GROUP=4 timeout 300 python tools/batch_check.py 2>&1 | tail -n 1 >> $L
+MNENC_FRAME_GROUP=16 timeout 300 python tools/batch_check.py 2>&1 | tail -n 1 >> $L
+echo "=== 16 MP timing with the restored decide pass" >> $L
+timeout 200 python tools/mp_check.py --sizes 64x64 --q 3.5 2>&1 | tail -n 3 >> $L
+tail -n 40 $L
