@@ -291,13 +291,13 @@ def quality_sweep_record(ctx, tensor_peak):
 
 
 def batch1080p_record(ctx, rank, world, barrier, max_over_ranks):
-    """BASELINE.json configs[4]: 1920x1080 frames (frame f: seed 12345 + f) in throughput mode, 64 frames per GPU and step."""
+    """BASELINE.json configs[4]: 1920x1080 frames (frame f: seed 12345 + f) in throughput mode, 192 frames per GPU and step."""
     import torch
 
     import imageexperiments_b200 as mn
     from imageexperiments_b200.synth import synthetic_rgb
     try:
-        fw, fh, nf = 1920, 1080, 64
+        fw, fh, nf = 1920, 1080, 192
         distinct = [torch.from_numpy(synthetic_rgb(fw, fh, 12345 + 8 * rank + f)).cuda() for f in range(8)]
         frames = [distinct[i % 8] for i in range(nf)]
         pinned = []

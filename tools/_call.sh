@@ -1,13 +1,11 @@
 mkdir -p gpurun_out
-L=gpurun_out/r02_call17.log
+L=gpurun_out/r02_call18.log
 : > $L
-echo "=== batch check" >> $L
-timeout 300 python tools/batch_check.py >> $L 2>&1; echo "rc=$?" >> $L
-echo "=== per-frame path for comparison (MNENC_FRAME_GROUP=1)" >> $L
-MNENC_FRAME_GROUP=1 timeout 300 python tools/batch_check.py 2>&1 | tail -n 1 >> $L
-echo "=== groups of 4 / 16" >> $L
-MNENC_FRAME_GROUP=4 timeout 300 python tools/batch_check.py 2>&1 | tail -n 1 >> $L
-MNENC_FRAME_GROUP=16 timeout 300 python tools/batch_check.py 2>&1 | tail -n 1 >> $L
-echo "=== 16 MP timing with the restored decide pass" >> $L
-timeout 200 python tools/mp_check.py --sizes 64x64 --q 3.5 2>&1 | tail -n 3 >> $L
-tail -n 40 $L
+echo "=== multi-GPU context, one process (60 s limit)" >> $L
+timeout 60 python tools/multi_check.py 2 >> $L 2>&1; echo "rc=$?" >> $L
+echo "=== bench N=2" >> $L
+( time timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 10 --warmup 3 ) > gpurun_out/r02_bench_n2.json 2>> $L; echo "rc=$?" >> $L
+tail -n 1 gpurun_out/r02_bench_n2.json | cut -c1-6000 >> $L
+echo "=== batch check (1 GPU)" >> $L
+timeout 200 python tools/batch_check.py 2>&1 | tail -n 2 >> $L
+tail -c 7000 $L
