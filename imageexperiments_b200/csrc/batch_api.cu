@@ -17,8 +17,7 @@ namespace {
 int makeLane(mnenc_ctx* parent, int threads, mnenc_ctx** out) {
     mnenc_ctx* l = new mnenc_ctx;
     l->device = parent->device, l->K = parent->K, l->nBase = parent->nBase, l->numSMs = parent->numSMs;
-    l->epsRel16 = parent->epsRel16, l->epsAbs16 = parent->epsAbs16, l->mpMode = parent->mpMode;
-    l->epsRel16Hi = parent->epsRel16Hi, l->residualLo = parent->residualLo;
+    l->epsAbs16 = parent->epsAbs16, l->epsRel16Hi = parent->epsRel16Hi;
     l->detRows.alias(parent->detRows);
     l->baseUm16.alias(parent->baseUm16), l->detUm16.alias(parent->detUm16), l->rows32.alias(parent->rows32);
     l->quant.alias(parent->quant);
@@ -69,7 +68,7 @@ extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
     // one pursuit, `group` frames at a time (about the block-channel count of a 16 MP image).
     size_t group = 1;
     {
-        bool uniform = c->mpMode == 4 && n_images > 1;
+        bool uniform = n_images > 1;
         for (size_t i = 1; i < n_images && uniform; ++i)
             uniform = width[i] == width[0] && height[i] == height[0] && (!on_device || row_stride_bytes[i] == row_stride_bytes[0]);
         if (uniform && width[0] && height[0] && row_stride_bytes[0] >= 3 * width[0]) {

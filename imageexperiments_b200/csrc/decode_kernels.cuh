@@ -13,7 +13,7 @@ struct DecodeParams {
     const uint16_t* counts;   // [3 * nblocks] the `lengths` stream
     const uint32_t* pairs;    // [3 * nblocks][K] deltaId | intCoeff << 16, DC chains undone
     const float* quant;       // [3][K] from the stream header
-    const float* rows32;      // [512 + 3 * nBase * 64][64] dictionary rows (MpParams::rows32)
+    const float* rows32;      // [512 + 3 * nBase * 64][64] dictionary rows (WaveParams::rows32)
     const uint8_t* detRows;   // [nBase] rows of each detail group
     int K, nBase;
     uint32_t nblocks, nby;    // block index = bx * nby + by

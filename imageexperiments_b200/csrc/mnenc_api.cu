@@ -509,7 +509,6 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     const uint32_t nbx = static_cast<uint32_t>((width + 7) / 8), nby = static_cast<uint32_t>((height + 7) / 8);
     const uint32_t frameBlocks = framesDev ? frameBlockSlots(width, height) : 0u;
     const uint64_t nbc64 = framesDev ? 3ull * frameBlocks * nFrames : 3ull * nbx * nby;
-    if (framesDev && c->mpMode != 4) return fail(MNENC_ERR_STATE, "frame groups need the level-synchronous pursuit");
     c->frameBc = 0;
     if (nbc64 >= 0x7FFFFFFFull) return fail(MNENC_ERR_ARG, "image too large");
     const uint32_t nbc = static_cast<uint32_t>(nbc64);
@@ -519,35 +518,7 @@ int runMatchingPursuit(mnenc_ctx* c, const uint8_t* rgbDev, size_t width, size_t
     CU(c->hStats.ensure(64));
     CU(cudaMemsetAsync(c->mpScratch.p, 0, 64, c->stream));
     CU(cudaEventRecord(c->ev[0], c->stream));
-    if (c->mpMode == 4) {
-        if (int rc = runWavePursuit(c, rgbDev, width, height, stride, nbx, nby, nbc, framesDev, frameBlocks)) return rc;
-    } else {
-        MpParams p{};
-        p.rgb = rgbDev;
-        p.stride = stride;
-        p.width = static_cast<int>(width);
-        p.height = static_cast<int>(height);
-        p.nbx = static_cast<int>(nbx);
-        p.nby = static_cast<int>(nby);
-        p.K = c->K;
-        p.nBase = c->nBase;
-        p.detRows = c->detRows.as<uint8_t>();
-        p.quant = c->quant.as<float>();
-        p.counts = c->counts.as<uint16_t>();
-        p.pairs = c->pairs.as<uint32_t>();
-        p.workCounter = c->mpScratch.as<unsigned int>();
-        p.stats = reinterpret_cast<unsigned long long*>(c->mpScratch.as<unsigned char>() + 16);
-        p.nbc = nbc;
-        p.baseUm16 = c->baseUm16.as<uint16_t>();
-        p.detUm16 = c->detUm16.as<uint16_t>();
-        p.rows32 = c->rows32.as<float>();
-        p.epsRel16 = !c->residualLo ? c->epsRel16Hi : c->epsRel16;
-        p.residualLo = c->residualLo;
-        p.epsAbs16 = c->epsAbs16;
-        p.debugTiming = std::getenv("MNENC_MP_TIMING") != nullptr;
-        CU(launchMatchingPursuitTeams(p, c->numSMs, c->stream));
-        c->launches += nbc ? 1 : 0;
-    }
+    if (int rc = runWavePursuit(c, rgbDev, width, height, stride, nbx, nby, nbc, framesDev, frameBlocks)) return rc;
     CU(cudaEventRecord(c->ev[1], c->stream));
     CU(cudaMemcpyAsync(c->hStats.p, c->mpScratch.as<unsigned char>() + 16, 48, cudaMemcpyDeviceToHost, c->stream));
     c->lastW = width;
@@ -630,21 +601,18 @@ int mnenc_create(mnenc_t** out, int device, int K, int block_size, const float* 
     for (auto& e : c->ev) CUB(cudaEventCreate(&e));
     CUB(cudaEventCreateWithFlags(&c->evSync, cudaEventDisableTiming));
     for (auto& e : c->evWave) CUB(cudaEventCreateWithFlags(&e, cudaEventDisableTiming | cudaEventBlockingSync));
-    if (const char* mode = std::getenv("MNENC_MP")) c->mpMode = std::string(mode) == "teams" ? 3 : 4;
     {   // fp16 operand images + exact row table of the fp16 tensor-core kernel, and its rigorous pre-filter bound:
         //   |p~ - p_oracle| <= ||d - fp16(d)|| ||r||  (dictionary rounding, Cauchy-Schwarz)
-        //                    + ||d|| ||r|| (2^-22 residual hi/lo split + 4e-5 tensor-core accumulation + 64 * 2^-24 oracle rounding)
+        //                    + ||d|| ||r|| (2^-11 residual rounded to fp16 + 4e-5 tensor-core accumulation + 64 * 2^-24 oracle rounding)
         //                    + 5e-7 (fp16 subnormal residual parts), 15 % margin on the relative part
         std::vector<uint16_t> b16(static_cast<size_t>(kRowsPad) * kN), d16(static_cast<size_t>(3) * n_base * 64 * kN);
         std::vector<float> rows(f16Rows32Count(n_base) * kN);
         const float* det3[3] = {detailY, detailU, detailV};
         double roundNorm = 0.0, maxNorm = 0.0;
         buildF16Images(base, n_base, detail_rows, det3, b16.data(), d16.data(), rows.data(), &roundNorm, &maxNorm);
-        c->epsRel16 = static_cast<float>((roundNorm + maxNorm * (1.0 / 4194304.0 + 4e-5 + 64.0 / 16777216.0)) * 1.15);
-        // residual rounded to fp16 without the lo part: |d.(r - fp16(r))| <= ||d|| 2^-11 ||r|| (subnormal parts: epsAbs16)
+        // residual rounded to fp16: |d.(r - fp16(r))| <= ||d|| 2^-11 ||r|| (subnormal parts: epsAbs16)
         c->epsRel16Hi = static_cast<float>((roundNorm + maxNorm * (1.0 / 2048.0 + 4e-5 + 64.0 / 16777216.0)) * 1.15);
         c->epsAbs16 = 5e-7f;
-        if (const char* lo = std::getenv("MNENC_MP_LO")) c->residualLo = std::atoi(lo) ? 1 : 0;
         CUB(c->baseUm16.ensure(b16.size() * 2));
         CUB(cudaMemcpy(c->baseUm16.p, b16.data(), b16.size() * 2, cudaMemcpyHostToDevice));
         CUB(c->detUm16.ensure(d16.size() * 2));

@@ -125,9 +125,7 @@ struct mnenc_ctx {
     float hQuant[3 * mnenc::kMaxK] = {};
     // dictionary
     mnenc::DevBuf detRows, quant, baseUm16, detUm16, rows32;
-    float epsRel16 = 0.0f, epsAbs16 = 0.0f, epsRel16Hi = 0.0f;
-    int residualLo = 0;  // MNENC_MP_LO=1 restores the hi + lo residual split (tighter pre-filter bound, twice the MMAs; measured slower)
-    int mpMode = 4;  // 4 = level-synchronous kernels (mp_wave.cu); MNENC_MP=teams = slot-persistent two-team kernel (mp_kernel_teams.cu)
+    float epsAbs16 = 0.0f, epsRel16Hi = 0.0f;  // pre-filter bound: eps = epsRel16Hi * ||r|| + epsAbs16 (mnenc_create)
     // image + symbols
     mnenc::DevBuf rgb, counts, pairs, mpScratch;
     // level-synchronous matching pursuit (mp_wave.cu): per block-channel state, work lists, (channel, atom) bins

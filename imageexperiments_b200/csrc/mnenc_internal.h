@@ -17,41 +17,12 @@ namespace mnenc {
 constexpr int kN = 64;        // pixels per 8x8 block (only block_size 8 is supported)
 constexpr int kMaxK = 32;     // greedy iterations per block-channel (Compression.cpp:28)
 constexpr int kRowsPad = 512; // base dictionary rows padded (510 real atoms)
-constexpr int kSlots = 32;    // block-channels in flight per CTA of the matching-pursuit kernel
 constexpr int kMaxSeq = 6 * kMaxK + 1;  // coded sequences: `lengths` + 6K symbol streams
-
-// ------------------------------------------------------------------------------------------------
-// Matching pursuit kernel parameters (slot-persistent kernel: mp_kernel_teams.cu)
-// ------------------------------------------------------------------------------------------------
-struct MpParams {
-    const uint8_t* rgb;      // device, packed RGB8
-    size_t stride;           // bytes per image row
-    int width, height;
-    int nbx, nby;            // blocks per row / column; block index = bx*nby + by (column-major walk)
-    int K;
-    int nBase;               // 510
-    const uint16_t* baseUm16; // [512][64] fp16 base atoms, canonical UMMA K-major image (fp16 tensor-core kernel)
-    const uint16_t* detUm16;  // [3][nBase] fp16 images of the detail groups, 64 rows x 64, 8 KB each, zero padded rows
-    const float* rows32;      // [512 + 3*nBase*64][64] exact FP32 rows: base atoms, then detail rows (64 per group)
-    float epsRel16, epsAbs16; // pre-filter error bound of the fp16 kernel: eps = epsRel16 * ||r||_2 + epsAbs16
-    const uint8_t* detRows;  // [nBase] rows of each detail group (62 or 63)
-    const float* quant;      // [3][32]
-    uint16_t* counts;        // [nbc] out: atoms per block-channel == the `lengths` stream
-    uint32_t* pairs;         // [nbc][K] out: deltaId | intCoeff << 16 (0 beyond count)
-    unsigned int* workCounter;      // [3] zeroed before launch ([0] only, except the team kernel: one per channel)
-    unsigned long long* stats;      // [2]: sum of dictionary heights over all iterations, sum of counts
-    unsigned int nbc;        // 3 * nbx * nby
-    int residualLo;          // team kernel: 1 = residual split hi + lo (two MMA passes), 0 = hi only (looser bound, half the MMAs)
-    int debugTiming;         // fp16 kernel: CTA 0 prints its per-phase cycle counts (MNENC_MP_TIMING=1)
-};
 
 // host: fp16 operand images + exact row table of the fp16 kernel; returns max ||d - fp16(d)||_2 and max ||d||_2 over all atoms
 void buildF16Images(const float* baseRowMajor, int nBase, const int32_t* detailRows, const float* const detail[3], uint16_t* baseUm16,
                     uint16_t* detUm16, float* rows32, double* maxRoundingNorm, double* maxNorm);
 size_t f16Rows32Count(int nBase);
-#ifdef __CUDACC__
-cudaError_t launchMatchingPursuitTeams(const MpParams& p, int numSMs, cudaStream_t stream);
-#endif
 
 // ------------------------------------------------------------------------------------------------
 // Level-synchronous matching pursuit (mp_wave.cu): every greedy iteration of ALL active block-channels is one

@@ -435,11 +435,15 @@ int encodeGroup(mnenc_ctx* c, const uint8_t* rgb, size_t width, size_t height, s
     for (int r = 1; r < nr; ++r) threads.emplace_back(work, r);
     work(0);
     for (auto& th : threads) th.join();
+    int bad = -1;  // the rank that failed first, not one that gave up at the meeting point because of it
     for (int r = 0; r < nr; ++r)
-        if (rcs[r]) {
-            for (uint8_t* p : outs) resultRelease(p);
-            return fail(rcs[r], "GPU " + std::to_string(ranks[r]->device) + ": " + errs[r]);
-        }
+        if (rcs[r] && (bad < 0 || (errs[bad].find("another GPU of the group failed") != std::string::npos &&
+                                   errs[r].find("another GPU of the group failed") == std::string::npos)))
+            bad = r;
+    if (bad >= 0) {
+        for (uint8_t* p : outs) resultRelease(p);
+        return fail(rcs[bad], "GPU " + std::to_string(ranks[bad]->device) + ": " + errs[bad]);
+    }
     *out = outs[0];
     *outBytes = sizes[0];
     return MNENC_OK;
