@@ -24,6 +24,7 @@
 #include "mp_tc_common.cuh"
 
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 
 namespace mnenc {
@@ -907,14 +908,17 @@ cudaError_t launchWaveInit(const WaveParams& p, cudaStream_t st) {
 }
 
 cudaError_t launchWaveIteration(const WaveParams& p, int iter, uint32_t nActHint, int numSMs, cudaStream_t st, int* launches) {
-    static bool configured = false;
+    static std::atomic<bool> configuredOn[64];  // the attribute is per device (one process may drive several GPUs)
+    int device = 0;
+    if (cudaError_t e = cudaGetDevice(&device); e != cudaSuccess) return e;
+    std::atomic<bool>& configured = configuredOn[device & 63];
     const size_t smemBase = sizeof(BaseSmem) + 1024, smemDetail = sizeof(DetailSmem) + 1024;
-    if (!configured) {
+    if (!configured.load(std::memory_order_acquire)) {
         cudaError_t e = cudaFuncSetAttribute(waveBaseKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemBase));
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(waveDetailKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smemDetail));
         if (e != cudaSuccess) return e;
-        configured = true;
+        configured.store(true, std::memory_order_release);
     }
     if (nActHint == 0) return cudaSuccess;
     const unsigned sms = static_cast<unsigned>(numSMs);
