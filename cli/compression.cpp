@@ -132,9 +132,8 @@ mnenc_t* createContext(const std::string& exeDir) {
         o += 4 * total * cols;
     }
     if (o != raw.size()) die(path + ": size does not match its header");
-    const char* dev = std::getenv("MNENC_DEVICE");
-    mnenc_t* ctx = nullptr;
-    if (mnenc_create(&ctx, dev ? std::atoi(dev) : 0, kK, kBlockSize, base, nBase, rows, det[0], det[1], det[2]) != MNENC_OK) dieLib("mnenc_create");
+    mnenc_t* ctx = nullptr;  // MNENC_DEVICE=n, or MNENC_DEVICES=0,1,... / all for one image over several GPUs
+    if (mnenc_create_auto(&ctx, kK, kBlockSize, base, nBase, rows, det[0], det[1], det[2]) != MNENC_OK) dieLib("mnenc_create_auto");
     return ctx;
 }
 

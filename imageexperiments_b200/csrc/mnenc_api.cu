@@ -79,7 +79,10 @@ struct ResultPool {
     // Idle buffers kept for reuse. cudaHostAlloc / cudaFreeHost synchronise the device, so the limits are generous: a batch of
     // 16 streams in flight must recycle without ever touching the allocator in steady state.
     // Decoded images are 48 MB each at 16 MP: a batch of 32 holds 1.7 GB at once, hence 4 GiB (MNENC_POOL_MB overrides).
-    static constexpr size_t kMaxIdle = 64;
+    // The count limit only bounds the linear searches: a batch of 1024 small frames (BASELINE.json configs[4]) returns 1024
+    // buffers at once - with 64 slots every batch freed and re-pinned most of them, and those calls serialised the lanes
+    // (192 frames of 1080p: 2131 -> ... MP/s, profiles/r02_batch1080p.md).
+    static constexpr size_t kMaxIdle = 2048;
     size_t maxIdleBytes = size_t(4) << 30;
     ResultPool() {
         if (const char* e = std::getenv("MNENC_POOL_MB")) maxIdleBytes = static_cast<size_t>(std::max(0L, std::atol(e))) << 20;
@@ -653,6 +656,10 @@ void mnenc_destroy(mnenc_t* c) {
     for (auto& e : c->ev)
         if (e) cudaEventDestroy(e);
     if (c->evSync) cudaEventDestroy(c->evSync);
+    for (auto& e : c->evChunk)
+        if (e) cudaEventDestroy(e);
+    if (c->copyStream) cudaStreamDestroy(c->copyStream);
+    if (c->stripeResult) resultRelease(c->stripeResult);
     for (auto& e : c->evWave)
         if (e) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);

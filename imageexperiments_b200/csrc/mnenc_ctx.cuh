@@ -154,6 +154,9 @@ struct mnenc_ctx {
     // stripe protocol
     std::unique_ptr<mnenc::StripeState, void (*)(mnenc::StripeState*)> stripe{nullptr, nullptr};
     std::unique_ptr<mnenc::StripeComm, void (*)(mnenc::StripeComm*)> comm{nullptr, mnenc::destroyStripeComm};
+    uint8_t* stripeResult = nullptr;   // striped encode, rank 0: result buffer already filled by the chunked reduce + D2H (stripe_comm.cu)
+    cudaStream_t copyStream = nullptr; // second stream of that pipeline, created on first use
+    cudaEvent_t evChunk[4] = {};
     uint32_t frameBc = 0;      // block-channel offset of the frame the back end works on (frames that shared one pursuit)
     mnenc::DevBuf frameTab;    // device pointers of the frames of a group
     mnenc::PinBuf hFrameTab;
@@ -192,5 +195,6 @@ int stripeExchangeHistogram(mnenc_ctx* c);
 int exchangeHistogramSparse(mnenc_ctx* c, BackendBuffers& b, int nSeq);
 int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats, std::vector<SequencePlan>& plans);
 int stripeRanks(const mnenc_ctx* c);  // ranks of the context's communicator (1 without one)
+size_t stripeTotalBytes(const mnenc_ctx* c);
 int encodeGroup(mnenc_ctx* c, const uint8_t* rgb, size_t width, size_t height, size_t stride, uint8_t** out, size_t* outBytes);
 }  // namespace mnenc

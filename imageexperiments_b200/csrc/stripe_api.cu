@@ -79,6 +79,7 @@ int mnenc_stripe_begin(mnenc_t* c, const uint8_t* rgb_stripe, int on_device, siz
     if (!c || !rec1) return fail(MNENC_ERR_ARG, "null argument");
     if (width == 0 || height == 0 || width > 0xFFFFFFFFull || height > 0xFFFFFFFFull) return fail(MNENC_ERR_ARG, "bad image geometry");
     if (!c->quantSet) return fail(MNENC_ERR_STATE, "mnenc_set_quant has not been called");
+    if (c->stripeResult) resultRelease(c->stripeResult), c->stripeResult = nullptr;  // left over from a striped encode that failed half way
     const uint32_t nbxAll = static_cast<uint32_t>((width + 7) / 8), nby = static_cast<uint32_t>((height + 7) / 8);
     if (nranks < 1 || rank < 0 || rank >= nranks || bx0 > bx1 || bx1 > nbxAll) return fail(MNENC_ERR_ARG, "bad stripe");
     if (bx1 > bx0 && (!rgb_stripe || row_stride_bytes < 3)) return fail(MNENC_ERR_ARG, "null pixels");
@@ -481,13 +482,17 @@ int mnenc_stripe_finish(mnenc_t* c, uint8_t** out, size_t* out_bytes) try {
     *out = nullptr;
     *out_bytes = 0;
     if (s->rank == 0) {
-        uint8_t* res = resultAcquire(s->totalBytes);
-        if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
-        cudaError_t e = cudaMemcpyAsync(res, c->outWords.p, s->totalBytes, cudaMemcpyDeviceToHost, c->stream);
-        if (e == cudaSuccess) e = waitStream(c);
-        if (e != cudaSuccess) {
-            resultRelease(res);
-            return fail(MNENC_ERR_CUDA, std::string("D2H of the stream: ") + cudaGetErrorString(e));
+        uint8_t* res = c->stripeResult;  // the in-library exchange has already brought the stream to the host, chunk by chunk
+        c->stripeResult = nullptr;
+        if (!res) {
+            res = resultAcquire(s->totalBytes);
+            if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
+            cudaError_t e = cudaMemcpyAsync(res, c->outWords.p, s->totalBytes, cudaMemcpyDeviceToHost, c->stream);
+            if (e == cudaSuccess) e = waitStream(c);
+            if (e != cudaSuccess) {
+                resultRelease(res);
+                return fail(MNENC_ERR_CUDA, std::string("D2H of the stream: ") + cudaGetErrorString(e));
+            }
         }
         mergeOverlays(res, s->overlays);
         *out = res;
@@ -503,6 +508,12 @@ int mnenc_stripe_finish(mnenc_t* c, uint8_t** out, size_t* out_bytes) try {
 } catch (...) {
     return mnenc::abiCaught();
 }
+
+}  // extern "C"
+
+size_t mnenc::stripeTotalBytes(const mnenc_ctx* c) { return c->stripe ? c->stripe->totalBytes : 0; }
+
+extern "C" {
 
 int mnenc_debug_plan_stripes(const uint32_t* records, int nranks, int n_streams, uint32_t* emitted, uint8_t* use_rle, uint64_t* raw_len,
                              uint64_t* rle_len) try {

@@ -219,6 +219,13 @@ int mnenc_last_stripe_timing(mnenc_t* ctx, float* ms16);
  */
 int mnenc_create_multi(mnenc_t** out, const int* devices, int n_devices, int K, int block_size, const float* base_rowmajor, int n_base,
                        const int32_t* detail_rows, const float* detailY, const float* detailU, const float* detailV);
+/*
+ * mnenc_create or mnenc_create_multi, chosen by the environment - what a host with no device argument of its own calls (the shim
+ * behind encodeImageFast, CompressedImage.cpp:578; the Compression front end): MNENC_DEVICES="0,1,2" or "all" names the GPUs of a
+ * multi-GPU context, otherwise MNENC_DEVICE (default 0) names the one GPU.
+ */
+int mnenc_create_auto(mnenc_t** out, int K, int block_size, const float* base_rowmajor, int n_base, const int32_t* detail_rows,
+                      const float* detailY, const float* detailU, const float* detailV);
 
 /*
  * Host-logic test hooks of the stripe path (used by the CPU-only world_size-2/3 gloo tests): run stitching of

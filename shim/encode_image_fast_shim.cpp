@@ -76,9 +76,10 @@ mnenc_t* contextFor(const size_t K, const size_t blockSize, const matching::Dyna
                 detailRows[a] = static_cast<int32_t>(full.rows() - nBase);
                 appendRows(detail[ch], full, nBase);
             }
-        if (mnenc_create(&g_cache.ctx, 0, k, static_cast<int>(blockSize), baseRows.data(), nBase, detailRows.data(), detail[0].data(),
-                         detail[1].data(), detail[2].data()) != MNENC_OK)
-            failWith("mnenc_create");
+        // MNENC_DEVICES="0,1,..." / "all": one image is sharded by block columns over those GPUs; otherwise MNENC_DEVICE (default 0)
+        if (mnenc_create_auto(&g_cache.ctx, k, static_cast<int>(blockSize), baseRows.data(), nBase, detailRows.data(), detail[0].data(),
+                              detail[1].data(), detail[2].data()) != MNENC_OK)
+            failWith("mnenc_create_auto");
         g_cache.K = k;
         g_cache.probe = probe;
     }

@@ -51,6 +51,24 @@ def test_create_rejects_bad_arguments():
     assert L.mnenc_create(C.byref(h), 0, 32, 8, None, 510, p(rows), p(det), p(det), p(det)) == -1        # null
 
 
+def test_create_auto_reads_the_device_list(monkeypatch):
+    """mnenc_create_auto: MNENC_DEVICES must be a comma-separated list of device numbers (or "all"); a malformed list is an
+    argument error before any CUDA call, a well-formed one goes on to mnenc_create / mnenc_create_multi."""
+    L = _lib.load()
+    h = C.c_void_p()
+    base = np.zeros((510, 64), np.float32)
+    rows = np.full(510, 62, np.int32)
+    det = np.zeros((62 * 510, 64), np.float32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    for bad in ("0;1", "a", "0,,x", "-1"):
+        monkeypatch.setenv("MNENC_DEVICES", bad)
+        assert L.mnenc_create_auto(C.byref(h), 32, 8, p(base), 510, p(rows), p(det), p(det), p(det)) == -1, bad
+        assert b"MNENC_DEVICES" in L.mnenc_last_error()
+    monkeypatch.setenv("MNENC_DEVICES", "0")
+    assert L.mnenc_create_auto(C.byref(h), 32, 16, p(base), 510, p(rows), p(det), p(det), p(det)) == -1  # reaches mnenc_create: block size
+    assert b"block_size" in L.mnenc_last_error()
+
+
 def test_gpu_entry_points_fail_loudly_without_device():
     import torch
     if torch.cuda.is_available():
