@@ -166,22 +166,27 @@ struct PlanWire {
 
 }  // namespace
 
-// Code tables of all sequences with the builds dealt over the ranks. stats[q] are this rank's entries of sequence q (same SET
-// on every rank after the histogram merge, order may differ); on return plans[q].code/len follow this rank's order.
-int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats, std::vector<SequencePlan>& plans) {
-    StripeComm* sc = c->comm.get();
-    std::string err;
-    const NcclApi* nccl = ncclApi(&err);
-    if (!nccl) return fail(MNENC_ERR_CUDA, err);
-    const int nSeq = static_cast<int>(stats.size()), nr = sc->nranks, me = sc->rank;
+// Which sequences rank `me` builds: largest alphabets first, dealt round-robin (the same list on every rank: the alphabet
+// sizes are those of the merged histogram).
+static std::vector<int> shareOf(const std::vector<std::vector<SymbolStat>>& stats, int me, int nr) {
+    const int nSeq = static_cast<int>(stats.size());
     std::vector<int> byLoad(nSeq);
     std::iota(byLoad.begin(), byLoad.end(), 0);
-    std::stable_sort(byLoad.begin(), byLoad.end(), [&](int a, int b2) { return stats[a].size() > stats[b2].size(); });  // identical on every rank
-    std::vector<int> mineSeqs;
-    for (int i = me; i < nSeq; i += nr) mineSeqs.push_back(byLoad[i]);
-    c->pool->parallelFor(static_cast<int>(mineSeqs.size()), [&](int i) { planSequence(stats[mineSeqs[i]], plans[mineSeqs[i]]); });
-    // serialise
-    std::vector<unsigned char> wire;
+    std::stable_sort(byLoad.begin(), byLoad.end(), [&](int a, int b2) { return stats[a].size() > stats[b2].size(); });
+    std::vector<int> mine;
+    for (int i = me; i < nSeq; i += nr) mine.push_back(byLoad[i]);
+    return mine;
+}
+
+// This rank's share of the code tables: built into plans[q] and serialised for the peers.
+void planShardBuild(const std::vector<std::vector<SymbolStat>>& stats, int me, int nr, HostPool* pool, std::vector<SequencePlan>& plans,
+                    std::vector<unsigned char>& wire) {
+    const std::vector<int> mineSeqs = shareOf(stats, me, nr);
+    auto build = [&](int i) { planSequence(stats[mineSeqs[i]], plans[mineSeqs[i]]); };
+    if (pool) pool->parallelFor(static_cast<int>(mineSeqs.size()), build);
+    else
+        for (int i = 0; i < static_cast<int>(mineSeqs.size()); ++i) build(i);
+    wire.clear();
     for (int q : mineSeqs) {
         const SequencePlan& p = plans[q];
         PlanWire w{};
@@ -201,6 +206,57 @@ int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats,
             sym[2 * k + 1] = p.code[k];
         }
     }
+}
+
+// A peer's serialised tables -> plans[q] in THIS rank's entry order (the peers hold the same set of (sequence, symbol) entries
+// after the histogram merge, possibly in another order: codes are matched by symbol).
+int planShardApply(const std::vector<std::vector<SymbolStat>>& stats, const unsigned char* p0, size_t size, std::vector<SequencePlan>& plans) {
+    const int nSeq = static_cast<int>(stats.size());
+    std::vector<uint32_t> slot(65536);
+    size_t at = 0;
+    while (at + sizeof(PlanWire) <= size) {
+        PlanWire w;
+        std::memcpy(&w, p0 + at, sizeof(w));
+        if (w.seq >= static_cast<uint32_t>(nSeq)) return fail(MNENC_ERR_INTERNAL, "bad code table from a peer");
+        const size_t hb = (static_cast<size_t>(w.headerBytes) + 7) / 8 * 8;
+        if (at + sizeof(PlanWire) + hb + static_cast<size_t>(w.nSym) * 8 > size) return fail(MNENC_ERR_INTERNAL, "truncated code table from a peer");
+        SequencePlan& p = plans[w.seq];
+        const std::vector<SymbolStat>& mineStats = stats[w.seq];
+        p = SequencePlan{};
+        p.golomb = w.golombM != 0;
+        p.golombM = w.golombM;
+        p.eofCode = w.eofCode, p.eofLen = static_cast<uint8_t>(w.eofLen), p.maxCodeLen = w.maxCodeLen;
+        p.payloadBits = w.payloadBits;
+        p.header.nbits = w.headerBits;
+        p.header.bytes.assign(p0 + at + sizeof(w), p0 + at + sizeof(w) + w.headerBytes);
+        p.code.assign(mineStats.size(), 0u);
+        p.len.assign(mineStats.size(), 0);
+        if (w.nSym) {
+            if (w.nSym != mineStats.size()) return fail(MNENC_ERR_INTERNAL, "code table of a peer does not match the merged histogram");
+            for (uint32_t k = 0; k < w.nSym; ++k) slot[mineStats[k].symbol & 0xFFFFu] = k;
+            const uint32_t* sym = reinterpret_cast<const uint32_t*>(p0 + at + sizeof(w) + hb);
+            for (uint32_t k = 0; k < w.nSym; ++k) {
+                const uint32_t s = sym[2 * k] & 0xFFFFu, mk = slot[s];
+                if (mk >= w.nSym || mineStats[mk].symbol != s) return fail(MNENC_ERR_INTERNAL, "code table of a peer names an unknown symbol");
+                p.code[mk] = sym[2 * k + 1];
+                p.len[mk] = static_cast<uint8_t>(sym[2 * k] >> 16);
+            }
+        }
+        at += sizeof(PlanWire) + hb + static_cast<size_t>(w.nSym) * 8;
+    }
+    return MNENC_OK;
+}
+
+// Code tables of all sequences with the builds dealt over the ranks. stats[q] are this rank's entries of sequence q (same SET
+// on every rank after the histogram merge, order may differ); on return plans[q].code/len follow this rank's order.
+int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats, std::vector<SequencePlan>& plans) {
+    StripeComm* sc = c->comm.get();
+    std::string err;
+    const NcclApi* nccl = ncclApi(&err);
+    if (!nccl) return fail(MNENC_ERR_CUDA, err);
+    const int nr = sc->nranks, me = sc->rank;
+    std::vector<unsigned char> wire;
+    planShardBuild(stats, me, nr, c->pool.get(), plans, wire);
     // sizes, then the tables
     std::vector<uint64_t> sizes(nr);
     const uint64_t mySize = wire.size();
@@ -209,40 +265,9 @@ int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats,
     wire.resize(maxSize);
     std::vector<unsigned char> all(maxSize * nr);
     if (int rc = allGatherHost(c, nccl, wire.data(), all.data(), maxSize)) return rc;
-    std::vector<uint32_t> slot(65536);
     for (int r = 0; r < nr; ++r) {
         if (r == me) continue;
-        const unsigned char* p0 = all.data() + maxSize * r;
-        size_t at = 0;
-        while (at + sizeof(PlanWire) <= sizes[r]) {
-            PlanWire w;
-            std::memcpy(&w, p0 + at, sizeof(w));
-            if (w.seq >= static_cast<uint32_t>(nSeq)) return fail(MNENC_ERR_INTERNAL, "bad code table from a peer");
-            const size_t hb = (w.headerBytes + 7) / 8 * 8;
-            SequencePlan& p = plans[w.seq];
-            const std::vector<SymbolStat>& mineStats = stats[w.seq];
-            p = SequencePlan{};
-            p.golomb = w.golombM != 0;
-            p.golombM = w.golombM;
-            p.eofCode = w.eofCode, p.eofLen = static_cast<uint8_t>(w.eofLen), p.maxCodeLen = w.maxCodeLen;
-            p.payloadBits = w.payloadBits;
-            p.header.nbits = w.headerBits;
-            p.header.bytes.assign(p0 + at + sizeof(w), p0 + at + sizeof(w) + w.headerBytes);
-            p.code.assign(mineStats.size(), 0u);
-            p.len.assign(mineStats.size(), 0);
-            if (w.nSym) {
-                if (w.nSym != mineStats.size()) return fail(MNENC_ERR_INTERNAL, "code table of a peer does not match the merged histogram");
-                for (uint32_t k = 0; k < w.nSym; ++k) slot[mineStats[k].symbol & 0xFFFFu] = k;
-                const uint32_t* sym = reinterpret_cast<const uint32_t*>(p0 + at + sizeof(w) + hb);
-                for (uint32_t k = 0; k < w.nSym; ++k) {
-                    const uint32_t s = sym[2 * k] & 0xFFFFu, mk = slot[s];
-                    if (mk >= w.nSym || mineStats[mk].symbol != s) return fail(MNENC_ERR_INTERNAL, "code table of a peer names an unknown symbol");
-                    p.code[mk] = sym[2 * k + 1];
-                    p.len[mk] = static_cast<uint8_t>(sym[2 * k] >> 16);
-                }
-            }
-            at += sizeof(PlanWire) + hb + static_cast<size_t>(w.nSym) * 8;
-        }
+        if (int rc = planShardApply(stats, all.data() + maxSize * r, static_cast<size_t>(sizes[r]), plans)) return rc;
     }
     return MNENC_OK;
 }
@@ -437,6 +462,37 @@ int mnenc_create_multi(mnenc_t** out, const int* devices, int n_devices, int K, 
         if (i) ctxs[0]->groupPeers.push_back(ctxs[i]);
     }
     *out = ctxs[0];
+    return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
+}
+
+int mnenc_debug_plan_sharded(const uint32_t* symbols, const uint32_t* freqs, const uint32_t* first_pos, const uint32_t* seq_start, int n_seq,
+                             int nranks, uint32_t* codes, uint8_t* lens, uint64_t* payload_bits, uint32_t* golomb_m) try {
+    if (!symbols || !freqs || !first_pos || !seq_start || !codes || !lens || !payload_bits || !golomb_m || n_seq < 1 || nranks < 1)
+        return fail(MNENC_ERR_ARG, "bad argument");
+    // rank 0 holds the entries in the caller's order, every other rank in reverse order (the merge kernel gives no order guarantee)
+    std::vector<std::vector<SymbolStat>> fwd(n_seq), rev(n_seq);
+    for (int q = 0; q < n_seq; ++q) {
+        for (uint32_t e = seq_start[q]; e < seq_start[q + 1]; ++e) fwd[q].push_back(SymbolStat{symbols[e], freqs[e], first_pos[e]});
+        rev[q].assign(fwd[q].rbegin(), fwd[q].rend());
+    }
+    std::vector<SequencePlan> plans(n_seq);
+    std::vector<unsigned char> wire;
+    planShardBuild(fwd, 0, nranks, nullptr, plans, wire);
+    for (int r = 1; r < nranks; ++r) {
+        std::vector<SequencePlan> theirs(n_seq);
+        planShardBuild(rev, r, nranks, nullptr, theirs, wire);
+        if (int rc = planShardApply(fwd, wire.data(), wire.size(), plans)) return rc;
+    }
+    for (int q = 0; q < n_seq; ++q) {
+        payload_bits[q] = plans[q].payloadBits;
+        golomb_m[q] = plans[q].golomb ? plans[q].golombM : 0u;
+        for (uint32_t e = seq_start[q]; e < seq_start[q + 1]; ++e) {
+            codes[e] = plans[q].golomb ? 0u : plans[q].code[e - seq_start[q]];
+            lens[e] = plans[q].golomb ? 0 : plans[q].len[e - seq_start[q]];
+        }
+    }
     return MNENC_OK;
 } catch (...) {
     return mnenc::abiCaught();

@@ -220,6 +220,13 @@ int mnenc_last_stripe_timing(mnenc_t* ctx, float* ms16);
 int mnenc_create_multi(mnenc_t** out, const int* devices, int n_devices, int K, int block_size, const float* base_rowmajor, int n_base,
                        const int32_t* detail_rows, const float* detailY, const float* detailU, const float* detailV);
 /*
+ * Host-logic test hook of the in-library stripe exchange (CPU only): the 193 code-table builds dealt over `nranks` ranks,
+ * serialised, and applied on rank 0 (whose peers hold the same entries in another order). Entries of sequence q are
+ * [seq_start[q], seq_start[q + 1]). Must give exactly what mnenc_debug_plan_sequence gives per sequence.
+ */
+int mnenc_debug_plan_sharded(const uint32_t* symbols, const uint32_t* freqs, const uint32_t* first_pos, const uint32_t* seq_start, int n_seq,
+                             int nranks, uint32_t* codes, uint8_t* lens, uint64_t* payload_bits, uint32_t* golomb_m);
+/*
  * mnenc_create or mnenc_create_multi, chosen by the environment - what a host with no device argument of its own calls (the shim
  * behind encodeImageFast, CompressedImage.cpp:578; the Compression front end): MNENC_DEVICES="0,1,2" or "all" names the GPUs of a
  * multi-GPU context, otherwise MNENC_DEVICE (default 0) names the one GPU.

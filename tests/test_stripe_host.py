@@ -135,3 +135,38 @@ def test_rle_stitching_matches_oracle(world, oraclelib):
         assert np.array_equal(np.asarray(g, np.uint16), want), (v.size, len(g), want.size)
         assert raw_len[i] == v.size and rle_len[i] == want.size
         assert bool(use_rle[i]) == (want.size + 4 < v.size)   # CompressedImage.cpp:508-516
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 3, 8])
+def test_sharded_code_tables_equal_unsharded(nranks):
+    """In-library stripe exchange (csrc/stripe_comm.cu planShardBuild / planShardApply): the table builds dealt over the ranks,
+    serialised and applied on a rank that holds its entries in another order must give the codes, lengths, Golomb parameters
+    and payload sizes of the plain per-sequence build (mnenc_debug_plan_sequence)."""
+    import ctypes as C
+
+    from imageexperiments_b200 import _lib
+    from imageexperiments_b200.compressed import planSequenceHost
+    rng = np.random.default_rng(1234 + nranks)
+    n_seq = 25
+    syms, freqs, first, start = [], [], [], [0]
+    for q in range(n_seq):
+        n = [0, 1, 2, 7, 300, 2000][q % 6] if q < 18 else int(rng.integers(1, 400))
+        s = rng.choice(65535, size=n, replace=False).astype(np.uint32)
+        # geometric-like counts for some sequences (Golomb wins), flat ones for others (Huffman wins)
+        f = (rng.geometric(0.02, size=n) if q % 2 else rng.integers(1, 50, size=n)).astype(np.uint32)
+        syms.append(s), freqs.append(f), first.append(rng.permutation(n).astype(np.uint32))
+        start.append(start[-1] + n)
+    symbols, fr, fp = np.concatenate(syms), np.concatenate(freqs), np.concatenate(first)
+    start = np.asarray(start, np.uint32)
+    n = int(start[-1])
+    codes, lens = np.zeros(n, np.uint32), np.zeros(n, np.uint8)
+    bits, gm = np.zeros(n_seq, np.uint64), np.zeros(n_seq, np.uint32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    _lib.check(_lib.load().mnenc_debug_plan_sharded(p(symbols), p(fr), p(fp), p(start), n_seq, nranks, p(codes), p(lens), p(bits), p(gm)))
+    for q in range(n_seq):
+        want = planSequenceHost(syms[q], freqs[q], first[q])
+        a, b = int(start[q]), int(start[q + 1])
+        assert int(gm[q]) == want["golomb_m"], q
+        assert int(bits[q]) == want["payload_bits"], q
+        if want["golomb_m"] == 0:
+            assert np.array_equal(codes[a:b], want["codes"]) and np.array_equal(lens[a:b], want["lens"]), q
