@@ -485,8 +485,9 @@ def run_ours(args):
     mp_total = world * args.steps * BATCH * W * H / 1e6
     value = mp_total / dt_dev
     e2e = mp_total / dt_e2e
-    stripes = stripes_record(ctx, rank, world, local, 5, barrier, max_over_ranks)
-    frames = batch1080p_record(ctx, rank, world, barrier, max_over_ranks)
+    quick = os.environ.get("MNENC_BENCH_SKIP_EXTRAS") == "2"  # (development switch: the headline pass only)
+    stripes = None if quick else stripes_record(ctx, rank, world, local, 5, barrier, max_over_ranks)
+    frames = None if quick else batch1080p_record(ctx, rank, world, barrier, max_over_ranks)
 
     if rank == 0:
         clocks = sampler.stop(windows)

@@ -80,8 +80,9 @@ extern "C" int mnenc_encode_batch_rgb8(mnenc_t* c, size_t n_images, const uint8_
                 const size_t most = std::clamp<size_t>(1572864 / nbcFrame, 1, 16);
                 const size_t rounds = (n_images + lanes.size() * most - 1) / (lanes.size() * most);
                 group = std::max<size_t>(1, (n_images + lanes.size() * rounds - 1) / (lanes.size() * rounds));
-                if (const char* e = std::getenv("MNENC_FRAME_GROUP")) group = std::clamp<size_t>(static_cast<size_t>(std::atoi(e)), 1, 64);
             }
+            if (uniform)
+                if (const char* e = std::getenv("MNENC_FRAME_GROUP")) group = std::clamp<size_t>(static_cast<size_t>(std::atoi(e)), 1, 64);
         }
     }
     std::atomic<size_t> next{0};

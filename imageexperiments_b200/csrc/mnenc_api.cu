@@ -243,6 +243,10 @@ int runBackend(mnenc_ctx* c, size_t width, size_t height, uint8_t** out, size_t*
     c->histDirty = true;  // until the touched bins have been reset: an early return leaves stale counts (ensureHistogram)
     c->launches += launchHistogram(b, upperM, nSeq, st);
     CU(cudaEventRecord(c->ev[4], st));
+    if (c->failNextBackend) {  // test hook (mnenc_debug_fail_next_backend): leave through an ordinary error return with the bins populated
+        c->failNextBackend = false;
+        return fail(MNENC_ERR_INTERNAL, "injected failure after the histogram (test hook)");
+    }
     const uint32_t firstChunk = 1u << 16;
     CU(c->hEntries.ensure(static_cast<size_t>(firstChunk) * sizeof(HistEntry)));
     CU(cudaMemcpyAsync(c->hSeqTable.p, b.seqTable, sizeof(SeqTable), cudaMemcpyDeviceToHost, st));
@@ -855,6 +859,14 @@ int mnenc_debug_plan_sequence(const uint32_t* symbols, const uint32_t* freqs, co
     *payload_bits = plan.payloadBits;
     if (plan.header.bytes.size() > header_cap) return fail(MNENC_ERR_ARG, "header buffer too small");
     if (header_bytes) std::memcpy(header_bytes, plan.header.bytes.data(), plan.header.bytes.size());
+    return MNENC_OK;
+} catch (...) {
+    return mnenc::abiCaught();
+}
+
+int mnenc_debug_fail_next_backend(mnenc_t* c) try {
+    if (!c) return fail(MNENC_ERR_ARG, "null argument");
+    c->failNextBackend = true;
     return MNENC_OK;
 } catch (...) {
     return mnenc::abiCaught();

@@ -157,6 +157,7 @@ struct mnenc_ctx {
     uint8_t* stripeResult = nullptr;   // striped encode, rank 0: result buffer already filled by the chunked reduce + D2H (stripe_comm.cu)
     cudaStream_t copyStream = nullptr; // second stream of that pipeline, created on first use
     cudaEvent_t evChunk[4] = {};
+    bool failNextBackend = false;      // test hook: the next back end returns an error right after its histogram launch
     uint32_t frameBc = 0;      // block-channel offset of the frame the back end works on (frames that shared one pursuit)
     mnenc::DevBuf frameTab;    // device pointers of the frames of a group
     mnenc::PinBuf hFrameTab;

@@ -220,6 +220,11 @@ int mnenc_last_stripe_timing(mnenc_t* ctx, float* ms16);
 int mnenc_create_multi(mnenc_t** out, const int* devices, int n_devices, int K, int block_size, const float* base_rowmajor, int n_base,
                        const int32_t* detail_rows, const float* detailY, const float* detailU, const float* detailV);
 /*
+ * Test hook: the next encode on this context fails with MNENC_ERR_INTERNAL right after its histogram kernel has run - an ordinary
+ * error return with the histogram bins populated. The encode after that must be unaffected (the context re-clears its tables).
+ */
+int mnenc_debug_fail_next_backend(mnenc_t* ctx);
+/*
  * Host-logic test hook of the in-library stripe exchange (CPU only): the 193 code-table builds dealt over `nranks` ranks,
  * serialised, and applied on rank 0 (whose peers hold the same entries in another order). Entries of sequence q are
  * [seq_start[q], seq_start[q + 1]). Must give exactly what mnenc_debug_plan_sequence gives per sequence.

@@ -268,3 +268,25 @@ def test_full_size_quality_sweep(ctx, oracle_ctx_factory, q):
     assert lo < mean_atoms < hi, mean_atoms
     oc.close()
     set_quality(ctx, 3.5)
+
+
+def test_encode_after_a_failed_encode_is_clean(dictionary, oracle_ctx_factory):
+    """An encode that fails between the histogram and its reset (an ordinary error return, injected by the test hook) must not
+    leave counts behind for the next encode on the same context - nor on a batch lane, which persists across calls."""
+    from imageexperiments_b200 import _lib
+    ctx = mn.createCompressionContextFast(32, 8, 3.5, dictionary=dictionary, device=0)
+    try:
+        oc = oracle_ctx_factory(ctx.Quant)
+        a, b = synthetic_rgb(200, 136, 5), synthetic_rgb(328, 240, 6)
+        want_a, want_b = oc.encode(a), oc.encode(b)
+        assert mn.encodeImageFast(a, ctx) == want_a
+        _lib.check(_lib.load().mnenc_debug_fail_next_backend(ctx._h))
+        with pytest.raises(mn.MnencError) as e:
+            mn.encodeImageFast(b, ctx)
+        assert e.value.code == -4 and "injected" in str(e.value)
+        assert mn.encodeImageFast(a, ctx) == want_a   # stale bins of image b would change the code tables
+        assert mn.encodeImageFast(b, ctx) == want_b
+        assert [bytes(x) for x in mn.encodeImageBatch([a, b, a], ctx)] == [want_a, want_b, want_a]
+        oc.close()
+    finally:
+        ctx.close()
