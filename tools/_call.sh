@@ -1,16 +1,11 @@
 mkdir -p gpurun_out
-L=gpurun_out/r02_call25.log
+L=gpurun_out/r02_call27.log
 : > $L
-run() { echo "--- $1" >> $L; env $1 MNENC_BENCH_SKIP_EXTRAS=2 timeout 200 python bench.py --steps 10 --warmup 3 2>/dev/null | python -c "
-import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('value',d['value'],'e2e',d['e2e']['value'],'mp_ms',d['roofline']['ms_per_launch'],'lat',d['single_image_latency_ms'])" >> $L 2>&1; }
-run "MNENC_LANES=6"
-run "MNENC_LANES=8"
-run "MNENC_LANES=12"
-run "MNENC_FRAME_GROUP=2"
-run "MNENC_FRAME_GROUP=2 MNENC_LANES=4"
-run "MNENC_FRAME_GROUP=4 MNENC_LANES=4"
-cat $L
-echo "=== failure-injection test" >> $L
-timeout 200 python -m pytest tests/test_gpu_parity.py -x -q -k "failed_encode" 2>&1 | tail -n 3 >> $L
-tail -n 4 $L
+echo "=== wave check" >> $L
+timeout 90 python tools/mp_check.py --sizes 64x64,200x136 --q 3.5 --time 0 >> $L 2>&1; rc=$?; echo "rc=$rc" >> $L
+if [ $rc -ne 0 ]; then tail -n 30 $L; exit 0; fi
+timeout 200 python tools/mp_check.py 2>&1 >> $L; echo "rc=$?" >> $L
+echo "=== ncu launch list" >> $L
+timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r02_wave_launches_16mp_h.csv python tools/profile_encode.py 2 >> $L 2>&1; echo "rc=$?" >> $L
+python tools/agg_launches.py gpurun_out/r02_wave_launches_16mp_h.csv | grep -i "wave\|matching" >> $L 2>&1
+grep -v "==WARNING\|==PROF" $L | tail -n 40
