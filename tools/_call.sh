@@ -1,12 +1,11 @@
 mkdir -p gpurun_out
-L=gpurun_out/r02_call28.log
+L=gpurun_out/r02_call29.log
 : > $L
-for lanes in 6 9 12 16; do
-  echo "--- MNENC_LANES=$lanes, 192 frames" >> $L
-  MNENC_LANES=$lanes BATCH_FRAMES=192 BATCH_SKIP_PARITY=1 timeout 120 python tools/batch_check.py 2>&1 | tail -n 1 >> $L
-done
-echo "--- MNENC_LANES=12 MNENC_FRAME_GROUP=8" >> $L
-MNENC_LANES=12 MNENC_FRAME_GROUP=8 BATCH_FRAMES=192 BATCH_SKIP_PARITY=1 timeout 120 python tools/batch_check.py 2>&1 | tail -n 1 >> $L
-echo "--- MNENC_LANES=16 MNENC_FRAME_GROUP=6" >> $L
-MNENC_LANES=16 MNENC_FRAME_GROUP=6 BATCH_FRAMES=192 BATCH_SKIP_PARITY=1 timeout 120 python tools/batch_check.py 2>&1 | tail -n 1 >> $L
-cat $L
+echo "=== smoke" >> $L
+timeout 120 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -n 2 >> $L
+echo "=== pytest -m gpu" >> $L
+timeout 1500 python -m pytest tests/ -x -q -m gpu 2>&1 | tail -n 6 >> $L
+echo "=== bench N=1" >> $L
+( time timeout 900 python bench.py ) > gpurun_out/r02_bench_n1_c.json 2>> $L; echo "rc=$?" >> $L
+tail -n 1 gpurun_out/r02_bench_n1_c.json | cut -c1-300 >> $L
+tail -n 30 $L
