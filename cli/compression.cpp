@@ -111,6 +111,20 @@ std::vector<uint8_t> loadFile(const std::string& path) {
 // `.mndict` (imageexperiments_b200/dictionary.py): "MNDICT1\0" | i32 n_base | i32 cols | i32 rows[n_base] | f32 base | f32 detail Y,U,V
 mnenc_t* createContext(const std::string& exeDir) {
     const char* env = std::getenv("MNENC_DICT");
+    if (env && std::string(env) == "builtin") {
+        // the dictionary computed by the library itself (mnenc_build_dictionary): no reference build needed, but its KLT rows are
+        // this library's own codec revision - encode and decode with the same setting
+        std::vector<float> base(512 * 64), det[3];
+        for (auto& d : det) d.resize(static_cast<size_t>(512) * 64 * 64);
+        std::vector<int32_t> rows(512);
+        int nBase = 0;
+        if (mnenc_build_dictionary(kBlockSize, 0, base.data(), &nBase, rows.data(), det[0].data(), det[1].data(), det[2].data()) != MNENC_OK)
+            dieLib("mnenc_build_dictionary");
+        mnenc_t* ctx = nullptr;
+        if (mnenc_create_auto(&ctx, kK, kBlockSize, base.data(), nBase, rows.data(), det[0].data(), det[1].data(), det[2].data()) != MNENC_OK)
+            dieLib("mnenc_create_auto");
+        return ctx;
+    }
     const std::string path = env ? env : exeDir + "/data/dict_bs8.mndict";
     const std::vector<uint8_t> raw = loadFile(path);
     if (raw.size() < 16 || std::memcmp(raw.data(), "MNDICT1\0", 8) != 0) die(path + ": not a .mndict file");

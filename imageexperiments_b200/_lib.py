@@ -21,7 +21,7 @@ EXPORTS = (
     "mnenc_decode_rgb8", "mnenc_decode_rgb8_device", "mnenc_decode_batch_rgb8", "mnenc_stream_info", "mnenc_debug_parse",
     "mnenc_stripe_begin", "mnenc_stripe_rle", "mnenc_stripe_histogram", "mnenc_stripe_plan", "mnenc_stripe_pack", "mnenc_stripe_finish",
     "mnenc_comm_unique_id", "mnenc_comm_init_rank", "mnenc_comm_destroy", "mnenc_encode_striped_rgb8", "mnenc_last_stripe_timing",
-    "mnenc_create_multi", "mnenc_create_auto", "mnenc_last_plan", "mnenc_debug_plan_sharded", "mnenc_debug_fail_next_backend",
+    "mnenc_create_multi", "mnenc_create_auto", "mnenc_last_plan", "mnenc_debug_plan_sharded", "mnenc_debug_fail_next_backend", "mnenc_build_dictionary",
 )
 
 
@@ -77,6 +77,7 @@ def load() -> C.CDLL:
     L.mnenc_create_multi.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp]
     L.mnenc_debug_plan_sharded.argtypes = [_vp, _vp, _vp, _vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp]
     L.mnenc_debug_fail_next_backend.argtypes = [_vp]
+    L.mnenc_build_dictionary.argtypes = [C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp]
     L.mnenc_create_auto.argtypes = [_vp, C.c_int, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp]
     L.mnenc_decode_rgb8.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp]
     L.mnenc_decode_rgb8_device.argtypes = [_vp, _vp, _sz, _vp, _sz, _sz, _vp, _vp]

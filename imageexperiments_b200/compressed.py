@@ -91,6 +91,8 @@ def createCompressionContextFast(K: int = 32, blockSize: int = 8, bppAllocation:
     """compressed::createCompressionContextFast (CompressedImage.cpp:317-341); the dictionary is imported data."""
     if dictionary is None:
         dictionary = Dictionary.load()
+    elif isinstance(dictionary, str) and dictionary == "builtin":  # computed by the library: its own codec revision (Dictionary.build)
+        dictionary = Dictionary.build(blockSize)
     if isinstance(bppAllocation, str):
         if bppAllocation != "max":
             raise ValueError("quality is a number or 'max'")

@@ -53,6 +53,27 @@ class Dictionary:
                 f.write(d.tobytes())
 
     @staticmethod
+    def build(blockSize: int = 8, threads: int = 0) -> "Dictionary":
+        """The dictionary computed here instead of imported (mnenc_build_dictionary, csrc/dictionary_host.cpp):
+        shapes and segment atoms are those of the reference bit for bit, the KLT refinement rows come from a pinned eigen
+        solver (double Jacobi) and therefore define their OWN codec revision - streams written with this dictionary decode with
+        this dictionary, not with a reference build's."""
+        import ctypes as C
+
+        from . import _lib
+        L = _lib.load()
+        cols = blockSize * blockSize
+        base = np.zeros((512, cols), np.float32)
+        rows = np.zeros(512, np.int32)
+        det = [np.zeros((512 * cols, cols), np.float32) for _ in range(3)]
+        n = C.c_int(0)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        _lib.check(L.mnenc_build_dictionary(blockSize, threads, p(base), C.byref(n), p(rows), p(det[0]), p(det[1]), p(det[2])))
+        nb = n.value
+        total = int(rows[:nb].sum())
+        return Dictionary(base[:nb].copy(), rows[:nb].copy(), [d[:total].copy() for d in det])
+
+    @staticmethod
     def load(path: str = DEFAULT_PATH) -> "Dictionary":
         if not os.path.exists(path):
             raise FileNotFoundError(f"{path} is missing: it is exported from the reference build by __graft_entry__.build() "

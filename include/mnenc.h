@@ -220,6 +220,18 @@ int mnenc_last_stripe_timing(mnenc_t* ctx, float* ms16);
 int mnenc_create_multi(mnenc_t** out, const int* devices, int n_devices, int K, int block_size, const float* base_rowmajor, int n_base,
                        const int32_t* detail_rows, const float* detailY, const float* detailU, const float* detailV);
 /*
+ * The dictionary, computed instead of imported (host only, no GPU): what the dictionary half of
+ * createCompressionContextFast builds at start-up (CompressedImage.cpp:317-341 -> BasisSet.cpp:204-297 distinctLineShapes,
+ * :430-511 createSegmentDictionaryFast, :618-721 createIntraSegmentDictionaryFast). Outputs in the layout mnenc_create takes:
+ * base_rowmajor [n_base][64] (capacity 512 rows), detail_rows [n_base] (capacity 512), detailY/U/V: the groups concatenated in
+ * atom order (capacity 512 * 64 rows of 64 each). Shapes, heights and segment atoms equal the reference's bit for bit; the KLT
+ * rows come from a pinned solver (cyclic Jacobi in double) instead of Eigen's float eigensolver, whose rounding is
+ * build-dependent - so a stream written with this dictionary decodes with this dictionary, not with a reference build's.
+ * threads <= 0: all host threads. Only block_size 8.
+ */
+int mnenc_build_dictionary(int block_size, int threads, float* base_rowmajor, int* n_base, int32_t* detail_rows, float* detailY,
+                           float* detailU, float* detailV);
+/*
  * Test hook: the next encode on this context fails with MNENC_ERR_INTERNAL right after its histogram kernel has run - an ordinary
  * error return with the histogram bins populated. The encode after that must be unaffected (the context re-clears its tables).
  */

@@ -117,3 +117,24 @@ def test_modes_equal_the_reference(exe, tmp_path, reflib):
     assert run("-c", "max", src, mnf).returncode == 0 and open(mnf, "rb").read() == want_max
     r = run("-d", src, dec)  # not a .mn stream
     assert r.returncode == 1 and "mnenc_decode_rgb8" in r.stderr
+
+
+@pytest.mark.gpu
+def test_builtin_dictionary_round_trip(exe, tmp_path):
+    """MNENC_DICT=builtin: the front end without any file from a reference build (mnenc_build_dictionary). The stream is this
+    library's own codec revision: it must decode with the same setting to the quality the reference dictionary gives."""
+    from imageexperiments_b200.synth import synthetic_rgb
+    img = synthetic_rgb(200, 136, 7)
+    src, mnf, dec = str(tmp_path / "i.ppm"), str(tmp_path / "o.mn"), str(tmp_path / "d.ppm")
+    write_ppm(src, img)
+    env = dict(os.environ, MNENC_DICT="builtin")
+    r = subprocess.run([EXE, "-n", "3.5", src, dec], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stderr
+    m = re.search(r"PSNR (\S+) bpp (\S+)", r.stdout)
+    r2 = run("-n", "3.5", src, dec)
+    m2 = re.search(r"PSNR (\S+) bpp (\S+)", r2.stdout)
+    assert m and m2 and abs(float(m.group(1)) - float(m2.group(1))) < 0.25 and abs(float(m.group(2)) - float(m2.group(2))) < 0.05 * float(m2.group(2))
+    assert subprocess.run([EXE, "-c", "3.5", src, mnf], capture_output=True, text=True, timeout=300, env=env).returncode == 0
+    assert subprocess.run([EXE, "-d", mnf, dec], capture_output=True, text=True, timeout=300, env=env).returncode == 0
+    err = read_ppm(dec).astype(np.float64) - img
+    assert 10 * np.log10(255.0 ** 2 / np.mean(err ** 2)) > 35.0

@@ -290,3 +290,30 @@ def test_encode_after_a_failed_encode_is_clean(dictionary, oracle_ctx_factory):
         oc.close()
     finally:
         ctx.close()
+
+
+def test_built_dictionary_is_a_working_codec_revision(dictionary, oraclelib):
+    """Dictionary.build() (csrc/dictionary_host.cpp) instead of the dictionary imported from the reference build:
+    GPU encoder and decoder must stay bit-exact against the CPU oracle run with the SAME dictionary, and the rate / distortion of
+    the new revision must be that of the reference's dictionary (the KLT rows span the same spaces)."""
+    from conftest import make_oracle_ctx
+    from imageexperiments_b200.dictionary import Dictionary
+    built = Dictionary.build()
+    assert np.array_equal(built.base, dictionary.base) and built.sha256() != dictionary.sha256()
+    img = synthetic_rgb(512, 384, 21)
+    out = {}
+    for name, d in (("built", built), ("reference", dictionary)):
+        ctx = mn.createCompressionContextFast(32, 8, 3.5, dictionary=d, device=0)
+        oc = make_oracle_ctx(oraclelib, d, ctx.Quant)
+        try:
+            data = bytes(mn.encodeImageFast(img, ctx))
+            assert data == oc.encode(img), name
+            px = mn.decodeImageFast(data, ctx)
+            assert np.array_equal(px, oc.decode(data)), name
+            err = px.astype(np.float64) - img
+            out[name] = (len(data), 10 * np.log10(255.0 ** 2 / np.mean(err ** 2)))
+        finally:
+            oc.close()
+            ctx.close()
+    (nb, pb), (nr, pr) = out["built"], out["reference"]
+    assert abs(pb - pr) < 0.25 and abs(nb - nr) < 0.03 * nr, out
