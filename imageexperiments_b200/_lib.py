@@ -22,6 +22,7 @@ EXPORTS = (
     "mnenc_stripe_begin", "mnenc_stripe_rle", "mnenc_stripe_histogram", "mnenc_stripe_plan", "mnenc_stripe_pack", "mnenc_stripe_finish",
     "mnenc_comm_unique_id", "mnenc_comm_init_rank", "mnenc_comm_destroy", "mnenc_encode_striped_rgb8", "mnenc_last_stripe_timing",
     "mnenc_create_multi", "mnenc_create_auto", "mnenc_last_plan", "mnenc_debug_plan_sharded", "mnenc_debug_fail_next_backend", "mnenc_build_dictionary",
+    "mnenc_scatter_streams_static",
 )
 
 
@@ -84,6 +85,7 @@ def load() -> C.CDLL:
     L.mnenc_decode_batch_rgb8.argtypes = [_vp, _sz, _vp, _vp, _vp, _vp, _vp]
     L.mnenc_stream_info.argtypes = [_vp, _sz, _vp, _vp, _vp, _vp, _vp]
     L.mnenc_debug_parse.argtypes = [_vp, _sz, _vp, _sz, _vp, _vp, _sz, C.c_int]
+    L.mnenc_scatter_streams_static.argtypes = [_vp, _vp, C.c_int, _sz, _vp, _sz, _vp, _vp]
     _lib = L
     return L
 

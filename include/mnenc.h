@@ -267,6 +267,36 @@ uint32_t mnenc_debug_rle_chunk_size(uint32_t carry, uint32_t len, uint64_t total
 int mnenc_debug_plan_stripes(const uint32_t* records, int nranks, int n_streams, uint32_t* emitted, uint8_t* use_rle, uint64_t* raw_len,
                              uint64_t* rle_len);
 
+/*
+ * The symbol-stream scatter for callers that cannot allocate GPU memory. This entry point has no counterpart in the
+ * reference; it exposes one step of the encoder (the stream scatter of encodeImageFast) in a form that never calls
+ * cudaMalloc, cudaFree or any other allocating routine.
+ *
+ * Who needs it: a plugin inside a host program that owns all of HBM and hands out every byte itself (a foreign cudaMalloc
+ * there either fails or counts as a leak), code on a latency-critical path where an allocator call would synchronise the
+ * device, and processes that gave the whole GPU to one pool at start-up. All other GPU entry points of this header grow
+ * per-context device buffers when they need them and are therefore unusable for such callers.
+ *
+ * Inputs and outputs are the caller's buffers, all in memory of the CURRENT device (cudaSetDevice) except stream_offsets:
+ *   counts_dev[3 * n_blocks]              counts, layout of mnenc_get_symbols; every value must be <= K
+ *   pairs_dev[3 * n_blocks * K * 2]       BasisChoice pairs, layout of mnenc_get_symbols
+ *   streams_dev[streams_capacity]         out: the 6K streams back to back, u16 symbols (2 * sum(counts) <= 6 * K * n_blocks)
+ *   stream_offsets[6K + 1]                out, HOST memory: stream s = streams_dev[stream_offsets[s], stream_offsets[s + 1]),
+ *                                         s = 2 * (layer * K + depth) + {0: deltaId, 1: intCoeff}; same numbering and same
+ *                                         contents as mnenc_debug_parse reports for the finished `.mn` file
+ *   cuda_stream                           a cudaStream_t (NULL = default stream); the call returns after the work is complete
+ * The per-tile offsets the kernels need in between live in a fixed 1.5 MB __device__ array inside the library (present on
+ * every GPU that loads the library, until the process exits). Hence the limit: n_blocks <= 1048576 (8192 x 8192 pixels);
+ * more gives MNENC_ERR_ARG, as does a streams_capacity below stream_offsets[6K] (stream_offsets is still filled in, so the
+ * caller learns the size). Host or foreign-GPU pointers are refused with MNENC_ERR_ARG.
+ * All calls on one GPU share that array, and it keeps the previous call's contents (each call overwrites what it reads, so
+ * nothing needs clearing): calls that overlap on the same GPU - from two threads or two streams - race and must be
+ * serialised by the caller. The first call on each device looks up the array's device address and makes the CUDA runtime
+ * load the library's kernels there; make that first call during start-up, before any stream capture begins.
+ */
+int mnenc_scatter_streams_static(const uint16_t* counts_dev, const uint16_t* pairs_dev, int K, size_t n_blocks, uint16_t* streams_dev,
+                                 size_t streams_capacity, uint64_t* stream_offsets, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
