@@ -72,7 +72,7 @@ void mnenc_free(uint8_t* p);
  * Batch / throughput mode (BASELINE.json configs[4]): n_images independent images -> n_images independent `.mn` streams,
  * what a caller of the reference gets from encodeImageFast in a loop (Compression.cpp:117-123), each stream byte-identical
  * to the one-at-a-time result. Inside, the images are pipelined over lanes (own stream + buffers, one shared dictionary in
- * HBM; MNENC_LANES, default 6, at most 16) so that host stages, H2D and D2H of one image overlap the matching pursuit of another.
+ * HBM; MNENC_LANES, default 9 with >= 12 host threads else 6, at most 16) so that host stages, H2D and D2H of one image overlap the matching pursuit of another.
  * rgb[i]: host pointers (on_device = 0) or pointers into the context's GPU (on_device = 1); out[i] from mnenc_free().
  * On error every out[i] is NULL. mnenc_last_timing/work afterwards describe the whole batch (ms[1] = summed kernel time,
  * ms[7] = wall time of the batch).
@@ -93,9 +93,10 @@ int mnenc_encode_batch_rgb8(mnenc_t* ctx, size_t n_images, const uint8_t* const*
  * The pixels are those of the reference's decoder, bit for bit. A stream the reference would reject (bad magic, no
  * pseudo-EOF) and any stream whose lengths are inconsistent — where the reference reads out of range — give
  * MNENC_ERR_STREAM; block sizes other than 8 and K > 32 give MNENC_ERR_STREAM as well (unsupported).
- * The entropy decode runs on the calling thread (one serial bit chain per image, see decode_host.cpp; environment
- * MNENC_DECODE_THREADS=N > 1 lets the context's host threads help with large Huffman payloads — same result), the block
- * loop on the GPU. mnenc_last_timing afterwards: ms[0] = header + `lengths`, ms[1] = symbol streams, ms[2] = uploads + kernels +
+ * The entropy decode runs on the host (decode_host.cpp), the block loop on the GPU. By default the context's host threads
+ * help the calling thread with large Huffman payloads (speculative chunk starts, same result); they busy-spin for the length
+ * of the call, so on a host shared with other work set the environment variable MNENC_DECODE_THREADS=1, which keeps the
+ * whole read on the calling thread (about 1.7x slower per image). mnenc_last_timing afterwards: ms[0] = header + `lengths`, ms[1] = symbol streams, ms[2] = uploads + kernels +
  * download (host clock), ms[3] = gather + reconstruct kernels (CUDA events), ms[7] = whole call.
  */
 int mnenc_decode_rgb8(mnenc_t* ctx, const uint8_t* mn, size_t mn_bytes, uint8_t** rgb, size_t* width, size_t* height);
