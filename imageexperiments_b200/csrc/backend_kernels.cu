@@ -519,11 +519,11 @@ __global__ void __launch_bounds__(256) compactKernel(uint32_t* hist, uint32_t* f
 }
 // Stripe path, sparse histogram exchange: the all-gathered entry lists of every rank ([nranks][nMax], counts[r] valid each) are
 // merged into the dense tables: SUM of the counts, MIN of the (global) first-occurrence positions, MAX of the largest symbol.
-__global__ void mergeEntriesKernel(const HistEntry* gathered, const uint32_t* counts, int nranks, uint32_t nMax, uint32_t* hist,
+__global__ void mergeEntriesKernel(const HistEntry* gathered, const uint32_t* counts, int countStride, int nranks, uint32_t nMax, uint32_t* hist,
                                    uint32_t* firstPos, uint32_t* maxSym) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const int r = blockIdx.y;
-    if (r >= nranks || i >= counts[r]) return;
+    if (r >= nranks || i >= counts[r * countStride]) return;
     const HistEntry e = gathered[static_cast<size_t>(r) * nMax + i];
     if (e.seq >= static_cast<uint32_t>(kMaxSeq) || e.symbol >= static_cast<uint32_t>(kHistBins)) return;
     const size_t bin = static_cast<size_t>(e.seq) * kHistBins + e.symbol;
@@ -803,9 +803,9 @@ int launchPack(const BackendBuffers& b, uint32_t M, int nSeq, cudaStream_t st) {
     return 3;
 }
 
-int launchMergeEntries(const BackendBuffers& b, const HistEntry* gathered, const uint32_t* counts, int nranks, uint32_t nMax, cudaStream_t st) {
+int launchMergeEntries(const BackendBuffers& b, const HistEntry* gathered, const uint32_t* counts, int countStride, int nranks, uint32_t nMax, cudaStream_t st) {
     if (!nMax) return 0;
-    mergeEntriesKernel<<<dim3((nMax + 255) / 256, static_cast<unsigned>(nranks)), 256, 0, st>>>(gathered, counts, nranks, nMax, b.hist, b.firstPos, b.maxSym);
+    mergeEntriesKernel<<<dim3((nMax + 255) / 256, static_cast<unsigned>(nranks)), 256, 0, st>>>(gathered, counts, countStride, nranks, nMax, b.hist, b.firstPos, b.maxSym);
     return 1;
 }
 

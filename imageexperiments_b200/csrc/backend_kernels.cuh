@@ -121,6 +121,7 @@ int launchDecide(const BackendBuffers& b, const StreamOffsets& so, SeqTable* hos
 int launchHistogram(const BackendBuffers& b, uint32_t upperBoundM, int nSeq, cudaStream_t st);
 int launchPack(const BackendBuffers& b, uint32_t M, int nSeq, cudaStream_t st);
 int launchResetHistogram(const BackendBuffers& b, uint32_t nEntries, cudaStream_t st);
-int launchMergeEntries(const BackendBuffers& b, const HistEntry* gathered, const uint32_t* counts, int nranks, uint32_t nMax, cudaStream_t st);
+// counts[r * countStride] = valid entries of rank r (the in-library exchange gathers {count, status} pairs: stride 2)
+int launchMergeEntries(const BackendBuffers& b, const HistEntry* gathered, const uint32_t* counts, int countStride, int nranks, uint32_t nMax, cudaStream_t st);
 
 }  // namespace mnenc

@@ -154,6 +154,7 @@ struct mnenc_ctx {
     // stripe protocol
     std::unique_ptr<mnenc::StripeState, void (*)(mnenc::StripeState*)> stripe{nullptr, nullptr};
     std::unique_ptr<mnenc::StripeComm, void (*)(mnenc::StripeComm*)> comm{nullptr, mnenc::destroyStripeComm};
+    bool stripeInLibrary = false;      // set by the in-library striped encode for the length of the call: mnenc_stripe_plan deals the table builds over the communicator
     uint8_t* stripeResult = nullptr;   // striped encode, rank 0: result buffer already filled by the chunked reduce + D2H (stripe_comm.cu)
     cudaStream_t copyStream = nullptr; // second stream of that pipeline, created on first use
     cudaEvent_t evChunk[4] = {};
@@ -192,9 +193,11 @@ int encodeFrames(mnenc_ctx* c, const uint8_t* const* rgb, int onDevice, size_t n
 void finishMpAccounting(mnenc_ctx* c);
 int checkEncodeArgs(mnenc_ctx* c, const void* rgb, size_t w, size_t h, size_t stride, uint8_t** out, size_t* outBytes);
 // stripe_comm.cu / stripe_api.cu: exchanges of the stripe protocol inside the library
-int stripeExchangeHistogram(mnenc_ctx* c);
-int exchangeHistogramSparse(mnenc_ctx* c, BackendBuffers& b, int nSeq);
-int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats, std::vector<SequencePlan>& plans);
+// localRc: result of this rank's local work since the previous exchange. It travels with the exchange; when any rank reports a
+// failure EVERY rank returns an error after the same collective instead of leaving its peers inside the next one.
+int stripeExchangeHistogram(mnenc_ctx* c, int localRc);
+int exchangeHistogramSparse(mnenc_ctx* c, BackendBuffers* b, int nSeq, int localRc);
+int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats, std::vector<SequencePlan>& plans, int localRc);
 int stripeRanks(const mnenc_ctx* c);  // ranks of the context's communicator (1 without one)
 size_t stripeTotalBytes(const mnenc_ctx* c);
 int encodeGroup(mnenc_ctx* c, const uint8_t* rgb, size_t width, size_t height, size_t stride, uint8_t** out, size_t* outBytes);

@@ -63,9 +63,9 @@ int needPhase(mnenc_ctx* c, int phase) {
 
 }  // namespace
 
-int stripeExchangeHistogram(mnenc_ctx* c) {
-    if (int rc = needPhase(c, 3)) return rc;
-    return exchangeHistogramSparse(c, c->stripe->b, 6 * c->K + 1);
+int stripeExchangeHistogram(mnenc_ctx* c, int localRc) {
+    if (!localRc) localRc = needPhase(c, 3);
+    return exchangeHistogramSparse(c, c->stripe ? &c->stripe->b : nullptr, 6 * c->K + 1, localRc);
 }
 
 }  // namespace mnenc
@@ -293,6 +293,11 @@ int mnenc_stripe_histogram(mnenc_t* c, const uint32_t* all_rec2, void** hist_dev
     c->histDirty = true;  // until mnenc_stripe_pack has reset the touched bins
     c->launches += launchHistogramOnly(b, s->M, nSeq, st);
     CU(cudaEventRecord(c->ev[4], st));
+    if (c->failNextBackend) {  // test hook (mnenc_debug_fail_next_backend): an ordinary error return on THIS rank only, bins populated
+        c->failNextBackend = false;
+        CU(waitStream(c));
+        return fail(MNENC_ERR_INTERNAL, "injected failure after the histogram (test hook)");
+    }
     // consistency: the device's stitched RLE size must be what every rank derived from the records
     CU(s->scratch.ensure(64));
     c->launches += launchReadIndirect(b.outOff, b.runIdx + s->N, s->scratch.as<uint32_t>(), st);
@@ -320,32 +325,46 @@ int mnenc_stripe_plan(mnenc_t* c, uint64_t* seq_bits) try {
     const double t0 = nowMs();
     cudaStream_t st = c->stream;
     BackendBuffers& b = s->b;
-    c->launches += launchCompact(b, nSeq, st);
-    CU(c->hNEntries.ensure(4));
-    CU(cudaMemcpyAsync(c->hNEntries.p, b.nEntries, 4, cudaMemcpyDeviceToHost, st));
-    CU(waitStream(c));
-    const uint32_t nEntries = s->nEntries = *c->hNEntries.as<uint32_t>();
-    if (nEntries > c->entryCap) {
-        c->histReady = false;  // bins were consumed; rebuild the clean state on the next encode
-        return fail(MNENC_ERR_INTERNAL, "more than 2^20 distinct (sequence, symbol) pairs");
-    }
-    CU(c->hEntries.ensure(static_cast<size_t>(nEntries) * sizeof(HistEntry) + 16));
-    CU(cudaMemcpyAsync(c->hEntries.p, b.entries, static_cast<size_t>(nEntries) * sizeof(HistEntry), cudaMemcpyDeviceToHost, st));
-    CU(waitStream(c));
-
-    // ---- identical code tables on every rank ----
-    const double tHost0 = nowMs();
-    const HistEntry* ent = c->hEntries.as<HistEntry>();
+    // In-library exchanges: a failure of the local steps up to the table builds must not keep this rank out of planSharded's
+    // collectives (its peers would wait there forever) - it joins them with its error code instead, and every rank stops.
+    const bool dealt = c->stripeInLibrary && stripeRanks(c) > 1;
     std::vector<std::vector<SymbolStat>> stats(nSeq);
-    s->entryOf.assign(nSeq, {});
-    for (uint32_t e = 0; e < nEntries; ++e) {
-        if (ent[e].seq >= static_cast<uint32_t>(nSeq)) return fail(MNENC_ERR_INTERNAL, "bad histogram entry");
-        stats[ent[e].seq].push_back(SymbolStat{ent[e].symbol, ent[e].freq, ent[e].firstPos});
-        s->entryOf[ent[e].seq].push_back(e);
-    }
-    s->plans.assign(nSeq, SequencePlan{});
-    if (stripeRanks(c) > 1) {  // in-library exchanges: the table builds are dealt over the ranks and all-gathered
-        if (int rc = planSharded(c, stats, s->plans)) return rc;
+    uint32_t nEntries = 0;
+    double tHost0 = nowMs();
+    const int prepRc = [&]() -> int {
+        try {
+            c->launches += launchCompact(b, nSeq, st);
+            CU(c->hNEntries.ensure(4));
+            CU(cudaMemcpyAsync(c->hNEntries.p, b.nEntries, 4, cudaMemcpyDeviceToHost, st));
+            CU(waitStream(c));
+            nEntries = s->nEntries = *c->hNEntries.as<uint32_t>();
+            if (nEntries > c->entryCap) {
+                c->histReady = false;  // bins were consumed; rebuild the clean state on the next encode
+                return fail(MNENC_ERR_INTERNAL, "more than 2^20 distinct (sequence, symbol) pairs");
+            }
+            CU(c->hEntries.ensure(static_cast<size_t>(nEntries) * sizeof(HistEntry) + 16));
+            CU(cudaMemcpyAsync(c->hEntries.p, b.entries, static_cast<size_t>(nEntries) * sizeof(HistEntry), cudaMemcpyDeviceToHost, st));
+            CU(waitStream(c));
+
+            // ---- identical code tables on every rank ----
+            tHost0 = nowMs();
+            const HistEntry* ent = c->hEntries.as<HistEntry>();
+            s->entryOf.assign(nSeq, {});
+            for (uint32_t e = 0; e < nEntries; ++e) {
+                if (ent[e].seq >= static_cast<uint32_t>(nSeq)) return fail(MNENC_ERR_INTERNAL, "bad histogram entry");
+                stats[ent[e].seq].push_back(SymbolStat{ent[e].symbol, ent[e].freq, ent[e].firstPos});
+                s->entryOf[ent[e].seq].push_back(e);
+            }
+            s->plans.assign(nSeq, SequencePlan{});
+            return MNENC_OK;
+        } catch (...) {
+            return abiCaught();
+        }
+    }();
+    if (prepRc && !dealt) return prepRc;
+    if (dealt) {  // in-library exchanges only (the caller-driven protocol may run on a context that also owns a communicator, with
+                  // other ranks): table builds dealt over the ranks, all-gathered
+        if (int rc = planSharded(c, stats, s->plans, prepRc)) return rc;
     } else {
         std::vector<int> byLoad(nSeq);
         std::iota(byLoad.begin(), byLoad.end(), 0);

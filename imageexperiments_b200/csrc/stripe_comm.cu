@@ -97,25 +97,62 @@ namespace {
         if ((sc)->sync && !(sc)->sync->arrive()) return ::mnenc::fail(MNENC_ERR_STATE, "another GPU of the group failed"); \
     } while (0)
 
-// all-gather of `bytes` host bytes per rank (small records): H2D, ncclAllGather, D2H on the context's stream
-int allGatherHost(mnenc_ctx* c, const NcclApi* nccl, const void* src, void* dst, size_t bytes) {
+// Failures are collective. A rank whose local work failed must not simply return: its peers would sit in the next NCCL
+// collective forever (there is no time-out, and across processes nobody can abort them). So every host-staged gather carries,
+// in a 16-byte header in front of the payload, the result code of the sender's local work since the previous exchange; after
+// the gather all ranks see all codes and, if any is non-zero, ALL of them return an error from this same point - the failing
+// rank its own code and text, the others MNENC_ERR_STATE naming the failed rank. What this cannot cover: a sticky CUDA error
+// (the rank can no longer launch anything, the collective included) and a rank that dies; both need the process group torn down.
+constexpr size_t kStatusBytes = 16;
+constexpr size_t kStageSlot = size_t(1) << 20;  // reserved per rank at communicator creation, so that the gathers allocate nothing
+
+int groupVerdict(const StripeComm* sc, const unsigned char* slots, size_t slotBytes, int localRc) {
+    for (int r = 0; r < sc->nranks; ++r) {
+        int32_t code = 0;
+        std::memcpy(&code, slots + slotBytes * r, sizeof(code));
+        if (code == 0) continue;
+        if (localRc) return localRc;  // this rank failed too: keep its own error text
+        return fail(MNENC_ERR_STATE, "rank " + std::to_string(r) + " of the group failed (code " + std::to_string(code) +
+                                         "); this rank stopped with it before the next exchange");
+    }
+    return localRc;
+}
+
+// all-gather of `bytes` host bytes per rank (small records): H2D, ncclAllGather, D2H on the context's stream. localRc: see above;
+// when it is non-zero the payload may be garbage (src may even be null), only the header matters.
+int allGatherHost(mnenc_ctx* c, const NcclApi* nccl, const void* src, void* dst, size_t bytes, int localRc) {
     StripeComm* sc = c->comm.get();
     if (sc->nranks == 1) {
-        std::memcpy(dst, src, bytes);
-        return MNENC_OK;
+        if (!localRc && bytes) std::memcpy(dst, src, bytes);
+        return localRc;
     }
-    const size_t padded = (bytes + 15) / 16 * 16;
+    const size_t padded = kStatusBytes + (bytes + 15) / 16 * 16;
+    // beyond the reservation only for very large code tables; a failure HERE still strands the peers (documented in DESIGN 7.2)
     CU(sc->stage.ensure(padded * (sc->nranks + 1)));
     CU(sc->hStage.ensure(padded * (sc->nranks + 1)));
     unsigned char* h = sc->hStage.as<unsigned char>();
     unsigned char* d = sc->stage.as<unsigned char>();
-    std::memcpy(h, src, bytes);
+    const int32_t code = localRc;
+    std::memset(h, 0, kStatusBytes);
+    std::memcpy(h, &code, sizeof(code));
+    if (!localRc && bytes) std::memcpy(h + kStatusBytes, src, bytes);
     MEET(sc);
     CU(cudaMemcpyAsync(d, h, padded, cudaMemcpyHostToDevice, c->stream));
     NC(nccl->allGather(d, d + padded, padded, ncclUint8, sc->comm, c->stream));
     CU(cudaMemcpyAsync(h + padded, d + padded, padded * sc->nranks, cudaMemcpyDeviceToHost, c->stream));
     CU(waitStream(c));
-    for (int r = 0; r < sc->nranks; ++r) std::memcpy(static_cast<unsigned char*>(dst) + r * bytes, h + padded * (r + 1), bytes);
+    if (int rc = groupVerdict(sc, h + padded, padded, localRc)) return rc;
+    if (bytes)
+        for (int r = 0; r < sc->nranks; ++r) std::memcpy(static_cast<unsigned char*>(dst) + r * bytes, h + padded * (r + 1) + kStatusBytes, bytes);
+    return MNENC_OK;
+}
+
+// Before an exchange that carries no host-staged record of its own (the reduce of the segments): gather the codes alone.
+int agreeStatus(mnenc_ctx* c, const NcclApi* nccl, int localRc) { return allGatherHost(c, nccl, nullptr, nullptr, 0, localRc); }
+
+int reserveStage(StripeComm* sc) {
+    CU(sc->stage.ensure(kStageSlot * (sc->nranks + 1)));
+    CU(sc->hStage.ensure(kStageSlot * (sc->nranks + 1)));
     return MNENC_OK;
 }
 
@@ -123,33 +160,47 @@ int allGatherHost(mnenc_ctx* c, const NcclApi* nccl, const void* src, void* dst,
 
 // Sparse exchange of the symbol histogram: local dense tables -> compact entries -> all-gather -> merge into the dense
 // tables of every rank (identical everywhere afterwards, like the three dense all-reduces it replaces).
-int exchangeHistogramSparse(mnenc_ctx* c, BackendBuffers& b, int nSeq) {
+int exchangeHistogramSparse(mnenc_ctx* c, BackendBuffers* bp, int nSeq, int localRc) {
     StripeComm* sc = c->comm.get();
     std::string err;
     const NcclApi* nccl = ncclApi(&err);
     if (!nccl) return fail(MNENC_ERR_CUDA, err);
     cudaStream_t st = c->stream;
     const int nr = sc->nranks;
-    c->launches += launchCompact(b, nSeq, st);  // hist bins -> entries (bins cleared, firstPos = entry index)
-    // counts of every rank
-    CU(sc->stage.ensure(16 * (nr + 1)));
-    CU(sc->hStage.ensure(16 * (nr + 1)));
-    uint32_t* dCounts = sc->stage.as<uint32_t>();
+    if (!localRc && !bp) localRc = fail(MNENC_ERR_STATE, "stripe protocol called out of order");
+    if (!localRc) c->launches += launchCompact(*bp, nSeq, st);  // hist bins -> entries (bins cleared, firstPos = entry index)
+    // {entries, result code of the local work} of every rank: the code rides along, so a rank whose histogram phase failed
+    // still joins this gather (with 0 entries) and every rank stops after it, together (see allGatherHost)
+    uint32_t* dMine = sc->stage.as<uint32_t>();       // reserved at communicator creation
+    uint32_t* dAll = dMine + 4;
+    uint32_t* hMine = sc->hStage.as<uint32_t>();
+    uint32_t* hAll = hMine + 4;
+    hMine[0] = 0, hMine[1] = static_cast<uint32_t>(localRc);
+    CU(cudaMemcpyAsync(dMine, hMine, 8, cudaMemcpyHostToDevice, st));
+    if (!localRc) CU(cudaMemcpyAsync(dMine, bp->nEntries, 4, cudaMemcpyDeviceToDevice, st));
     MEET(sc);
-    NC(nccl->allGather(b.nEntries, dCounts, 1, ncclUint32, sc->comm, st));
-    CU(cudaMemcpyAsync(sc->hStage.p, dCounts, 4 * nr, cudaMemcpyDeviceToHost, st));
+    NC(nccl->allGather(dMine, dAll, 2, ncclUint32, sc->comm, st));
+    CU(cudaMemcpyAsync(hAll, dAll, 8 * nr, cudaMemcpyDeviceToHost, st));
     CU(waitStream(c));
-    const uint32_t* counts = sc->hStage.as<uint32_t>();
+    for (int r = 0; r < nr; ++r)
+        if (hAll[2 * r + 1]) {
+            if (localRc) return localRc;
+            return fail(MNENC_ERR_STATE, "rank " + std::to_string(r) + " of the group failed (code " + std::to_string(static_cast<int32_t>(hAll[2 * r + 1])) +
+                                             "); this rank stopped with it before the histogram exchange");
+        }
+    BackendBuffers& b = *bp;
     uint32_t nMax = 0;
-    for (int r = 0; r < nr; ++r) nMax = std::max(nMax, counts[r]);
+    for (int r = 0; r < nr; ++r) nMax = std::max(nMax, hAll[2 * r]);
+    // the same decision on every rank (all see the same counts), so nobody is left alone in the next gather
     if (nMax > c->entryCap) return fail(MNENC_ERR_INTERNAL, "more than 2^20 distinct (sequence, symbol) pairs on one rank");
-    const uint32_t mine = counts[sc->rank];
+    const uint32_t mine = hAll[2 * sc->rank];
     c->launches += launchResetHistogram(b, mine, st);  // firstPos back to "not seen", maxSym and nEntries to 0; the entry list stays
     if (nMax) {
-        CU(sc->gathered.ensure(static_cast<size_t>(nMax) * nr * sizeof(HistEntry)));
+        // grow-only; sized for the worst case the first time, so that this allocation cannot fail on one rank in a later image
+        CU(sc->gathered.ensure(static_cast<size_t>(c->entryCap) * nr * sizeof(HistEntry)));
         MEET(sc);
         NC(nccl->allGather(b.entries, sc->gathered.p, static_cast<size_t>(nMax) * sizeof(HistEntry), ncclUint8, sc->comm, st));
-        c->launches += launchMergeEntries(b, sc->gathered.as<HistEntry>(), dCounts, nr, nMax, st);
+        c->launches += launchMergeEntries(b, sc->gathered.as<HistEntry>(), dAll, 2, nr, nMax, st);
     }
     return MNENC_OK;
 }
@@ -249,22 +300,34 @@ int planShardApply(const std::vector<std::vector<SymbolStat>>& stats, const unsi
 
 // Code tables of all sequences with the builds dealt over the ranks. stats[q] are this rank's entries of sequence q (same SET
 // on every rank after the histogram merge, order may differ); on return plans[q].code/len follow this rank's order.
-int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats, std::vector<SequencePlan>& plans) {
+int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats, std::vector<SequencePlan>& plans, int localRc) {
     StripeComm* sc = c->comm.get();
     std::string err;
     const NcclApi* nccl = ncclApi(&err);
     if (!nccl) return fail(MNENC_ERR_CUDA, err);
     const int nr = sc->nranks, me = sc->rank;
     std::vector<unsigned char> wire;
-    planShardBuild(stats, me, nr, c->pool.get(), plans, wire);
-    // sizes, then the tables
+    if (!localRc) {
+        try {
+            planShardBuild(stats, me, nr, c->pool.get(), plans, wire);
+        } catch (...) {
+            localRc = abiCaught();  // joins the gather below with its code; every rank stops there
+        }
+    }
+    // sizes (with the result codes of the local work, see allGatherHost), then the tables
     std::vector<uint64_t> sizes(nr);
     const uint64_t mySize = wire.size();
-    if (int rc = allGatherHost(c, nccl, &mySize, sizes.data(), 8)) return rc;
+    if (int rc = allGatherHost(c, nccl, &mySize, sizes.data(), 8, localRc)) return rc;
     const size_t maxSize = static_cast<size_t>(*std::max_element(sizes.begin(), sizes.end()));
-    wire.resize(maxSize);
-    std::vector<unsigned char> all(maxSize * nr);
-    if (int rc = allGatherHost(c, nccl, wire.data(), all.data(), maxSize)) return rc;
+    std::vector<unsigned char> all;
+    int rcLocal = MNENC_OK;
+    try {
+        wire.resize(maxSize);
+        all.resize(maxSize * nr);
+    } catch (...) {
+        rcLocal = abiCaught();
+    }
+    if (int rc = allGatherHost(c, nccl, wire.data(), all.data(), maxSize, rcLocal)) return rc;
     for (int r = 0; r < nr; ++r) {
         if (r == me) continue;
         if (int rc = planShardApply(stats, all.data() + maxSize * r, static_cast<size_t>(sizes[r]), plans)) return rc;
@@ -275,22 +338,28 @@ int planSharded(mnenc_ctx* c, const std::vector<std::vector<SymbolStat>>& stats,
 // reduce(SUM) of the packed words to rank 0, in up to four chunks: while chunk i + 1 is being reduced over NVLink, rank 0 already
 // copies chunk i to the host on a second stream (the 56 MB stream of a 16384^2 image is 1 ms of PCIe time, as long as the rest of
 // the tail together).
-int reduceSegments(mnenc_ctx* c, void* words, size_t nWords) {
+// Rank 0's fallible set-up for reduceSegments (second stream, events, the host result buffer), done BEFORE the ranks agree
+// to enter the reduce: an out-of-memory here is reported to the peers instead of leaving them inside ncclReduce.
+int prepareReduce(mnenc_ctx* c, uint8_t** res) {
+    StripeComm* sc = c->comm.get();
+    *res = nullptr;
+    if (c->stripeResult) resultRelease(c->stripeResult), c->stripeResult = nullptr;
+    if (sc->rank != 0) return MNENC_OK;
+    if (!c->copyStream) CU(cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));
+    for (auto& e : c->evChunk)
+        if (!e) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    *res = resultAcquire(stripeTotalBytes(c));
+    if (!*res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
+    return MNENC_OK;
+}
+
+int reduceSegments(mnenc_ctx* c, void* words, size_t nWords, uint8_t* res) {
     StripeComm* sc = c->comm.get();
     std::string err;
     const NcclApi* nccl = ncclApi(&err);
     if (!nccl) return fail(MNENC_ERR_CUDA, err);
     const size_t totalBytes = stripeTotalBytes(c);
     const int chunks = nWords >= (size_t(1) << 20) ? 4 : 1;
-    uint8_t* res = nullptr;
-    if (c->stripeResult) resultRelease(c->stripeResult), c->stripeResult = nullptr;
-    if (sc->rank == 0) {  // allocations before the meeting point
-        if (!c->copyStream) CU(cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));
-        for (auto& e : c->evChunk)
-            if (!e) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        res = resultAcquire(totalBytes);
-        if (!res) return fail(MNENC_ERR_INTERNAL, "out of host memory");
-    }
     auto bail = [&](int rc) {
         resultRelease(res);
         return rc;
@@ -336,36 +405,55 @@ int encodeStriped(mnenc_ctx* c, const uint8_t* rgb, int onDevice, size_t width, 
         sc->ms[i] += static_cast<float>(now - t);
         t = now;
     };
+    // Every phase's result code goes into the exchange that follows it (allGatherHost): a failing rank still joins that exchange
+    // and all ranks return from there together, instead of the healthy ones waiting in NCCL for a peer that has left.
+    struct InLibrary {  // mnenc_stripe_plan deals the table builds over the communicator only while this call runs
+        mnenc_ctx* c;
+        explicit InLibrary(mnenc_ctx* x) : c(x) { c->stripeInLibrary = true; }
+        ~InLibrary() { c->stripeInLibrary = false; }
+    } inLibrary(c);
     std::vector<uint32_t> rec1(3 * K + 3), all1(static_cast<size_t>(nr) * (3 * K + 3));
-    if (int rc = mnenc_stripe_begin(c, rgb, onDevice, width, height, stride, sc->rank, nr, bx0, bx1, rec1.data())) return rc;
+    int rc = mnenc_stripe_begin(c, rgb, onDevice, width, height, stride, sc->rank, nr, bx0, bx1, rec1.data());
     lap(0);
-    if (int rc = allGatherHost(c, nccl, rec1.data(), all1.data(), rec1.size() * 4)) return rc;
+    if (int g = allGatherHost(c, nccl, rec1.data(), all1.data(), rec1.size() * 4, rc)) return g;
     lap(1);
     std::vector<uint32_t> rec2(static_cast<size_t>(6) * K * 6), all2(rec2.size() * nr);
-    if (int rc = mnenc_stripe_rle(c, all1.data(), rec2.data())) return rc;
+    rc = mnenc_stripe_rle(c, all1.data(), rec2.data());
     lap(2);
-    if (int rc = allGatherHost(c, nccl, rec2.data(), all2.data(), rec2.size() * 4)) return rc;
+    if (int g = allGatherHost(c, nccl, rec2.data(), all2.data(), rec2.size() * 4, rc)) return g;
     lap(3);
     void *hist = nullptr, *first = nullptr, *msym = nullptr;
     size_t nh = 0, nm = 0;
-    if (int rc = mnenc_stripe_histogram(c, all2.data(), &hist, &first, &nh, &msym, &nm)) return rc;
+    rc = mnenc_stripe_histogram(c, all2.data(), &hist, &first, &nh, &msym, &nm);
     lap(4);
-    if (nr > 1)
-        if (int rc = stripeExchangeHistogram(c)) return rc;
+    if (nr > 1) {
+        if (int g = stripeExchangeHistogram(c, rc)) return g;
+    } else if (rc) {
+        return rc;
+    }
     lap(5);
     std::vector<uint64_t> bits(nSeq), allBits(static_cast<size_t>(nSeq) * nr);
-    if (int rc = mnenc_stripe_plan(c, bits.data())) return rc;  // code tables dealt over the ranks when a communicator is set
+    rc = mnenc_stripe_plan(c, bits.data());  // code tables dealt over the ranks; joins its own exchanges even when it fails
     lap(6);
-    if (int rc = allGatherHost(c, nccl, bits.data(), allBits.data(), bits.size() * 8)) return rc;
+    if (int g = allGatherHost(c, nccl, bits.data(), allBits.data(), bits.size() * 8, rc)) return g;
     lap(7);
     void* words = nullptr;
     size_t nWords = 0, nBytes = 0;
-    if (int rc = mnenc_stripe_pack(c, allBits.data(), &words, &nWords, &nBytes)) return rc;
+    rc = mnenc_stripe_pack(c, allBits.data(), &words, &nWords, &nBytes);
     lap(8);
-    if (nr > 1)
-        if (int rc = reduceSegments(c, words, nWords)) return rc;
+    if (nr > 1) {
+        uint8_t* res = nullptr;
+        if (!rc) rc = prepareReduce(c, &res);
+        if (int g = agreeStatus(c, nccl, rc)) {
+            resultRelease(res);
+            return g;
+        }
+        if (int g = reduceSegments(c, words, nWords, res)) return g;
+    } else if (rc) {
+        return rc;
+    }
     lap(9);
-    if (int rc = mnenc_stripe_finish(c, out, outBytes)) return rc;
+    if (int rc2 = mnenc_stripe_finish(c, out, outBytes)) return rc2;
     lap(10);
     return MNENC_OK;
 }
@@ -401,6 +489,7 @@ int mnenc_comm_init_rank(mnenc_t* c, int rank, int nranks, const uint8_t* id128)
     ncclUniqueId id;
     std::memcpy(&id, id128, 128);
     NC(nccl->commInitRank(&sc->comm, nranks, id, rank));
+    if (int rc = reserveStage(sc.get())) return rc;
     c->comm = std::move(sc);
     return MNENC_OK;
 } catch (...) {
@@ -458,6 +547,8 @@ int mnenc_create_multi(mnenc_t** out, const int* devices, int n_devices, int K, 
     for (int i = 0; i < n_devices; ++i) {
         std::unique_ptr<StripeComm, void (*)(StripeComm*)> sc(new StripeComm, destroyStripeComm);
         sc->rank = i, sc->nranks = n_devices, sc->comm = comms[i], sc->sync = sync;
+        CU(cudaSetDevice(devices[i]));
+        if (int rc = reserveStage(sc.get())) return bail(rc);
         ctxs[i]->comm = std::move(sc);
         if (i) ctxs[0]->groupPeers.push_back(ctxs[i]);
     }
@@ -557,8 +648,8 @@ int encodeGroup(mnenc_ctx* c, const uint8_t* rgb, size_t width, size_t height, s
     for (auto& th : threads) th.join();
     int bad = -1;  // the rank that failed first, not one that gave up at the meeting point because of it
     for (int r = 0; r < nr; ++r)
-        if (rcs[r] && (bad < 0 || (errs[bad].find("another GPU of the group failed") != std::string::npos &&
-                                   errs[r].find("another GPU of the group failed") == std::string::npos)))
+        if (rcs[r] && (bad < 0 || (errs[bad].find("of the group failed") != std::string::npos &&  // "another GPU ..." / "rank r ..."
+                                   errs[r].find("of the group failed") == std::string::npos)))
             bad = r;
     if (bad >= 0) {
         for (uint8_t* p : outs) resultRelease(p);

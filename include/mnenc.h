@@ -202,6 +202,10 @@ int mnenc_stripe_finish(mnenc_t* ctx, uint8_t** out, size_t* out_bytes);
  * calls mnenc_comm_init_rank on its context, then all ranks call mnenc_encode_striped_rgb8 collectively with their block
  * columns [bx0, bx1) (arguments as mnenc_stripe_begin). Rank 0 receives the complete `.mn` stream (mnenc_free it), the others
  * *out = NULL. The result is byte-identical to mnenc_encode_rgb8 of the whole image on one GPU.
+ * Errors are collective: each exchange also carries the result code of every rank's local work since the previous one, so when
+ * one rank fails (bad argument, out of memory, ...) ALL ranks return an error from the same point - the failing rank its own
+ * code, the others MNENC_ERR_STATE naming it - and the communicator stays usable. Not covered: a rank that dies or whose CUDA
+ * context is broken (sticky error); its peers then wait in NCCL until the process group is torn down.
  * mnenc_last_stripe_timing: host milliseconds of the last striped encode on this rank — ms[0] begin (H2D, matching pursuit,
  * scatter), [1] gather of sizes, [2] DC + runs, [3] gather of run records, [4] stitched RLE + local histogram, [5] histogram
  * exchange (sparse all-gather + merge), [6] code tables (dealt over the ranks) + payload bits, [7] offset scan gather,
@@ -235,6 +239,9 @@ int mnenc_build_dictionary(int block_size, int threads, float* base_rowmajor, in
 /*
  * Test hook: the next encode on this context fails with MNENC_ERR_INTERNAL right after its histogram kernel has run - an ordinary
  * error return with the histogram bins populated. The encode after that must be unaffected (the context re-clears its tables).
+ * In a striped encode (mnenc_encode_striped_rgb8) it fails the histogram phase of THIS rank only: every rank of the group must
+ * then return an error from the same exchange (the failing rank MNENC_ERR_INTERNAL, its peers MNENC_ERR_STATE) instead of
+ * waiting in NCCL, and the group must encode correctly afterwards.
  */
 int mnenc_debug_fail_next_backend(mnenc_t* ctx);
 /*

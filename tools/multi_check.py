@@ -30,6 +30,18 @@ multi.setQuant(mn.createQuantizationTables(32, 8, 6.0))
 one.setQuant(mn.createQuantizationTables(32, 8, 6.0))
 img = synthetic_rgb(640, 480, 3)
 assert mn.encodeImageFast(img, multi) == mn.encodeImageFast(img, one)
+# a failure on one GPU of the group (test hook: GPU 0's histogram phase) comes back as ONE error naming that GPU - no thread is left
+# waiting in NCCL - and the group encodes correctly right afterwards
+from imageexperiments_b200 import _lib
+_lib.check(_lib.load().mnenc_debug_fail_next_backend(multi._h))
+try:
+    mn.encodeImageFast(img, multi)
+except mn.MnencError as e:
+    assert e.code == -4 and "GPU 0" in str(e) and "injected failure" in str(e), str(e)
+else:
+    raise AssertionError("the injected failure was not reported")
+assert mn.encodeImageFast(img, multi) == mn.encodeImageFast(img, one)
+print("collective failure handling OK (one process)", flush=True)
 multi.close()
 one.close()
 print("multi_check OK", flush=True)

@@ -56,10 +56,59 @@ def main():
         else:
             assert got is None and lib is None
         dist.barrier()
+    if world > 1 and len(sys.argv) < 3:
+        check_collective_failures(mn, ctx, rank, world)
     if rank == 0:
         print("stripe_check OK", flush=True)
     ctx.close()
     dist.destroy_process_group()
+
+
+def check_collective_failures(mn, ctx, rank, world):
+    """One rank fails in the middle of a striped encode: nobody may be left waiting inside NCCL. Every rank has to come back with
+    an error from the same exchange (the failing rank with its own code, its peers with MNENC_ERR_STATE naming it), and the very
+    next striped encode on the same communicator must give the right bytes again."""
+    import ctypes as C
+
+    import torch.distributed as dist
+    from imageexperiments_b200 import _lib
+    from imageexperiments_b200.synth import synthetic_rgb
+
+    L = _lib.load()
+    img = synthetic_rgb(640, 512, 99)
+    want = mn.encodeImageFast(img, ctx) if rank == 0 else None
+    bad = world - 1
+
+    def expect_group_error(own_code, what):
+        try:
+            what()
+        except mn.MnencError as e:
+            assert e.code == (own_code if rank == bad else -3), f"rank {rank}: {e}"
+            if rank != bad:
+                assert f"rank {bad} of the group failed" in str(e), str(e)
+        else:
+            raise AssertionError(f"rank {rank}: the striped encode succeeded although rank {bad} failed")
+        dist.barrier()
+        got = mn.encodeImageStriped(img, ctx)  # the group still works
+        assert (got == want) if rank == 0 else got is None
+
+    # (1) the histogram phase fails on the last rank (test hook): the code travels with the entry-count gather of the histogram exchange
+    if rank == bad:
+        _lib.check(L.mnenc_debug_fail_next_backend(ctx._h))
+    expect_group_error(-4, lambda: mn.encodeImageStriped(img, ctx))
+
+    # (2) the last rank passes block columns outside the image: mnenc_stripe_begin fails there, the code travels with the first gather
+    def bad_columns():
+        nbx = 640 // 8
+        bx0, bx1 = mn.stripeColumns(nbx, world)[rank]
+        if rank == bad:
+            bx1 = nbx + 5
+        out, n = C.c_void_p(), C.c_size_t()
+        _lib.check(L.mnenc_encode_striped_rgb8(ctx._h, C.c_void_p(img.ctypes.data + 24 * bx0), 0, 640, 512, img.strides[0], bx0, bx1, C.byref(out),
+                                               C.byref(n)))
+    expect_group_error(-1, bad_columns)
+    if rank == 0:
+        print(f"collective failure handling OK over {world} ranks (histogram phase, begin phase)", flush=True)
 
 
 if __name__ == "__main__":
