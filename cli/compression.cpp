@@ -111,6 +111,11 @@ std::vector<uint8_t> loadFile(const std::string& path) {
 // `.mndict` (imageexperiments_b200/dictionary.py): "MNDICT1\0" | i32 n_base | i32 cols | i32 rows[n_base] | f32 base | f32 detail Y,U,V
 mnenc_t* createContext(const std::string& exeDir) {
     const char* env = std::getenv("MNENC_DICT");
+    // A `.mn` stream does not say which dictionary wrote it: decoding with another one "succeeds" and gives a wrong picture. So
+    // whenever the dictionary is not the default one, say so once on stderr (the default is the export of the reference build).
+    if (env)
+        std::cerr << "Compression: note: dictionary " << (std::string(env) == "builtin" ? "computed by the library (MNENC_DICT=builtin, own codec revision)" : std::string("from ") + env)
+                  << " - streams written with it decode only with the same dictionary, not with the default one or a reference build\n";
     if (env && std::string(env) == "builtin") {
         // the dictionary computed by the library itself (mnenc_build_dictionary): no reference build needed, but its KLT rows are
         // this library's own codec revision - encode and decode with the same setting

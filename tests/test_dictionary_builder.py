@@ -36,6 +36,16 @@ def test_build_is_deterministic_and_independent_of_the_thread_count(built):
     assert again.sha256() == built.sha256()
 
 
+def test_built_dictionary_is_the_pinned_codec_revision(built):
+    """The computed dictionary defines its own codec revision: a stream written with it only decodes with the very same floats.
+    Its hash is pinned here, so that drift in the host's libm (the covariance model calls exp) or in the builder shows up as a
+    test failure instead of as silently wrong pictures. After a DELIBERATE change of the builder: regenerate
+    tests/golden/built_dictionary.sha256 with Dictionary.build().sha256() and say in DESIGN.md 6 that old streams are orphaned."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "built_dictionary.sha256")
+    assert built.sha256() == open(path).read().strip()
+
+
 def test_refinement_rows_have_the_structure_of_the_reference(built, ref):
     off = np.concatenate([[0], np.cumsum(built.detail_rows)])
     rng = np.random.default_rng(0)
