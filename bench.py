@@ -82,6 +82,16 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def cpu_model() -> str:
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name"):
+                return ln.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
 def cpu_baseline_sample(gpu_ctx=None):
     """The reference's own encodeImageFast (oracle/_ref, unmodified sources) on one core, bounded sample. With `gpu_ctx` the
     same crop also goes through the GPU encoder (outside the timed region): BASELINE.json's "PSNR delta" is reported from the
@@ -100,7 +110,7 @@ def cpu_baseline_sample(gpu_ctx=None):
     R.destroy(ctx)
     out = {"value": round(sw * sh / 1e6 / dt, 4), "unit": "MP/s", "cores": 1, "kind": "reference",
            "sample": f"top-left {sw}x{sh} crop of the workload image, encodeImageFast of the unmodified reference (g++ -O2), "
-                     f"1 thread, {dt:.1f} s, {len(data)} B", "host_cores": os.cpu_count()}
+                     f"1 thread, {dt:.1f} s, {len(data)} B", "host_cores": os.cpu_count(), "cpu_model": cpu_model()}
     if gpu_ctx is not None:
         try:  # the checker must never break the bench line
             import imageexperiments_b200 as mn
@@ -125,17 +135,33 @@ def full_image_parity(gpu_ctx):
     from imageexperiments_b200.synth import synthetic_rgb
     from oracle.bindings import Dictionary as ODict, OracleLib
     img = synthetic_rgb(W, H, seed=12345)
-    t = time.perf_counter()
-    mn.encodeImageFast(img, gpu_ctx)
-    counts, pairs = mn.lastSymbols(gpu_ctx, W, H)
     d = gpu_ctx.dictionary
-    oc = OracleLib().create(ODict(K_ATOMS, 8, d.base, d.detail_rows, d.detail, gpu_ctx.Quant))
-    oc_c, oc_p = oc.symbols_parallel(img)
-    oc.close()
-    same = (counts == oc_c) & (pairs == oc_p).all(axis=(2, 3))
-    return {"full_image": f"{W}x{H}, all {same.shape[0]} blocks against the CPU oracle", "blocks_identical_pct": round(100.0 * float(same.all(axis=1).mean()), 5),
-            "block_channels_identical_pct": round(100.0 * float(same.mean()), 5), "block_channels_identical": int(same.sum()),
-            "block_channels": int(same.size), "bar_pct": 99.9, "oracle_seconds": round(time.perf_counter() - t, 1)}
+
+    def compare():
+        mn.encodeImageFast(img, gpu_ctx)
+        counts, pairs = mn.lastSymbols(gpu_ctx, W, H)
+        oc = OracleLib().create(ODict(K_ATOMS, 8, d.base, d.detail_rows, d.detail, gpu_ctx.Quant))
+        oc_c, oc_p = oc.symbols_parallel(img)
+        oc.close()
+        return (counts == oc_c) & (pairs == oc_p).all(axis=(2, 3))
+
+    t = time.perf_counter()
+    same = compare()
+    out = {"full_image": f"{W}x{H}, all {same.shape[0]} blocks against the CPU oracle", "blocks_identical_pct": round(100.0 * float(same.all(axis=1).mean()), 5),
+           "block_channels_identical_pct": round(100.0 * float(same.mean()), 5), "block_channels_identical": int(same.sum()),
+           "block_channels": int(same.size), "bar_pct": 99.9, "oracle_seconds": round(time.perf_counter() - t, 1)}
+    per_quality = []  # BASELINE.json configs[2]: the same whole-image comparison at the other qualities of the sweep
+    try:
+        for q in (1.0, 2.0, 5.0, 8.0):
+            gpu_ctx.setQuant(mn.createQuantizationTables(K_ATOMS, 8, q))
+            sq = compare()
+            per_quality.append({"quality": q, "blocks_identical_pct": round(100.0 * float(sq.all(axis=1).mean()), 5),
+                                "block_channels_identical_pct": round(100.0 * float(sq.mean()), 5)})
+    finally:
+        gpu_ctx.setQuant(mn.createQuantizationTables(K_ATOMS, 8, QUALITY))
+    out["per_quality"] = per_quality
+    out["oracle_seconds_all_qualities"] = round(time.perf_counter() - t, 1)
+    return out
 
 
 _REF = {}
@@ -172,16 +198,39 @@ def decode_sample(ctx, inputs):
 SW, SH = 16384, 16384  # BASELINE.json configs[3]
 
 
-def stripe_image_columns(x0, x1):
-    """Columns [x0, x1) of the configs[3] image: the 2048x2048 seeded synthetic tile repeated (a 268 MP image from the numpy
-    generator itself would need minutes and tens of GB on every rank; statistics per block are those of the tile)."""
+_band_tiles = {}
+_band_lock = threading.Lock()
+
+
+def band_tile(band: int):
+    """The 2048x2048 seeded synthetic tile of column band `band` (columns [2048 * band, 2048 * band + 2048)): seed 12345 + band."""
     from imageexperiments_b200.synth import synthetic_rgb
-    tile = synthetic_rgb(2048, 2048, 12345)
-    cols = tile[:, np.arange(x0, x1) % 2048]
-    return np.ascontiguousarray(np.tile(cols, ((SH + 2047) // 2048, 1, 1))[:SH])
+    with _band_lock:
+        t = _band_tiles.get(band)
+    if t is None:
+        t = synthetic_rgb(2048, 2048, 12345 + band)
+        with _band_lock:
+            _band_tiles[band] = t
+    return t
 
 
-def stripes_record(ctx, rank, world, local, steps, barrier, max_over_ranks):
+def stripe_image_columns(x0, x1):
+    """Columns [x0, x1) of the configs[3] image. Every 2048-column band has its OWN seeded synthetic tile (seed 12345 + band),
+    repeated down the band - so the stripes of different ranks differ in content (edges, first atoms, symbol statistics) and the
+    load balance between the ranks is a measurement, not a given. (One 268 MP run of the numpy generator would need minutes and
+    tens of GB on every rank; the vertical repetition does not matter to a partition by block COLUMNS.)"""
+    from concurrent.futures import ThreadPoolExecutor
+    bands = list(range(x0 // 2048, (x1 - 1) // 2048 + 1))
+    with ThreadPoolExecutor(max_workers=min(8, max(1, len(bands)))) as ex:
+        list(ex.map(band_tile, bands))
+    parts = []
+    for b in bands:
+        lo, hi = max(x0, 2048 * b), min(x1, 2048 * (b + 1))
+        parts.append(np.tile(band_tile(b)[:, lo - 2048 * b:hi - 2048 * b], ((SH + 2047) // 2048, 1, 1))[:SH])
+    return np.ascontiguousarray(np.concatenate(parts, axis=1)) if len(parts) > 1 else np.ascontiguousarray(parts[0])
+
+
+def stripes_record(ctx, rank, world, local, steps, barrier, max_over_ranks, cpu_barrier=lambda: None):
     """BASELINE.json configs[3]: ONE 16384x16384 image sharded by block columns over the ranks, every exchange inside the
     library over NCCL (mnenc_encode_striped_rgb8). Outside the timed region rank 0 checks the bytes against the single-GPU
     encodeImageFast of the same image and round-trips a stripe-sharded 2048x1024 crop through the reference decoder."""
@@ -212,17 +261,19 @@ def stripes_record(ctx, rank, world, local, steps, barrier, max_over_ranks):
         tm = {}
         dt, nbytes = run(dev, steps, tm)
         dt_e2e, _ = run(pin, steps)
-        mp_ms = max_over_ranks(float(ctx.last_timing()[0][1]))
+        mp_ms_mine = float(ctx.last_timing()[0][1])
+        mp_ms = max_over_ranks(mp_ms_mine)
+        mp_ms_min = -max_over_ranks(-mp_ms_mine)
         striped = mn.encodeImageStriped(dev, ctx, width=SW)
         rec = None
         if rank == 0:
             mpix = SW * SH / 1e6
-            rec = {"workload": f"{SW}x{SH} RGB (2048x2048 seeded synthetic tile repeated), quality {QUALITY}, ONE image sharded by block columns "
+            rec = {"workload": f"{SW}x{SH} RGB (non-periodic across ranks: every 2048-column band has its own seeded synthetic tile, seed 12345 + band), quality {QUALITY}, ONE image sharded by block columns "
                                f"over {world} GPU(s); exchanges inside the library (NCCL): sparse histogram all-gather + merge, code tables dealt "
                                "over the ranks, offset scan, reduce of the packed segments to rank 0",
                    "value": round(mpix / dt, 1), "unit": "MP/s", "ms_per_image": round(dt * 1e3, 3), "e2e": round(mpix / dt_e2e, 1),
                    "e2e_ms_per_image": round(dt_e2e * 1e3, 3), "h2d_bytes_per_image": SW * SH * 3, "d2h_bytes_per_image": nbytes,
-                   "mp_ms_max_over_ranks": round(mp_ms, 3), "bytes_out": nbytes, "steps": steps,
+                   "mp_ms_max_over_ranks": round(mp_ms, 3), "mp_ms_min_over_ranks": round(mp_ms_min, 3), "bytes_out": nbytes, "steps": steps,
                    "rank0_phase_ms": {k: round(v / steps * 1e3, 3) for k, v in tm.items()}}
         # ---- parity, outside the timed region ----
         dev = pin = None
@@ -237,7 +288,24 @@ def stripes_record(ctx, rank, world, local, steps, barrier, max_over_ranks):
                 full = np.concatenate([stripe_image_columns(x, min(x + 2048, SW)) for x in range(0, SW, 2048)], axis=1)
                 single = mn.encodeImageFast(full, ctx)
                 parity["bytes_identical_to_single_gpu"] = bool(bytes(single) == bytes(striped))
-                full = single = None
+                single = None
+                if world > 1:  # the one-process route (mnenc_create_multi: ncclCommInitAll, one host thread per GPU) - what the shim and the CLI use
+                    try:
+                        multi = mn.createCompressionContextFast(K_ATOMS, 8, QUALITY, device=list(range(world)))
+                        small = make_ring(0)[0]
+                        same_small = bytes(mn.encodeImageFast(small, multi)) == bytes(mn.encodeImageFast(small, ctx))
+                        got = mn.encodeImageFast(full, multi, zero_copy=True)
+                        t0 = time.perf_counter()
+                        got = mn.encodeImageFast(full, multi, zero_copy=True)
+                        dt1 = time.perf_counter() - t0
+                        rec["one_process"] = {"bytes_identical": bool(bytes(got) == bytes(striped)), "workload_image_bytes_identical": bool(same_small),
+                                              "ms_per_image": round(dt1 * 1e3, 3), "value": round(SW * SH / 1e6 / dt1, 1),
+                                              "note": f"rank 0 alone, ONE context over {world} GPUs (the other ranks' processes idle), pageable host image in, host stream out"}
+                        got = None
+                        multi.close()
+                    except Exception as e:  # noqa: BLE001
+                        rec["one_process"] = {"error": repr(e)}
+                full = None
                 from oracle.bindings import RefLib, ref_available
                 if ref_available():
                     R = RefLib()
@@ -251,8 +319,10 @@ def stripes_record(ctx, rank, world, local, steps, barrier, max_over_ranks):
             except Exception as e:  # noqa: BLE001
                 parity["error"] = repr(e)
             rec["parity"] = parity
+        cpu_barrier()  # the other ranks wait here on the CPU (no NCCL kernel spinning on their GPUs) while rank 0 checks
         return rec
     except Exception as e:  # noqa: BLE001
+        cpu_barrier()
         return {"error": repr(e)} if rank == 0 else None
 
 
@@ -395,7 +465,7 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{W}x{H} RGB synthetic, quality {QUALITY}, K={K_ATOMS}, block 8 (BASELINE.json configs[1])", "sample": sample},
-        "cpu_baseline": {"value": round(value, 4), "unit": "MP/s", "cores": workers, "kind": "reference", "sample": sample},
+        "cpu_baseline": {"value": round(value, 4), "unit": "MP/s", "cores": workers, "kind": "reference", "sample": sample, "cpu_model": cpu_model()},
         "e2e": {"value": round(value, 4), "unit": "MP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -413,8 +483,14 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: there is no CPU fallback for the encoder")
     torch.cuda.set_device(local)
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        cpu_group = dist.new_group(backend="gloo")
+
+    def cpu_barrier():
+        if cpu_group is not None:
+            dist.barrier(group=cpu_group)
 
     def barrier():
         if world > 1:
@@ -480,13 +556,14 @@ def run_ours(args):
     lat_s, mp_ms, flops = timed_single(dev)
     dt_dev, out_b, launches = timed(dev)
     dt_e2e, out_b2, _ = timed(pinned)
-    dt_dev2, _, _ = timed(dev)  # the resident pass again, after the end-to-end pass: the better of the two is reported
-    dt_dev = min(dt_dev, dt_dev2)
+    dt_dev2, _, _ = timed(dev)  # the resident pass again, after the end-to-end pass: `value` is all the work of both passes / all their time
+    passes_ms = [round(dt_dev / args.steps * 1e3, 3), round(dt_dev2 / args.steps * 1e3, 3)]
+    dt_dev = 0.5 * (dt_dev + dt_dev2)
     mp_total = world * args.steps * BATCH * W * H / 1e6
     value = mp_total / dt_dev
     e2e = mp_total / dt_e2e
     quick = os.environ.get("MNENC_BENCH_SKIP_EXTRAS") == "2"  # (development switch: the headline pass only)
-    stripes = None if quick else stripes_record(ctx, rank, world, local, 5, barrier, max_over_ranks)
+    stripes = None if quick else stripes_record(ctx, rank, world, local, 5, barrier, max_over_ranks, cpu_barrier)
     frames = None if quick else batch1080p_record(ctx, rank, world, barrier, max_over_ranks)
 
     if rank == 0:
@@ -505,11 +582,18 @@ def run_ours(args):
         fp32_peak = 148 * 128 * sm_max * 1e6 / 1e12  # unfused mul+add issue slots: what an exact full-scan kernel would be bound by
         achieved = flops / (mp_ms / 1e3) / 1e12 if mp_ms > 0 else 0.0
         control_d2h = 65536 * 16 + 4096
-        prof = {}
-        try:
+        prof, prof_note = {}, "no ncu summary found"
+        try:  # ncu-derived DRAM traffic: only reported while the kernel source still is the one that was profiled
+            import hashlib
             prof = json.load(open(os.path.join(ROOT, "profiles", "r02_mp_ncu_summary.json")))
+            valid = prof.get("valid_for", {})
+            now = hashlib.sha256(open(os.path.join(ROOT, valid.get("file", "imageexperiments_b200/csrc/mp_wave.cu")), "rb").read()).hexdigest()
+            if now == valid.get("sha256"):
+                prof_note = f"profiles/r02_mp_ncu_summary.json (ncu capture; {valid.get('file')} still hashes to the profiled source {now[:12]})"
+            else:
+                prof, prof_note = {}, "dropped: the kernel source changed since the ncu capture in profiles/r02_mp_ncu_summary.json"
         except Exception:
-            pass
+            prof = {}
         line = {
             "metric": METRIC, "value": round(value, 2), "unit": "MP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(dt_dev / args.steps * 1e3, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -518,7 +602,8 @@ def run_ours(args):
                                    "through encodeImageBatch (pipelined lanes; every stream byte-identical to the one-at-a-time encode)",
                        "parallelism": f"image-parallel replicas x{world}, no data-path collective (the stripe-sharded single image with its NCCL exchanges is the `stripes` record)",
                        "l2": f"ring of {RING} distinct {W * H * 3 / 1e6:.1f} MB inputs per GPU ({RING * W * H * 3 / 1e6:.0f} MB > 126 MB L2)",
-                       "timed": "value: pixels resident in HBM, stream returned to host (better of two passes, before and after the e2e pass); e2e: pinned host pixels, H2D+D2H inside"},
+                       "timed": "value: pixels resident in HBM, stream returned to host (mean of two passes of `steps` steps, before and after the e2e pass; both in resident_passes_ms_per_step); e2e: pinned host pixels, H2D+D2H inside"},
+            "resident_passes_ms_per_step": passes_ms,
             "clocks": clocks,
             "e2e": {"value": round(e2e, 2), "unit": "MP/s", "h2d_bytes_per_step": BATCH * W * H * 3, "d2h_bytes_per_step": int(out_b2) + BATCH * control_d2h,
                     "ms_per_step": round(dt_e2e / args.steps * 1e3, 3)},
@@ -531,13 +616,11 @@ def run_ours(args):
                                  "traffic = dram read+write bytes of all matching-pursuit launches of one image, summed from the ncu capture "
                                  "summarised in profiles/r02_mp_ncu_summary.json (algorithmic: 48.3 MB pixels in + 11.7 MB symbols out; the "
                                  "residuals live in HBM between the rounds: 0.64 KB read + written per block-channel and iteration)",
-                         "per_kernel": prof.get("per_kernel"),
+                         "per_kernel": prof.get("per_kernel"), "traffic_source": prof_note,
                          "frac_of_fp32_issue_peak": round(achieved / fp32_peak, 4),
                          "ms_per_launch": round(mp_ms, 3), "gflop_per_launch": round(flops / 1e9, 2)},
             "bytes_out_per_step": int(out_b),
             "single_image_latency_ms": round(lat_s * 1e3, 3),
-            "stripes": stripes,
-            "batch1080p": frames,
         }
         if world == 1 and not os.environ.get("MNENC_BENCH_SKIP_EXTRAS"):  # (development switch: scaling runs on a shared multi-GPU box)
             line["cpu_baseline"] = cpu_baseline_sample(ctx)
@@ -545,6 +628,8 @@ def run_ours(args):
             line["vs_cpu_reference_1core"] = round(value / cb, 1) if cb else None
             line["quality_sweep"] = quality_sweep_record(ctx, tensor_peak)
             line["decode"] = decode_sample(ctx, pinned)
+        line["batch1080p"] = frames  # the two scaling records go LAST, so that a tail of the line still holds them
+        line["stripes"] = stripes
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
